@@ -1,0 +1,446 @@
+"""Optimal-control front end with the reference's Python surface for the transcription path.
+
+Mirrors ``oc.ODEArguments`` (/root/reference/src/OptimalControl/ODEArguments.h:22-39), ``oc.ODEBase``
+(/root/reference/asset_asrl/OptimalControl/ODEBaseClass.py:7-254), ``ode.phase(...)`` (ODE.h:138-166) and the phase
+methods bound in ODEPhaseBaseBind.cpp.  The transcription itself (index maps, function list) runs in C++
+(csrc/phase.cpp); this file only forwards.  PSIOPT (the interior-point solver and its sparse LDLT) is out of scope:
+``phase.optimize()`` raises, while ``phase.transcribe()`` returns the NonLinearProgram whose eval* methods run on
+the GPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from . import VectorFunctions as vf
+from ._lib import lib
+from .Solvers import NonLinearProgram
+from .VectorFunctions import GRAPH, Arguments, ScalarFunction, VectorFunction
+
+
+class _Enum:
+    @classmethod
+    def parse(cls, v):
+        if isinstance(v, str):
+            for k, val in cls.__dict__.items():
+                if not k.startswith("_") and k.lower() == v.lower():
+                    return val
+            alias = getattr(cls, "_alias", {})
+            if v in alias:
+                return alias[v]
+            raise ValueError(f"Unrecognized {cls.__name__} string: {v}")
+        return int(v)
+
+
+class PhaseRegionFlags(_Enum):
+    NotSet, Front, Back, FrontandBack, BackandFront, Path, InnerPath, NodalPath, DefectPath, PairWisePath, \
+        DefectPairWisePath, FrontNodalBackPath, Params, ODEParams, StaticParams, Accumulate, BlockDefectPath = range(17)
+    _alias = {"First": 1, "Last": 2, "FirstandLast": 3, "LastandFirst": 4}
+
+
+class TranscriptionModes(_Enum):
+    LGL3, LGL5, LGL7, Trapezoidal, CentralShooting = range(5)
+
+
+class ControlModes(_Enum):
+    HighestOrderSpline, FirstOrderSpline, NoSpline, BlockConstant = range(4)
+
+
+class IntegralModes(_Enum):
+    BaseIntegral, SimpsonIntegral, TrapIntegral = range(3)
+
+
+class ODEArguments(Arguments):
+    """Arguments laid out as [X, t, U, P] (ODEArguments.h:22-39)."""
+
+    def __init__(self, Xv, Uv=0, Pv=0):
+        self._xv, self._uv, self._pv = int(Xv), int(Uv or 0), int(Pv or 0)
+        super().__init__(self._xv + 1 + self._uv + self._pv)
+
+    def XVars(self):
+        return self._xv
+
+    def UVars(self):
+        return self._uv
+
+    def PVars(self):
+        return self._pv
+
+    def XVec(self):
+        return self.head(self._xv)
+
+    def XtVec(self):
+        return self.head(self._xv + 1)
+
+    def XVar(self, i):
+        return self.coeff(i)
+
+    def TVar(self):
+        return self.coeff(self._xv)
+
+    def UVec(self):
+        return self.segment(self._xv + 1, self._uv)
+
+    def UVar(self, i):
+        return self.coeff(self._xv + 1 + i)
+
+    def PVec(self):
+        return self.tail(self._pv)
+
+    def PVar(self, i):
+        return self.coeff(self._xv + 1 + self._uv + i)
+
+
+def _idx(v):
+    if v is None:
+        return []
+    if isinstance(v, (int, np.integer)):
+        return [int(v)]
+    return [int(k) for k in v]
+
+
+def _rawnode(kind, ir, orows, ch=(), d=(), ip=()):
+    """Node with the type a C++-built helper has in the reference: not wrapped in a GenericFunction."""
+    n = GRAPH.node(kind, ir, orows, [c.node for c in ch], d, ip, -1, 1)
+    return (ScalarFunction if orows == 1 else VectorFunction)(n, ir, orows)
+
+
+def _lu_bound(lb, ub, lbs, ubs):
+    """StackedOutputs{(lb - x) * lbscale, (x - ub) * ubscale} (ODEPhaseBase.cpp:110-130)."""
+    x = _rawnode(vf.VK_ARGS, 1, 1)
+    low = _rawnode(vf.VK_SCALED, 1, 1, [_rawnode(vf.VK_VECMINUS, 1, 1, [x], d=[lb])], d=[lbs])
+    up = _rawnode(vf.VK_SCALED, 1, 1, [_rawnode(vf.VK_ADDVEC, 1, 1, [x], d=[-ub])], d=[ubs])
+    return _rawnode(vf.VK_STACK, 1, 2, [low, up])
+
+
+class ODEBase:
+    """oc.ODEBase(odefunc, Xvars, Uvars, Pvars) (ODEBaseClass.py:7-41)."""
+
+    def __init__(self, odefunc, Xvars, Uvars=None, Pvars=None, Vgroups=None):
+        self.XV, self.UV, self.PV = int(Xvars), int(Uvars or 0), int(Pvars or 0)
+        if not isinstance(odefunc, VectorFunction):
+            raise TypeError("odefunc must be a VectorFunction")
+        if odefunc.ir != self.XV + 1 + self.UV + self.PV or odefunc.orows != self.XV:
+            raise ValueError("ODE function sizes do not match Xvars/Uvars/Pvars")
+        self.odefunc = odefunc
+        self.ode = self
+
+    def XVars(self):
+        return self.XV
+
+    def UVars(self):
+        return self.UV
+
+    def PVars(self):
+        return self.PV
+
+    def TVar(self):
+        return self.XV
+
+    def XtUVars(self):
+        return self.XV + 1 + self.UV
+
+    def IRows(self):
+        return self.odefunc.ir
+
+    def ORows(self):
+        return self.XV
+
+    def vf(self):
+        return self.odefunc
+
+    def phase(self, mode, Traj=None, numDefects=None, LerpIG=True):
+        ph = ODEPhase(self, mode)
+        if Traj is not None:
+            ph.setTraj(Traj, numDefects)
+        return ph
+
+    def integrator(self, *a, **k):
+        raise NotImplementedError("integrators are outside the KKT evaluation path (SURVEY.md section 2, row 15)")
+
+
+class ODEPhase:
+    """The phase object returned by ``ode.phase(mode, Traj, n)`` (ODEPhaseBase / ODEPhase<DODE>)."""
+
+    def __init__(self, ode, mode):
+        self.ode = ode
+        self.tmode = TranscriptionModes.parse(mode)
+        if self.tmode == TranscriptionModes.CentralShooting:
+            raise NotImplementedError("CentralShooting needs the sequential integrators, which are outside the KKT path")
+        self.h = None
+        self._nseg = 0
+        self._cmode = ControlModes.FirstOrderSpline
+        self._imode = IntegralModes.BaseIntegral
+        self._funcs = []  # (role, fun, region, xtuv, opv, spv, ext) in insertion order
+        self._spv = 0
+        self._static = np.zeros(0)
+        self._bins = (np.array([0.0, 1.0]), None)
+        self._traj = None
+        self.Threads = 1
+        self.nlp = None
+
+    # ------------------------------------------------------------------ mesh / trajectory
+    def _rebuild(self):
+        if self.h:
+            lib.ab_phase_destroy(self.h)
+        self.h = lib.ab_phase_create(GRAPH.h, self.ode.odefunc.node, self.ode.XV, self.ode.UV, self.ode.PV, self.tmode, self._nseg)
+        if not self.h:
+            raise ValueError(_lib.last_error())
+        _lib.check(lib.ab_phase_set_control_mode(self.h, self._cmode))
+        _lib.check(lib.ab_phase_set_integral_mode(self.h, self._imode))
+        _lib.check(lib.ab_phase_set_static_params(self.h, self._spv))
+        sp, defs = self._bins
+        if defs is not None:
+            a, ap = _lib.darr(sp)
+            b, bp = _lib.iarr(defs)
+            _lib.check(lib.ab_phase_set_mesh(self.h, len(b), ap, bp))
+        for (role, fun, reg, x, o, s, e) in self._funcs:
+            xa, xp = _lib.iarr(x)
+            oa, op = _lib.iarr(o)
+            sa, sp_ = _lib.iarr(s)
+            ea, ep = _lib.iarr(e)
+            _lib.check(lib.ab_phase_add_function(self.h, role, fun.node, reg, xp, len(xa), op, len(oa), sp_, len(sa), ep, len(ea)))
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.ab_phase_destroy(self.h)
+        except Exception:
+            pass
+
+    def dims(self):
+        out = (C.c_int * 8)()
+        _lib.check(lib.ab_phase_dims(self.h, out))
+        return dict(zip(["numPhaseVars", "numStates", "numDefects", "cardinalStates", "XtUVars", "PVars", "StaticPVars",
+                         "blocked"], list(out)))
+
+    def state_spacing(self):
+        n = self.dims()["numStates"]
+        out = np.zeros(n)
+        _lib.check(lib.ab_phase_state_spacing(self.h, _lib.dptr(out)))
+        return out
+
+    def setTraj(self, Traj, numDefects=None, DefBinSpacing=None, DefsPerBin=None, LerpIG=True):
+        """Resample ``Traj`` (list of [X,t,U,P] states) onto the collocation mesh by linear interpolation in time.
+
+        The reference's default is its LGLInterpTable; only the ``LerpIG`` behaviour is provided because the
+        interpolation tables are outside the KKT path.  A trajectory that already has exactly numStates nodes is
+        taken as is."""
+        T = np.asarray(Traj, dtype=np.float64)
+        if T.ndim != 2 or T.shape[1] != self.ode.XtUVars() + self.ode.PV:
+            raise ValueError("Trajectory states must have XVars+1+UVars+PVars entries")
+        if not np.all(np.isfinite(T)):
+            raise ValueError("NaN or Inf detected in trajectory")
+        if DefBinSpacing is not None:
+            self._bins = (np.asarray(DefBinSpacing, dtype=np.float64), np.asarray(DefsPerBin, dtype=np.int32))
+            self._nseg = int(np.sum(DefsPerBin))
+        else:
+            if numDefects is None:
+                raise ValueError("number of segments required")
+            self._nseg = int(numDefects)
+            self._bins = (np.array([0.0, 1.0]), None)
+        self._rebuild()
+        d = self.dims()
+        S = d["numStates"]
+        if T.shape[0] == S:
+            self._traj = T.copy()
+        else:
+            tv = self.ode.XV
+            t0, tf = T[0, tv], T[-1, tv]
+            ts = t0 + (tf - t0) * self.state_spacing()
+            self._traj = np.stack([np.interp(ts, T[:, tv], T[:, k]) for k in range(T.shape[1])], axis=1)
+            self._traj[:, tv] = ts
+        self.nlp = None
+
+    def returnTraj(self):
+        return [r.copy() for r in self._traj]
+
+    def setStaticParams(self, params):
+        self._static = np.asarray(params, dtype=np.float64).ravel()
+        self._spv = self._static.size
+        if self.h:
+            self._rebuild()
+        self.nlp = None
+
+    def setControlMode(self, m):
+        self._cmode = ControlModes.parse(m)
+        if self.h:
+            self._rebuild()
+        self.nlp = None
+
+    def setIntegralMode(self, m):
+        self._imode = IntegralModes.parse(m)
+        if self.h:
+            self._rebuild()
+        self.nlp = None
+
+    def setThreads(self, *a):
+        self.Threads = int(a[0]) if a else 1
+
+    # ------------------------------------------------------------------ function registration
+    def _add(self, role, fun, reg, x, o=(), s=(), e=()):
+        reg = PhaseRegionFlags.parse(reg)
+        x, o, s, e = _idx(x), _idx(o), _idx(s), _idx(e)
+        if reg == PhaseRegionFlags.ODEParams and not o:
+            x, o = [], x
+        elif reg == PhaseRegionFlags.StaticParams and not s:
+            x, s = [], x
+        if not isinstance(fun, VectorFunction):
+            raise TypeError("expected a VectorFunction")
+        self._funcs.append((role, fun, reg, x, o, s, e))
+        if self.h:
+            xa, xp = _lib.iarr(x)
+            oa, op = _lib.iarr(o)
+            sa, sp_ = _lib.iarr(s)
+            ea, ep = _lib.iarr(e)
+            _lib.check(lib.ab_phase_add_function(self.h, role, fun.node, reg, xp, len(xa), op, len(oa), sp_, len(sa), ep, len(ea)))
+        self.nlp = None
+        return len(self._funcs) - 1
+
+    def addEqualCon(self, reg, fun, XtUvars, OPvars=(), SPvars=()):
+        return self._add(1, fun, reg, XtUvars, OPvars, SPvars)
+
+    def addInequalCon(self, reg, fun, XtUvars, OPvars=(), SPvars=()):
+        return self._add(2, fun, reg, XtUvars, OPvars, SPvars)
+
+    def addStateObjective(self, reg, fun, XtUvars, OPvars=(), SPvars=()):
+        return self._add(0, fun, reg, XtUvars, OPvars, SPvars)
+
+    def addIntegralObjective(self, fun, XtUvars, OPvars=(), SPvars=()):
+        return self._add(3, fun, PhaseRegionFlags.Path, XtUvars, OPvars, SPvars)
+
+    def addIntegralParamFunction(self, fun, XtUvars, accum_param, OPvars=(), SPvars=()):
+        return self._add(4, fun, PhaseRegionFlags.Path, XtUvars, OPvars, SPvars, _idx(accum_param))
+
+    def addBoundaryValue(self, reg, args, value):
+        value = np.atleast_1d(np.asarray(value, dtype=np.float64))
+        args = _idx(args)
+        x = _rawnode(vf.VK_ARGS, value.size, value.size)
+        return self.addEqualCon(reg, _rawnode(vf.VK_ADDVEC, value.size, value.size, [x], d=-value), args)
+
+    def addDeltaVarEqualCon(self, var, value, scale=1.0):
+        a = _rawnode(vf.VK_ARGS, 2, 2)
+        d = _rawnode(vf.VK_DIFF, 2, 1, [_rawnode(vf.VK_SEGMENT, 2, 1, [a], ip=[1, 1]), _rawnode(vf.VK_SEGMENT, 2, 1, [a], ip=[0, 1])])
+        f = _rawnode(vf.VK_SCALED, 2, 1, [_rawnode(vf.VK_ADDVEC, 2, 1, [d], d=[-float(value)])], d=[float(scale)])
+        return self.addEqualCon(PhaseRegionFlags.FrontandBack, f, var)
+
+    def addDeltaTimeEqualCon(self, value, scale=1.0):
+        return self.addDeltaVarEqualCon(self.ode.TVar(), value, scale)
+
+    def addLUVarBound(self, reg, var, lowerbound, upperbound, lbscale=1.0, ubscale=None):
+        if lowerbound > upperbound:
+            raise ValueError("Lower-bound greater than Upper-bound")
+        ubscale = lbscale if ubscale is None else ubscale
+        return self.addInequalCon(reg, _lu_bound(lowerbound, upperbound, lbscale, ubscale), var)
+
+    def addLUVarBounds(self, reg, vars_, lowerbound, upperbound, scale=1.0):
+        return [self.addLUVarBound(reg, v, lowerbound, upperbound, scale) for v in _idx(vars_)]
+
+    def addLowerVarBound(self, reg, var, lowerbound, lbscale=1.0):
+        x = _rawnode(vf.VK_ARGS, 1, 1)
+        return self.addInequalCon(reg, _rawnode(vf.VK_SCALED, 1, 1, [_rawnode(vf.VK_VECMINUS, 1, 1, [x], d=[lowerbound])], d=[lbscale]), var)
+
+    def addUpperVarBound(self, reg, var, upperbound, ubscale=1.0):
+        x = _rawnode(vf.VK_ARGS, 1, 1)
+        return self.addInequalCon(reg, _rawnode(vf.VK_SCALED, 1, 1, [_rawnode(vf.VK_ADDVEC, 1, 1, [x], d=[-upperbound])], d=[ubscale]), var)
+
+    def addLUFuncBound(self, reg, func, XtUvars, lowerbound, upperbound, lbscale=1.0, ubscale=None, OPvars=(), SPvars=()):
+        if lowerbound > upperbound:
+            raise ValueError("Lower-bound greater than Upper-bound")
+        ubscale = lbscale if ubscale is None else ubscale
+        lub = _lu_bound(lowerbound, upperbound, lbscale, ubscale)
+        n = GRAPH.node(vf.VK_NESTED, func.ir, 2, [lub.node, func.node], (), (), -1, 1)
+        return self.addInequalCon(reg, VectorFunction(n, func.ir, 2), XtUvars, OPvars, SPvars)
+
+    def _norm_bound(self, reg, XtUvars, lb, ub, lbs, ubs, p):
+        XtUvars = _idx(XtUvars)
+        size = len(XtUvars) * (2 if PhaseRegionFlags.parse(reg) in (3, 4) else 1)
+        args = _rawnode(vf.VK_ARGS, size, size)
+        nrm = _rawnode(vf.VK_NORM, size, 1, [args], ip=[p])
+        return self.addLUFuncBound(reg, nrm, XtUvars, lb, ub, lbs, ubs)
+
+    def addLUNormBound(self, reg, XtUvars, lowerbound, upperbound, lbscale=1.0, ubscale=None):
+        return self._norm_bound(reg, XtUvars, lowerbound, upperbound, lbscale, ubscale, 1)
+
+    def addLUSquaredNormBound(self, reg, XtUvars, lowerbound, upperbound, lbscale=1.0, ubscale=None):
+        return self._norm_bound(reg, XtUvars, lowerbound, upperbound, lbscale, ubscale, 2)
+
+    def addValueObjective(self, reg, var, scale):
+        x = _rawnode(vf.VK_ARGS, 1, 1)
+        return self.addStateObjective(reg, _rawnode(vf.VK_SCALED, 1, 1, [x], d=[float(scale)]), var)
+
+    def addDeltaVarObjective(self, var, scale):
+        a = _rawnode(vf.VK_ARGS, 2, 2)
+        d = _rawnode(vf.VK_DIFF, 2, 1, [_rawnode(vf.VK_SEGMENT, 2, 1, [a], ip=[1, 1]), _rawnode(vf.VK_SEGMENT, 2, 1, [a], ip=[0, 1])])
+        return self.addStateObjective(PhaseRegionFlags.FrontandBack, _rawnode(vf.VK_SCALED, 2, 1, [d], d=[float(scale)]), var)
+
+    def addDeltaTimeObjective(self, scale):
+        return self.addDeltaVarObjective(self.ode.TVar(), scale)
+
+    # ------------------------------------------------------------------ transcription / evaluation
+    def makeSolverInput(self):
+        d = self.dims()
+        X = np.zeros(d["numPhaseVars"])
+        traj = np.ascontiguousarray(self._traj)
+        sp = np.ascontiguousarray(self._static) if self._spv else np.zeros(1)
+        _lib.check(lib.ab_phase_make_input(self.h, _lib.dptr(traj), _lib.dptr(sp), _lib.dptr(X)))
+        return X
+
+    def transcribe(self, showstats=False, showfuns=False):
+        """ODEPhaseBase::transcribe (ODEPhaseBase.cpp:1383-1418): builds the NonLinearProgram for this phase."""
+        if not self.h:
+            raise RuntimeError("setTraj must be called before transcribe")
+        nlp = NonLinearProgram()
+        out = (C.c_int * 3)()
+        _lib.check(lib.ab_phase_transcribe(self.h, nlp.h, 0, 0, 0, out))
+        nlp.set_dims(out[0], out[1], out[2])
+        nlp.analyze()
+        self.nlp = nlp
+        return nlp
+
+    def optimize(self, *a, **k):
+        raise NotImplementedError("PSIOPT's interior-point loop and sparse LDLT are out of scope for this build "
+                                  "(SURVEY.md section 2 row 13); use phase.transcribe() and nlp.evalKKT(...)")
+
+    solve = optimize
+    solve_optimize = optimize
+
+    def test_threads(self, i, j, n):
+        """The reference's own KKT micro-benchmark protocol (ODEPhaseBase.cpp:1420-1441, NonLinearProgram.cpp:686-820):
+        n repetitions of evalKKT with random multipliers; here the GPU evaluation is timed and compared run-to-run."""
+        nlp = self.nlp or self.transcribe()
+        return nlp.NLPTest(self.makeSolverInput(), n)
+
+
+class OptimalControlProblem:
+    """Multi-phase problem: phase offsets and one shared NonLinearProgram (OptimalControlProblem.cpp:115-155)."""
+
+    def __init__(self):
+        self.Phases = []
+        self.nlp = None
+
+    def addPhase(self, ph):
+        self.Phases.append(ph)
+        return len(self.Phases) - 1
+
+    def transcribe(self, showstats=False, showfuns=False):
+        nlp = NonLinearProgram()
+        v = e = i = 0
+        self.offsets = []
+        for ph in self.Phases:
+            out = (C.c_int * 3)()
+            _lib.check(lib.ab_phase_transcribe(ph.h, nlp.h, v, e, i, out))
+            self.offsets.append((v, e, i))
+            v, e, i = v + out[0], e + out[1], i + out[2]
+        nlp.set_dims(v, e, i)
+        nlp.analyze()
+        self.nlp = nlp
+        return nlp
+
+    def makeSolverInput(self):
+        return np.concatenate([ph.makeSolverInput() for ph in self.Phases])
+
+    def optimize(self, *a, **k):
+        raise NotImplementedError("PSIOPT is out of scope for this build; use ocp.transcribe() and nlp.evalKKT(...)")
+
+    solve = optimize

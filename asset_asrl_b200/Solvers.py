@@ -1,0 +1,202 @@
+"""NonLinearProgram: the KKT evaluation object PSIOPT calls, evaluated on the GPU.
+
+Mirrors the eight eval entry points of /root/reference/src/Solvers/NonLinearProgram.h:411-478 (argument meaning
+and output set per mode) and the set-up products of make_NLP / analyzeSparsity (NonLinearProgram.cpp:25-39,
+:267-344).  Outputs are *assigned* sums (the reference accumulates into caller-zeroed buffers; the results are
+the same numbers).  There is no CPU fallback: creating the device plan without a GPU raises.
+"""
+import ctypes as C
+import time
+
+import numpy as np
+
+from . import _lib
+from ._lib import lib
+
+EVAL_KKT, EVAL_KKTNO, EVAL_SOE, EVAL_AUG, EVAL_RHS, EVAL_OGC, EVAL_OCC, EVAL_OBJ = range(8)
+
+
+class NonLinearProgram:
+    def __init__(self, nvars=0, neq=0, niq=0):
+        self.h = lib.ab_problem_create(nvars, neq, niq)
+        if not self.h:
+            raise MemoryError("ab_problem_create failed")
+        self.plan = None
+        self.device = 0
+        self._dims = None
+
+    def __del__(self):
+        try:
+            if self.plan:
+                lib.ab_plan_destroy(self.plan)
+            if self.h:
+                lib.ab_problem_destroy(self.h)
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ set-up
+    def set_dims(self, nvars, neq, niq):
+        _lib.check(lib.ab_problem_set_dims(self.h, nvars, neq, niq))
+        self._dims = None
+
+    def add_tape(self, fun, with_adjoint=True):
+        from .VectorFunctions import GRAPH
+        return _lib.check(lib.ab_problem_add_tape(self.h, GRAPH.h, fun.node, 1 if with_adjoint else 0))
+
+    def add_function(self, role, tape, linear, vindex, cindex=None, appconst=None, unique_constraints=True):
+        """vindex: [nappl][ir] global variable indices; cindex: [nappl][orows] rows within the eq / iq block."""
+        V = np.ascontiguousarray(vindex, dtype=np.int32)
+        nappl = V.shape[0]
+        va, vp = _lib.iarr(V)
+        ca, cp = _lib.iarr(cindex if cindex is not None else [])
+        aa, ap = _lib.darr(appconst if appconst is not None else [])
+        return _lib.check(lib.ab_problem_add_function(self.h, role, tape, int(linear), int(unique_constraints), nappl, vp,
+                                                      cp if cindex is not None else None, ap if appconst is not None else None))
+
+    def analyze(self):
+        _lib.check(lib.ab_problem_analyze(self.h))
+        self._dims = None
+
+    def dims(self):
+        if self._dims is None:
+            out = (C.c_longlong * 10)()
+            _lib.check(lib.ab_problem_dims(self.h, out))
+            self._dims = dict(zip(["nvars", "neq", "niq", "kktdim", "nnz", "n_user", "n_solver", "stage_size", "nfuncs",
+                                   "ntapes"], [int(v) for v in out]))
+        return self._dims
+
+    PrimalVars = property(lambda s: s.dims()["nvars"])
+    EqualCons = property(lambda s: s.dims()["neq"])
+    InequalCons = property(lambda s: s.dims()["niq"])
+    KKTdim = property(lambda s: s.dims()["kktdim"])
+
+    def pattern(self):
+        """(indptr, indices) of the upper-triangular row-major CSR KKT pattern (analyzeSparsity)."""
+        d = self.dims()
+        indptr = np.zeros(d["kktdim"] + 1, dtype=np.int32)
+        indices = np.zeros(d["nnz"], dtype=np.int32)
+        _lib.check(lib.ab_problem_pattern(self.h, indptr.ctypes.data_as(_lib._ip), indices.ctypes.data_as(_lib._ip)))
+        return indptr, indices
+
+    def kkt_locations(self):
+        d = self.dims()
+        out = np.zeros(d["n_user"] + d["n_solver"], dtype=np.int32)
+        _lib.check(lib.ab_problem_kkt_locations(self.h, out.ctypes.data_as(_lib._ip)))
+        return out
+
+    def function_info(self, f):
+        out = (C.c_int * 8)()
+        _lib.check(lib.ab_problem_function_info(self.h, f, out))
+        return dict(zip(["role", "tape", "ir", "orows", "linear", "unique_constraints", "nappl", "nappconst"], list(out)))
+
+    def function_indices(self, f):
+        fi = self.function_info(f)
+        V = np.zeros((fi["nappl"], fi["ir"]), dtype=np.int32)
+        Cc = np.zeros((fi["nappl"], fi["orows"] if fi["role"] != 0 else 0), dtype=np.int32)
+        _lib.check(lib.ab_problem_function_indices(self.h, f, V.ctypes.data_as(_lib._ip),
+                                                   Cc.ctypes.data_as(_lib._ip) if Cc.size else None))
+        return V, Cc
+
+    def tape(self, t):
+        out = (C.c_int * 8)()
+        _lib.check(lib.ab_problem_tape_info(self.h, t, out))
+        info = dict(zip(["n_instr", "n_primal", "slots_primal", "slots_total", "nin", "nout", "nappconst", "has_adjoint"],
+                        list(out)))
+        dt = np.dtype([("op", "<u2"), ("dst", "<u2"), ("a", "<u2"), ("b", "<u2"), ("imm", "<f8")])
+        code = np.zeros(info["n_instr"], dtype=dt)
+        if info["n_instr"]:
+            _lib.check(lib.ab_problem_tape_code(self.h, t, code.ctypes.data_as(C.c_void_p)))
+        return info, code
+
+    # ------------------------------------------------------------------ device
+    def to_device(self, device=0):
+        if self.plan:
+            lib.ab_plan_destroy(self.plan)
+            self.plan = None
+        if self._dims is None or not self.dims()["kktdim"]:
+            self.analyze()
+        p = C.c_void_p()
+        _lib.check0(lib.ab_plan_create(self.h, device, C.byref(p)))
+        self.plan = p
+        self.device = device
+        return self
+
+    def _need_plan(self):
+        if not self.plan:
+            self.to_device(self.device)
+
+    def set_solver_coeffs(self, coeffs):
+        self._need_plan()
+        a, ap = _lib.darr(coeffs)
+        assert a.size == self.dims()["n_solver"]
+        _lib.check0(lib.ab_plan_set_solver_coeffs(self.plan, ap))
+
+    def _eval(self, mode, ObjScale, X, LE, LI, want):
+        self._need_plan()
+        d = self.dims()
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        LE = np.ascontiguousarray(LE if LE is not None else np.zeros(d["neq"]), dtype=np.float64)
+        LI = np.ascontiguousarray(LI if LI is not None else np.zeros(d["niq"]), dtype=np.float64)
+        if X.size != d["nvars"] or LE.size != d["neq"] or LI.size != d["niq"]:
+            raise ValueError("X / LE / LI sizes do not match the problem")
+        out = {}
+        if "val" in want:
+            out["val"] = np.zeros(1)
+        if "PGX" in want:
+            out["PGX"] = np.zeros(d["nvars"])
+        if "AGX" in want:
+            out["AGX"] = np.zeros(d["nvars"])
+        if "FX" in want:
+            out["FXE"] = np.zeros(d["neq"])
+            out["FXI"] = np.zeros(d["niq"])
+        if "KKT" in want:
+            out["KKT"] = np.zeros(d["nnz"])
+        g = lambda k: _lib.dptr(out[k]) if k in out else None  # noqa: E731
+        _lib.check0(lib.ab_plan_eval_host(self.plan, mode, float(ObjScale), _lib.dptr(X), _lib.dptr(LE), _lib.dptr(LI),
+                                          g("val"), g("PGX"), g("AGX"), g("FXE"), g("FXI"), g("KKT")))
+        if "val" in out:
+            out["val"] = float(out["val"][0])
+        return out
+
+    def evalKKT(self, ObjScale, X, LE, LI):
+        return self._eval(EVAL_KKT, ObjScale, X, LE, LI, {"val", "PGX", "AGX", "FX", "KKT"})
+
+    def evalKKTNO(self, ObjScale, X, LE, LI):
+        return self._eval(EVAL_KKTNO, ObjScale, X, LE, LI, {"AGX", "FX", "KKT"})
+
+    def evalSOE(self, ObjScale, X, LE, LI):
+        return self._eval(EVAL_SOE, ObjScale, X, LE, LI, {"FX", "KKT"})
+
+    def evalAUG(self, ObjScale, X, LE, LI):
+        return self._eval(EVAL_AUG, ObjScale, X, LE, LI, {"val", "PGX", "AGX", "FX", "KKT"})
+
+    def evalRHS(self, ObjScale, X, LE, LI):
+        return self._eval(EVAL_RHS, ObjScale, X, LE, LI, {"val", "PGX", "AGX", "FX"})
+
+    def evalOGC(self, ObjScale, X):
+        return self._eval(EVAL_OGC, ObjScale, X, None, None, {"val", "PGX", "FX"})
+
+    def evalOCC(self, ObjScale, X):
+        return self._eval(EVAL_OCC, ObjScale, X, None, None, {"val", "FX"})
+
+    def evalOBJ(self, ObjScale, X):
+        return self._eval(EVAL_OBJ, ObjScale, X, None, None, {"val"})
+
+    def launches(self):
+        return int(lib.ab_plan_launches(self.plan)) if self.plan else 0
+
+    def NLPTest(self, X, n, seed=67890):
+        """NLPTest protocol (NonLinearProgram.cpp:686-820): multipliers 100*U(-1,1), n repetitions of evalKKT;
+        returns mean ms per evalKKT (host buffers in and out) and the max run-to-run difference (0 = deterministic)."""
+        d = self.dims()
+        rng = np.random.default_rng(seed)
+        LE = 100.0 * rng.uniform(-1, 1, d["neq"])
+        LI = 100.0 * rng.uniform(-1, 1, d["niq"])
+        ref = self.evalKKT(1.0, X, LE, LI)
+        t0 = time.perf_counter()
+        maxdiff = 0.0
+        for _ in range(n):
+            r = self.evalKKT(1.0, X, LE, LI)
+            maxdiff = max(maxdiff, float(np.max(np.abs(r["KKT"] - ref["KKT"]))) if d["nnz"] else 0.0)
+        ms = (time.perf_counter() - t0) * 1e3 / max(n, 1)
+        return {"ms_per_evalKKT": ms, "max_run_to_run_diff": maxdiff}

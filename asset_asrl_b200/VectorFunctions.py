@@ -1,0 +1,618 @@
+"""Expression front end with the reference's Python surface (``vf.Arguments``, operators, ``vf.sin`` ...).
+
+Mirrors the names bound in /root/reference/src/VectorFunctions/DenseFunctionBase.h:1643-2263 and
+re-exported by /root/reference/asset_asrl/VectorFunctions/__init__.py:6-56.  Every object is a node id in a
+C++ expression graph (asset_asrl_b200/csrc/expr.hpp); nothing is evaluated in Python.
+"""
+import numbers
+
+import numpy as np
+
+from . import _lib
+from ._lib import lib
+
+# ab::VKind (csrc/expr.hpp)
+(VK_ARGS, VK_SEGMENT, VK_ELEMENTS, VK_CONSTANT, VK_STACK, VK_SUM, VK_DIFF, VK_SCALED, VK_ROWSCALED, VK_ADDVEC,
+ VK_VECMINUS, VK_UNARY, VK_NORM, VK_NORMALIZED, VK_DOT, VK_CROSS, VK_CWISEPROD, VK_CWISEQUOT, VK_VSPROD, VK_VSDIV,
+ VK_CWISESUM, VK_ATAN2, VK_NESTED, VK_IFELSE, VK_COMPARE, VK_BOOL, VK_IOSCALED, VK_APPCONST, VK_MATVEC) = range(29)
+
+# ab::Op (csrc/tape.h)
+OPS = ["CONST", "INPUT", "LAMBDA", "APPCONST", "ADD", "SUB", "MUL", "DIV", "NEG", "ADDC", "MULC", "SQUARE", "INV", "SQRT",
+       "EXP", "LOG", "SIN", "COS", "TAN", "ASIN", "ACOS", "ATAN", "SINH", "COSH", "TANH", "ASINH", "ACOSH", "ATANH", "ABS",
+       "SIGN", "POWC", "ATAN2", "LT", "LE", "SELECT", "FMA", "OUT_F", "OUT_G"]
+OP = {n: i for i, n in enumerate(OPS)}
+
+
+class _Graph:
+    """Process-wide expression graph (the C++ arena every function lives in)."""
+
+    def __init__(self):
+        self.h = lib.ab_graph_create()
+        if not self.h:
+            raise MemoryError("ab_graph_create failed")
+
+    def node(self, kind, ir, orows, ch=(), d=(), ip=(), tlin=-1, raw=0):
+        cha, chp = _lib.iarr(list(ch))
+        da, dp = _lib.darr(list(d))
+        ipa, ipp = _lib.iarr(list(ip))
+        return _lib.check(lib.ab_graph_node(self.h, kind, ir, orows, chp, len(cha), dp, len(da), ipp, len(ipa), tlin, raw))
+
+
+GRAPH = _Graph()
+
+
+def _is_num(x):
+    return isinstance(x, numbers.Real) and not isinstance(x, bool)
+
+
+def _vec(x):
+    return np.atleast_1d(np.asarray(x, dtype=np.float64)).ravel()
+
+
+class VectorFunction:
+    """Generic vector function f: R^IRows -> R^ORows (the reference's GenericFunction<-1,-1>)."""
+
+    __array_priority__ = 1000
+
+    def __init__(self, node, ir=None, orows=None):
+        if isinstance(node, VectorFunction):  # allow class MyFun(vf.VectorFunction): super().__init__(expr)
+            node, ir, orows = node.node, node.ir, node.orows
+        self.node = int(node)
+        self.ir = ir
+        self.orows = orows
+
+    # ---- sizing / meta
+    def IRows(self):
+        return self.ir
+
+    def ORows(self):
+        return self.orows
+
+    def is_linear(self):
+        import ctypes as C
+        t = C.c_int()
+        _lib.check(lib.ab_graph_node_info(GRAPH.h, self.node, None, None, C.byref(t), None))
+        return bool(t.value)
+
+    def describe(self):
+        n = lib.ab_graph_describe(GRAPH.h, self.node, None, 0)
+        import ctypes as C
+        buf = C.create_string_buffer(int(n) + 1)
+        lib.ab_graph_describe(GRAPH.h, self.node, buf, n + 1)
+        return buf.value.decode()
+
+    def vf(self):
+        return VectorFunction(self.node, self.ir, self.orows)
+
+    def sf(self):
+        if self.orows != 1:
+            raise ValueError("sf(): function is not scalar valued")
+        return ScalarFunction(self.node, self.ir, 1)
+
+    # ---- construction helpers
+    def _new(self, kind, orows, ch, d=(), ip=(), raw=0):
+        cls = ScalarFunction if orows == 1 else VectorFunction
+        for c in ch:
+            if c.ir != self.ir:
+                raise ValueError(f"Input Size of Func1 (IRows = {self.ir}) does not match Input Size of Func2 (IRows = {c.ir}).")
+        n = GRAPH.node(kind, self.ir, orows, [c.node for c in ch], d, ip, -1, raw)
+        return cls(n, self.ir, orows)
+
+    def _raw(self):
+        import ctypes as C
+        r = C.c_int()
+        _lib.check(lib.ab_graph_node_info(GRAPH.h, self.node, None, None, None, C.byref(r)))
+        return r.value
+
+    def _coerce(self, other):
+        """number / vector -> None (handled by caller); function -> function"""
+        if isinstance(other, VectorFunction):
+            return other
+        return None
+
+    # ---- element access
+    def segment(self, start, size):
+        if start < 0 or size < 0 or start + size > self.orows:
+            raise ValueError("Segment index out of bounds.")
+        return self._new(VK_SEGMENT, size, [self], ip=[start, size], raw=self._raw())
+
+    def head(self, size):
+        return self.segment(0, size)
+
+    def tail(self, size):
+        return self.segment(self.orows - size, size)
+
+    def coeff(self, i):
+        return self.segment(i, 1)
+
+    def head2(self):
+        return self.head(2)
+
+    def head3(self):
+        return self.head(3)
+
+    def tail2(self):
+        return self.tail(2)
+
+    def tail3(self):
+        return self.tail(3)
+
+    def segment2(self, s):
+        return self.segment(s, 2)
+
+    def segment3(self, s):
+        return self.segment(s, 3)
+
+    head_2, head_3, tail_2, tail_3, segment_2, segment_3 = head2, head3, tail2, tail3, segment2, segment3
+
+    def tolist(self, spec=None):
+        if spec is None:
+            return [self.coeff(i) for i in range(self.orows)]
+        return [self.segment(s, n) for (s, n) in spec]
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            idx = list(range(*i.indices(self.orows)))
+            if not idx:
+                raise ValueError("empty slice")
+            if idx == list(range(idx[0], idx[0] + len(idx))):
+                return self.segment(idx[0], len(idx))
+            return self._new(VK_ELEMENTS, len(idx), [self], ip=idx, raw=self._raw())
+        if isinstance(i, (list, tuple, np.ndarray)):
+            idx = [int(k) for k in i]
+            return self._new(VK_ELEMENTS, len(idx), [self], ip=idx, raw=self._raw())
+        i = int(i)
+        if i < 0:
+            i += self.orows
+        return self.coeff(i)
+
+    def __len__(self):
+        return self.orows
+
+    def __iter__(self):
+        return iter(self.tolist())
+
+    # ---- arithmetic
+    def __neg__(self):
+        return self._new(VK_SCALED, self.orows, [self], d=[-1.0])
+
+    def __add__(self, o):
+        f = self._coerce(o)
+        if f is not None:
+            if f.orows != self.orows:
+                raise ValueError("Output sizes do not match in sum")
+            return self._new(VK_SUM, self.orows, [self, f])
+        v = _vec(o)
+        if v.size == 1 and self.orows > 1:
+            v = np.full(self.orows, v[0])
+        if v.size != self.orows:
+            raise ValueError("vector size does not match function output size")
+        return self._new(VK_ADDVEC, self.orows, [self], d=v)
+
+    __radd__ = __add__
+
+    def __sub__(self, o):
+        f = self._coerce(o)
+        if f is not None:
+            if f.orows != self.orows:
+                raise ValueError("Output sizes do not match in difference")
+            return self._new(VK_DIFF, self.orows, [self, f])
+        return self.__add__(-_vec(o))
+
+    def __rsub__(self, o):
+        v = _vec(o)
+        if v.size == 1 and self.orows > 1:
+            v = np.full(self.orows, v[0])
+        if v.size != self.orows:
+            raise ValueError("vector size does not match function output size")
+        return self._new(VK_VECMINUS, self.orows, [self], d=v)
+
+    def __mul__(self, o):
+        f = self._coerce(o)
+        if f is not None:
+            if f.orows == 1 and self.orows == 1:
+                return self._new(VK_CWISEPROD, 1, [self, f])
+            if f.orows == 1:
+                return self._new(VK_VSPROD, self.orows, [self, f])
+            if self.orows == 1:
+                return f._new(VK_VSPROD, f.orows, [f, self])
+            raise ValueError("vector * vector is ambiguous: use dot / cross / cwiseProduct")
+        if _is_num(o):
+            return self._new(VK_SCALED, self.orows, [self], d=[float(o)])
+        v = _vec(o)
+        if self.orows == 1:  # scalar function times constant vector
+            c = self._new(VK_CONSTANT, v.size, [], d=v)
+            return c._new(VK_VSPROD, v.size, [c, self])
+        if v.size != self.orows:
+            raise ValueError("vector size does not match function output size")
+        return self._new(VK_ROWSCALED, self.orows, [self], d=v)
+
+    __rmul__ = __mul__
+
+    def __truediv__(self, o):
+        f = self._coerce(o)
+        if f is not None:
+            if f.orows != 1:
+                raise ValueError("can only divide by a scalar function")
+            if self.orows == 1:
+                return self._new(VK_CWISEQUOT, 1, [self, f])
+            return self._new(VK_VSDIV, self.orows, [self, f])
+        if _is_num(o):
+            return self._new(VK_SCALED, self.orows, [self], d=[1.0 / float(o)])
+        v = _vec(o)
+        return self._new(VK_ROWSCALED, self.orows, [self], d=1.0 / v)
+
+    def __rtruediv__(self, o):
+        if self.orows != 1:
+            raise ValueError("can only divide by a scalar function")
+        inv = self._unary("INV")
+        return inv.__mul__(o)
+
+    def __pow__(self, p):
+        return self.pow(p)
+
+    def __abs__(self):
+        return self._unary("ABS")
+
+    # ---- cwise math (scalar functions in the reference; applied elementwise here)
+    def _unary(self, name, imm=None):
+        d = [] if imm is None else [float(imm)]
+        return self._new(VK_UNARY, self.orows, [self], d=d, ip=[OP[name]])
+
+    def sin(self):
+        return self._unary("SIN")
+
+    def cos(self):
+        return self._unary("COS")
+
+    def tan(self):
+        return self._unary("TAN")
+
+    def sqrt(self):
+        return self._unary("SQRT")
+
+    def exp(self):
+        return self._unary("EXP")
+
+    def log(self):
+        return self._unary("LOG")
+
+    def squared(self):
+        return self._unary("SQUARE")
+
+    def inverse(self):
+        return self._unary("INV")
+
+    def arcsin(self):
+        return self._unary("ASIN")
+
+    def arccos(self):
+        return self._unary("ACOS")
+
+    def arctan(self):
+        return self._unary("ATAN")
+
+    def sinh(self):
+        return self._unary("SINH")
+
+    def cosh(self):
+        return self._unary("COSH")
+
+    def tanh(self):
+        return self._unary("TANH")
+
+    def arcsinh(self):
+        return self._unary("ASINH")
+
+    def arccosh(self):
+        return self._unary("ACOSH")
+
+    def arctanh(self):
+        return self._unary("ATANH")
+
+    def sign(self):
+        return self._unary("SIGN")
+
+    def pow(self, p):
+        if not _is_num(p):
+            raise TypeError("pow: exponent must be a number")
+        return self._unary("POWC", float(p))
+
+    # ---- norms
+    def _norm(self, p):
+        return self._new(VK_NORM, 1, [self], ip=[p])
+
+    def norm(self):
+        return self._norm(1)
+
+    def squared_norm(self):
+        return self._norm(2)
+
+    def cubed_norm(self):
+        return self._norm(3)
+
+    def inverse_norm(self):
+        return self._norm(-1)
+
+    def inverse_squared_norm(self):
+        return self._norm(-2)
+
+    def inverse_cubed_norm(self):
+        return self._norm(-3)
+
+    def inverse_four_norm(self):
+        return self._norm(-4)
+
+    def _normalized(self, p):
+        return self._new(VK_NORMALIZED, self.orows, [self], ip=[p])
+
+    def normalized(self):
+        return self._normalized(1)
+
+    def normalized_power2(self):
+        return self._normalized(2)
+
+    def normalized_power3(self, shift=None, scale=None):
+        f = self
+        if shift is not None:
+            f = self + _vec(shift)
+        r = f._normalized(3)
+        return r if scale is None else r * float(scale)
+
+    def normalized_power4(self):
+        return self._normalized(4)
+
+    def normalized_power5(self):
+        return self._normalized(5)
+
+    def sum(self):
+        return self._new(VK_CWISESUM, 1, [self])
+
+    # ---- products
+    def _other(self, o):
+        if isinstance(o, VectorFunction):
+            return o
+        v = _vec(o)
+        return self._new(VK_CONSTANT, v.size, [], d=v, raw=1)
+
+    def dot(self, o):
+        o = self._other(o)
+        if o.orows != self.orows:
+            raise ValueError("dot: size mismatch")
+        return self._new(VK_DOT, 1, [self, o])
+
+    def cross(self, o):
+        o = self._other(o)
+        if o.orows != 3 or self.orows != 3:
+            raise ValueError("cross: both operands must have 3 outputs")
+        return self._new(VK_CROSS, 3, [self, o])
+
+    def cwiseProduct(self, o):
+        o = self._other(o)
+        if o.orows != self.orows:
+            raise ValueError("cwiseProduct: size mismatch")
+        return self._new(VK_CWISEPROD, self.orows, [self, o])
+
+    def cwiseQuotient(self, o):
+        o = self._other(o)
+        if o.orows != self.orows:
+            raise ValueError("cwiseQuotient: size mismatch")
+        return self._new(VK_CWISEQUOT, self.orows, [self, o])
+
+    # ---- composition
+    def eval(self, inner, *rest):
+        """self(inner(x)); ``eval(ir, indices)`` selects elements of a larger argument vector."""
+        if rest:
+            ir, idx = int(inner), [int(k) for k in rest[0]]
+            inner = Arguments(ir)[idx]
+        if not isinstance(inner, VectorFunction):
+            raise TypeError("eval expects a VectorFunction")
+        if inner.orows != self.ir:
+            raise ValueError(f"eval: inner function has {inner.orows} outputs but outer expects {self.ir} inputs")
+        cls = ScalarFunction if self.orows == 1 else VectorFunction
+        n = GRAPH.node(VK_NESTED, inner.ir, self.orows, [self.node, inner.node], (), (), -1, 0)
+        return cls(n, inner.ir, self.orows)
+
+    def __call__(self, inner):
+        return self.eval(inner)
+
+    # ---- comparisons (scalar) -> conditional objects for ifelse
+    def _cmp(self, o, code):
+        if self.orows != 1:
+            raise ValueError("comparison needs scalar functions")
+        if not isinstance(o, VectorFunction):
+            o = self._new(VK_CONSTANT, 1, [], d=[float(o)], raw=1)
+        return self._new(VK_COMPARE, 1, [self, o], ip=[code])
+
+    def __lt__(self, o):
+        return self._cmp(o, 0)
+
+    def __le__(self, o):
+        return self._cmp(o, 1)
+
+    def __gt__(self, o):
+        return self._cmp(o, 2)
+
+    def __ge__(self, o):
+        return self._cmp(o, 3)
+
+    def __and__(self, o):
+        return self._new(VK_BOOL, 1, [self, o], ip=[0])
+
+    def __or__(self, o):
+        return self._new(VK_BOOL, 1, [self, o], ip=[1])
+
+
+class ScalarFunction(VectorFunction):
+    """f: R^IRows -> R (the reference's GenericFunction<-1,1>)."""
+
+    def __init__(self, node, ir=None, orows=1):
+        super().__init__(node, ir, orows)
+        if self.orows != 1:
+            raise ValueError("ScalarFunction needs a single output")
+
+
+class Arguments(VectorFunction):
+    """Arguments(n): the identity on R^n, root of every expression (Segment.h / Arguments)."""
+
+    def __init__(self, n):
+        n = int(n)
+        if n <= 0:
+            raise ValueError("Arguments size must be positive")
+        node = GRAPH.node(VK_ARGS, n, n, raw=1)
+        super().__init__(node, n, n)
+
+
+def ConstantVector(ir, values):
+    v = _vec(values)
+    return VectorFunction(GRAPH.node(VK_CONSTANT, int(ir), v.size, d=v, raw=1), int(ir), v.size)
+
+
+def ConstantScalar(ir, value):
+    return ScalarFunction(GRAPH.node(VK_CONSTANT, int(ir), 1, d=[float(value)], raw=1), int(ir), 1)
+
+
+def _as_fun(f):
+    if not isinstance(f, VectorFunction):
+        raise TypeError("expected a VectorFunction")
+    return f
+
+
+def stack(*fs):
+    """vf.stack([f1, f2, ...]) (BulkOperationsBuild.cpp:6-15)."""
+    if len(fs) == 1 and isinstance(fs[0], (list, tuple)):
+        fs = fs[0]
+    fs = [_as_fun(f) for f in fs]
+    if not fs:
+        raise ValueError("stack of nothing")
+    return fs[0]._new(VK_STACK, builtins_sum(f.orows for f in fs), fs)
+
+
+def builtins_sum(it):
+    t = 0
+    for v in it:
+        t += v
+    return t
+
+
+stack_scalar = stack
+Stack = stack
+StackScalar = stack
+
+
+def sum(*fs):  # noqa: A001 - the reference exports vf.sum
+    if len(fs) == 1 and isinstance(fs[0], (list, tuple)):
+        fs = fs[0]
+    fs = [_as_fun(f) for f in fs]
+    for f in fs:
+        if f.orows != fs[0].orows:
+            raise ValueError("sum: output sizes differ")
+    return fs[0]._new(VK_SUM, fs[0].orows, fs)
+
+
+Sum = sum
+SumScalar = sum
+
+
+def SumElems(f):
+    return f.sum()
+
+
+def _u(name):
+    def fn(f):
+        return _as_fun(f)._unary(name)
+    fn.__name__ = name.lower()
+    return fn
+
+
+sin, cos, tan = _u("SIN"), _u("COS"), _u("TAN")
+arcsin, arccos, arctan = _u("ASIN"), _u("ACOS"), _u("ATAN")
+sinh, cosh, tanh = _u("SINH"), _u("COSH"), _u("TANH")
+arcsinh, arccosh, arctanh = _u("ASINH"), _u("ACOSH"), _u("ATANH")
+sqrt, exp, log, squared, sign = _u("SQRT"), _u("EXP"), _u("LOG"), _u("SQUARE"), _u("SIGN")
+abs = _u("ABS")  # noqa: A001
+
+
+def pow(f, p):  # noqa: A001
+    return _as_fun(f).pow(p)
+
+
+def arctan2(y, x):
+    y, x = _as_fun(y), _as_fun(x)
+    return y._new(VK_ATAN2, 1, [y, x])
+
+
+def norm(f):
+    return f.norm()
+
+
+def inverse_norm(f):
+    return f.inverse_norm()
+
+
+def normalize(f):
+    return f.normalized()
+
+
+def dot(a, b):
+    return (a if isinstance(a, VectorFunction) else b).dot(b if isinstance(a, VectorFunction) else a)
+
+
+def cross(a, b):
+    if isinstance(a, VectorFunction):
+        return a.cross(b)
+    return -(b.cross(a))
+
+
+def cwiseProduct(a, b):
+    return (a if isinstance(a, VectorFunction) else b).cwiseProduct(b if isinstance(a, VectorFunction) else a)
+
+
+def cwiseQuotient(a, b):
+    if isinstance(a, VectorFunction):
+        return a.cwiseQuotient(b)
+    c = b._other(a)
+    return c.cwiseQuotient(b)
+
+
+def doublecross(a, b, c):
+    return cross(a, cross(b, c))
+
+
+def ifelse(cond, a, b):
+    """vf.ifelse(condition, f_true, f_false) (Conditional.h:19-235)."""
+    a = a if isinstance(a, VectorFunction) else cond._other(a)
+    b = b if isinstance(b, VectorFunction) else cond._other(b)
+    if a.orows != b.orows:
+        raise ValueError("ifelse: branch sizes differ")
+    return cond._new(VK_IFELSE, a.orows, [cond, a, b])
+
+
+def matmul(M, f):
+    M = np.asarray(M, dtype=np.float64)
+    if M.ndim != 2 or M.shape[1] != f.orows:
+        raise ValueError("matmul: shape mismatch")
+    return f._new(VK_MATVEC, M.shape[0], [f], d=M.ravel())
+
+
+def ioscaled(f, in_scales, out_scales):
+    """IOScaled wrapper (IOScaled.h:8-158): out_scales .* f(in_scales .* x)."""
+    i, o = _vec(in_scales), _vec(out_scales)
+    if i.size != f.ir or o.size != f.orows:
+        raise ValueError("ioscaled: scale sizes do not match")
+    return f._new(VK_IOSCALED, f.orows, [f], d=np.concatenate([i, o]))
+
+
+Element = ScalarFunction
+Segment = VectorFunction
+Segment2 = VectorFunction
+Segment3 = VectorFunction
+
+
+class PyVectorFunction:
+    def __init__(self, *a, **k):
+        raise NotImplementedError("PyVectorFunction is a host callback and cannot be lowered to a device tape; "
+                                  "there is no CPU fallback on this path")
+
+
+PyScalarFunction = PyVectorFunction

@@ -1,0 +1,494 @@
+// extern "C" boundary (include/asset_b200.h).  No exceptions cross it.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <exception>
+#include <stdexcept>
+#include <algorithm>
+#include <memory>
+#include <string>
+
+#include "../../include/asset_b200.h"
+#include "phase.hpp"
+#include "plan.hpp"
+
+using namespace ab;
+
+struct ab_graph {
+  Graph g;
+};
+struct ab_problem {
+  Problem p;
+};
+struct ab_phase {
+  Phase ph;
+};
+struct ab_plan {
+  Plan plan;
+};
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define AB_TRY try {
+#define AB_CATCH                                                     \
+  }                                                                  \
+  catch (const std::exception& e) { return fail(AB_ERR_INVALID, e.what()); } \
+  catch (...) { return fail(AB_ERR_RUNTIME, "unknown exception"); }
+
+extern "C" {
+
+const char* ab_last_error(void) { return g_err.c_str(); }
+int ab_version(void) { return 100; }
+int ab_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// ------------------------------------------------------------------ graph
+ab_graph* ab_graph_create(void) { return new (std::nothrow) ab_graph(); }
+void ab_graph_destroy(ab_graph* g) { delete g; }
+
+static bool auto_tlin(const Graph& g, const VNode& n) {
+  auto all_seen = [&]() {
+    for (int c: n.ch)
+      if (!g.seen_lin(c)) return false;
+    return true;
+  };
+  switch (n.kind) {
+    case VK_ARGS:
+    case VK_CONSTANT:
+    case VK_APPCONST: return true;
+    case VK_SEGMENT:
+    case VK_ELEMENTS:
+    case VK_STACK:
+    case VK_SUM:
+    case VK_DIFF:
+    case VK_SCALED:
+    case VK_ROWSCALED:
+    case VK_ADDVEC:
+    case VK_VECMINUS:
+    case VK_CWISESUM:
+    case VK_IOSCALED:
+    case VK_MATVEC:
+    case VK_NESTED: return all_seen();
+    default: return false;
+  }
+}
+
+int ab_graph_node(ab_graph* g, int kind, int ir, int orows, const int* ch, int nch, const double* d, int nd, const int* ip,
+                  int nip, int tlin, int raw) {
+  AB_TRY
+  if (!g) return fail(AB_ERR_INVALID, "null graph");
+  VNode n;
+  n.kind = kind;
+  n.ir = ir;
+  n.orows = orows;
+  n.ch.assign(ch, ch + nch);
+  n.d.assign(d, d + nd);
+  n.ip.assign(ip, ip + nip);
+  for (int c: n.ch)
+    if (c < 0 || c >= (int) g->g.nodes.size()) return fail(AB_ERR_INVALID, "child id out of range");
+  n.raw = raw != 0;
+  n.tlin = (tlin < 0) ? auto_tlin(g->g, n) : (tlin != 0);
+  // structural validation by a trial lowering on a scratch DAG
+  int id = g->g.add(n);
+  try {
+    SDag dag;
+    std::vector<int> in(ir);
+    for (int i = 0; i < ir; i++) in[i] = dag.input(i);
+    lower(g->g, id, in, dag);
+  } catch (...) {
+    g->g.nodes.pop_back();
+    throw;
+  }
+  return id;
+  AB_CATCH
+}
+
+int ab_graph_node_info(const ab_graph* g, int node, int* ir, int* orows, int* tlin, int* raw) {
+  AB_TRY
+  const VNode& n = g->g.at(node);
+  if (ir) *ir = n.ir;
+  if (orows) *orows = n.orows;
+  if (tlin) *tlin = n.tlin;
+  if (raw) *raw = n.raw;
+  return AB_OK;
+  AB_CATCH
+}
+
+long long ab_graph_describe(const ab_graph* g, int node, char* buf, long long cap) {
+  try {
+    std::string s = g->g.describe(node);
+    if (buf && cap > 0) {
+      long long n = std::min<long long>(cap - 1, (long long) s.size());
+      std::memcpy(buf, s.data(), (size_t) n);
+      buf[n] = 0;
+    }
+    return (long long) s.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
+
+// ------------------------------------------------------------------ problem
+ab_problem* ab_problem_create(int nvars, int neq, int niq) {
+  ab_problem* p = new (std::nothrow) ab_problem();
+  if (p) {
+    p->p.nvars = nvars;
+    p->p.neq = neq;
+    p->p.niq = niq;
+  }
+  return p;
+}
+void ab_problem_destroy(ab_problem* p) { delete p; }
+int ab_problem_set_dims(ab_problem* p, int nvars, int neq, int niq) {
+  if (!p) return fail(AB_ERR_INVALID, "null problem");
+  p->p.nvars = nvars;
+  p->p.neq = neq;
+  p->p.niq = niq;
+  p->p.analyzed = false;
+  return AB_OK;
+}
+
+int ab_problem_add_tape(ab_problem* p, const ab_graph* g, int node, int with_adjoint) {
+  AB_TRY
+  ScalarFn f = lower_function(g->g, node);
+  if (with_adjoint) f.make_gradient();
+  p->p.tapes.push_back(emit_tape(f, with_adjoint != 0));
+  return (int) p->p.tapes.size() - 1;
+  AB_CATCH
+}
+
+int ab_problem_add_function(ab_problem* p, int role, int tape, int linear, int unique, int nappl, const int* vindex,
+                            const int* cindex, const double* appconst) {
+  AB_TRY
+  if (tape < 0 || tape >= (int) p->p.tapes.size()) return fail(AB_ERR_INVALID, "tape id out of range");
+  if (role < 0 || role > 2) return fail(AB_ERR_INVALID, "role must be 0 (objective), 1 (equality) or 2 (inequality)");
+  const Tape& t = p->p.tapes[tape];
+  FuncRec fr;
+  fr.role = role;
+  fr.tape = tape;
+  fr.ir = t.nin;
+  fr.orows = t.nout;
+  fr.linear = linear != 0;
+  fr.unique_constraints = unique != 0;
+  fr.nappl = nappl;
+  fr.nappconst = t.nappconst;
+  fr.vindex.assign(vindex, vindex + (size_t) nappl * fr.ir);
+  if (role != 0) fr.cindex.assign(cindex, cindex + (size_t) nappl * fr.orows);
+  if (fr.nappconst > 0) {
+    if (!appconst) return fail(AB_ERR_INVALID, "tape needs per-application constants");
+    fr.appconst.assign(appconst, appconst + (size_t) nappl * fr.nappconst);
+  }
+  fr.name = "function" + std::to_string(p->p.funcs.size());
+  p->p.funcs.push_back(std::move(fr));
+  p->p.analyzed = false;
+  return (int) p->p.funcs.size() - 1;
+  AB_CATCH
+}
+
+int ab_problem_analyze(ab_problem* p) {
+  AB_TRY
+  p->p.analyze();
+  return AB_OK;
+  AB_CATCH
+}
+
+int ab_problem_dims(const ab_problem* p, long long out[10]) {
+  const Problem& q = p->p;
+  out[0] = q.nvars;
+  out[1] = q.neq;
+  out[2] = q.niq;
+  out[3] = q.kktdim;
+  out[4] = q.nnz();
+  out[5] = q.n_user;
+  out[6] = q.n_solver;
+  out[7] = q.stage_size;
+  out[8] = (long long) q.funcs.size();
+  out[9] = (long long) q.tapes.size();
+  return AB_OK;
+}
+
+int ab_problem_pattern(const ab_problem* p, int* indptr, int* indices) {
+  if (!p->p.analyzed) return fail(AB_ERR_INVALID, "problem not analyzed");
+  std::memcpy(indptr, p->p.indptr.data(), p->p.indptr.size() * sizeof(int));
+  std::memcpy(indices, p->p.indices.data(), p->p.indices.size() * sizeof(int));
+  return AB_OK;
+}
+int ab_problem_kkt_locations(const ab_problem* p, int* out) {
+  if (!p->p.analyzed) return fail(AB_ERR_INVALID, "problem not analyzed");
+  std::memcpy(out, p->p.kktloc.data(), p->p.kktloc.size() * sizeof(int));
+  return AB_OK;
+}
+int ab_problem_function_info(const ab_problem* p, int f, int out[8]) {
+  AB_TRY
+  const FuncRec& fr = p->p.funcs.at(f);
+  out[0] = fr.role;
+  out[1] = fr.tape;
+  out[2] = fr.ir;
+  out[3] = fr.orows;
+  out[4] = fr.linear;
+  out[5] = fr.unique_constraints;
+  out[6] = fr.nappl;
+  out[7] = fr.nappconst;
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_function_indices(const ab_problem* p, int f, int* vindex, int* cindex) {
+  AB_TRY
+  const FuncRec& fr = p->p.funcs.at(f);
+  if (vindex) std::memcpy(vindex, fr.vindex.data(), fr.vindex.size() * sizeof(int));
+  if (cindex) std::memcpy(cindex, fr.cindex.data(), fr.cindex.size() * sizeof(int));
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_tape_info(const ab_problem* p, int t, int out[8]) {
+  AB_TRY
+  const Tape& tp = p->p.tapes.at(t);
+  out[0] = (int) tp.code.size();
+  out[1] = tp.n_primal;
+  out[2] = tp.slots_primal;
+  out[3] = tp.slots_total;
+  out[4] = tp.nin;
+  out[5] = tp.nout;
+  out[6] = tp.nappconst;
+  out[7] = tp.has_adjoint;
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_tape_code(const ab_problem* p, int t, void* out) {
+  AB_TRY
+  const Tape& tp = p->p.tapes.at(t);
+  std::memcpy(out, tp.code.data(), tp.code.size() * sizeof(Instr));
+  return AB_OK;
+  AB_CATCH
+}
+
+// ------------------------------------------------------------------ phase
+ab_phase* ab_phase_create(ab_graph* g, int ode_node, int xv, int uv, int pv, int tmode, int nseg) {
+  try {
+    if (!g) throw std::invalid_argument("null graph");
+    const VNode& n = g->g.at(ode_node);
+    if (n.ir != xv + 1 + uv + pv || n.orows != xv) throw std::invalid_argument("ODE expression must map (XV+1+UV+PV) -> XV");
+    if (tmode < TM_LGL3 || tmode > TM_TRAPEZOIDAL) throw std::invalid_argument("Invalid Transcription Method");
+    if (nseg < 1) throw std::invalid_argument("number of segments must be positive");
+    ab_phase* ph = new ab_phase();
+    ph->ph.g = &g->g;
+    ph->ph.ode_root = ode_node;
+    ph->ph.XV = xv;
+    ph->ph.UV = uv;
+    ph->ph.PV = pv;
+    ph->ph.tmode = tmode;
+    ph->ph.defs_per_bin = {nseg};
+    ph->ph.init_indexing();
+    return ph;
+  } catch (const std::exception& e) {
+    fail(AB_ERR_INVALID, e.what());
+    return nullptr;
+  }
+}
+void ab_phase_destroy(ab_phase* ph) { delete ph; }
+int ab_phase_set_control_mode(ab_phase* ph, int m) {
+  if (m < 0 || m > 3) return fail(AB_ERR_INVALID, "bad control mode");
+  ph->ph.cmode = m;
+  ph->ph.init_indexing();
+  return AB_OK;
+}
+int ab_phase_set_integral_mode(ab_phase* ph, int m) {
+  if (m < 0 || m > 2) return fail(AB_ERR_INVALID, "bad integral mode");
+  ph->ph.imode = m;
+  return AB_OK;
+}
+int ab_phase_set_static_params(ab_phase* ph, int n) {
+  if (n < 0) return fail(AB_ERR_INVALID, "negative static parameter count");
+  ph->ph.SPV = n;
+  ph->ph.init_indexing();
+  return AB_OK;
+}
+int ab_phase_set_mesh(ab_phase* ph, int nbins, const double* sp, const int* defs) {
+  AB_TRY
+  if (nbins < 1) return fail(AB_ERR_INVALID, "need at least one bin");
+  ph->ph.bin_spacing.assign(sp, sp + nbins + 1);
+  ph->ph.defs_per_bin.assign(defs, defs + nbins);
+  ph->ph.init_indexing();
+  return AB_OK;
+  AB_CATCH
+}
+int ab_phase_add_function(ab_phase* ph, int role, int node, int region, const int* x, int nx, const int* o, int no, const int* s,
+                          int ns, const int* e, int ne) {
+  AB_TRY
+  StateFn sf;
+  sf.root = node;
+  sf.region = region;
+  sf.xtuv.assign(x, x + nx);
+  sf.opv.assign(o, o + no);
+  sf.spv.assign(s, s + ns);
+  sf.ext.assign(e, e + ne);
+  ph->ph.g->at(node);
+  if (region == R_ODEPARAMS || region == R_STATICPARAMS) sf.region = R_PARAMS;
+  switch (role) {
+    case AB_ROLE_OBJECTIVE: ph->ph.objs.push_back(sf); return (int) ph->ph.objs.size() - 1;
+    case AB_ROLE_EQUALITY: ph->ph.eqs.push_back(sf); return (int) ph->ph.eqs.size() - 1;
+    case AB_ROLE_INEQUALITY: ph->ph.iqs.push_back(sf); return (int) ph->ph.iqs.size() - 1;
+    case AB_ROLE_INTEGRAL_OBJECTIVE: ph->ph.integrals.push_back(sf); return (int) ph->ph.integrals.size() - 1;
+    case AB_ROLE_INTEGRAL_PARAM: ph->ph.param_integrals.push_back(sf); return (int) ph->ph.param_integrals.size() - 1;
+    default: return fail(AB_ERR_INVALID, "bad role");
+  }
+  AB_CATCH
+}
+int ab_phase_clear_functions(ab_phase* ph) {
+  ph->ph.eqs.clear();
+  ph->ph.iqs.clear();
+  ph->ph.objs.clear();
+  ph->ph.integrals.clear();
+  ph->ph.param_integrals.clear();
+  return AB_OK;
+}
+int ab_phase_dims(ab_phase* ph, int out[8]) {
+  AB_TRY
+  ph->ph.init_indexing();
+  const PhaseIndexer& ix = ph->ph.idx;
+  out[0] = ix.numPhaseVars;
+  out[1] = ix.numStates;
+  out[2] = ix.numDefects;
+  out[3] = ix.DCS;
+  out[4] = ix.XtUV();
+  out[5] = ix.PV;
+  out[6] = ix.SPV;
+  out[7] = ix.blocked;
+  return AB_OK;
+  AB_CATCH
+}
+int ab_phase_state_spacing(ab_phase* ph, double* out) {
+  AB_TRY
+  auto s = ph->ph.state_spacing();
+  std::memcpy(out, s.data(), s.size() * sizeof(double));
+  return AB_OK;
+  AB_CATCH
+}
+int ab_phase_transcribe(ab_phase* ph, ab_problem* p, int voff, int eoff, int ioff, int out[3]) {
+  AB_TRY
+  ph->ph.transcribe(p->p, voff, eoff, ioff);
+  out[0] = ph->ph.idx.numPhaseVars;
+  out[1] = ph->ph.idx.numEq;
+  out[2] = ph->ph.idx.numIq;
+  p->p.analyzed = false;
+  return AB_OK;
+  AB_CATCH
+}
+int ab_phase_make_input(ab_phase* ph, const double* traj, const double* sp, double* X) {
+  AB_TRY
+  ph->ph.init_indexing();
+  const PhaseIndexer& ix = ph->ph.idx;
+  const int n = ix.XtUV(), w = n + ix.PV, xt = ix.XtV();
+  if (ix.blocked) {
+    for (int i = 0; i < ix.numStates; i++)
+      for (int k = 0; k < xt; k++) X[(size_t) i * xt + k] = traj[(size_t) i * w + k];
+    for (int i = 0; i < ix.numDefects; i++)
+      for (int k = 0; k < ix.UV; k++)
+        X[(size_t) ix.numStates * xt + (size_t) i * ix.UV + k] = traj[(size_t) i * (ix.DCS - 1) * w + xt + k];
+    for (int k = 0; k < ix.PV; k++) X[(size_t) ix.numStates * xt + (size_t) ix.numDefects * ix.UV + k] = traj[n + k];
+  } else {
+    for (int i = 0; i < ix.numStates; i++)
+      for (int k = 0; k < n; k++) X[(size_t) i * n + k] = traj[(size_t) i * w + k];
+    for (int k = 0; k < ix.PV; k++) X[(size_t) ix.numStates * n + k] = traj[n + k];
+  }
+  for (int k = 0; k < ix.SPV; k++) X[(size_t) ix.numPhaseVars - ix.SPV + k] = sp[k];
+  return AB_OK;
+  AB_CATCH
+}
+
+// ------------------------------------------------------------------ plan
+int ab_plan_create(const ab_problem* p, int device, ab_plan** out) {
+  AB_TRY
+  if (!out) return fail(AB_ERR_INVALID, "null out pointer");
+  *out = nullptr;
+  if (ab_device_count() <= 0)
+    return fail(AB_ERR_NO_DEVICE, "no CUDA device: the KKT evaluation path has no CPU fallback");
+  std::unique_ptr<ab_plan> pl(new ab_plan());
+  pl->plan.prob = p->p;
+  int rc = pl->plan.build(device);
+  if (rc != 0) return fail(rc, pl->plan.last_error);
+  *out = pl.release();
+  return AB_OK;
+  AB_CATCH
+}
+void ab_plan_destroy(ab_plan* plan) { delete plan; }
+
+#define PLAN_CUDA(call)                                                              \
+  do {                                                                               \
+    cudaError_t e__ = (call);                                                        \
+    if (e__ != cudaSuccess) return fail((int) e__, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+  } while (0)
+
+int ab_plan_set_inputs(ab_plan* plan, const double* X, const double* LE, const double* LI) {
+  Plan& P = plan->plan;
+  PLAN_CUDA(cudaSetDevice(P.device));
+  if (X) PLAN_CUDA(cudaMemcpyAsync(P.d_X, X, sizeof(double) * P.prob.nvars, cudaMemcpyHostToDevice, P.stream));
+  if (LE && P.prob.neq) PLAN_CUDA(cudaMemcpyAsync(P.d_LE, LE, sizeof(double) * P.prob.neq, cudaMemcpyHostToDevice, P.stream));
+  if (LI && P.prob.niq) PLAN_CUDA(cudaMemcpyAsync(P.d_LI, LI, sizeof(double) * P.prob.niq, cudaMemcpyHostToDevice, P.stream));
+  return AB_OK;
+}
+int ab_plan_set_solver_coeffs(ab_plan* plan, const double* c) {
+  int rc = plan->plan.set_solver_coeffs(c);
+  return rc ? fail(rc, plan->plan.last_error) : AB_OK;
+}
+int ab_plan_eval(ab_plan* plan, int mode, double obj_scale) {
+  int rc = plan->plan.eval(mode, obj_scale);
+  return rc ? fail(rc, plan->plan.last_error) : AB_OK;
+}
+int ab_plan_sync(ab_plan* plan) {
+  PLAN_CUDA(cudaSetDevice(plan->plan.device));
+  PLAN_CUDA(cudaStreamSynchronize(plan->plan.stream));
+  return AB_OK;
+}
+int ab_plan_get_outputs(ab_plan* plan, double* val, double* pgx, double* agx, double* fxe, double* fxi, double* kkt) {
+  Plan& P = plan->plan;
+  PLAN_CUDA(cudaSetDevice(P.device));
+  auto D2H = [&](double* dst, const double* src, size_t n) -> cudaError_t {
+    if (!dst || n == 0) return cudaSuccess;
+    return cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost, P.stream);
+  };
+  PLAN_CUDA(D2H(val, P.d_val, 1));
+  PLAN_CUDA(D2H(pgx, P.d_pgx, P.prob.nvars));
+  PLAN_CUDA(D2H(agx, P.d_agx, P.prob.nvars));
+  PLAN_CUDA(D2H(fxe, P.d_fxe, P.prob.neq));
+  PLAN_CUDA(D2H(fxi, P.d_fxi, P.prob.niq));
+  PLAN_CUDA(D2H(kkt, P.d_kkt, (size_t) P.prob.nnz()));
+  PLAN_CUDA(cudaStreamSynchronize(P.stream));
+  return AB_OK;
+}
+int ab_plan_eval_host(ab_plan* plan, int mode, double obj_scale, const double* X, const double* LE, const double* LI, double* val,
+                      double* pgx, double* agx, double* fxe, double* fxi, double* kkt) {
+  int rc = ab_plan_set_inputs(plan, X, LE, LI);
+  if (rc) return rc;
+  rc = ab_plan_eval(plan, mode, obj_scale);
+  if (rc) return rc;
+  return ab_plan_get_outputs(plan, val, pgx, agx, fxe, fxi, kkt);
+}
+void* ab_plan_device_ptr(ab_plan* plan, int which) {
+  Plan& P = plan->plan;
+  switch (which) {
+    case AB_PTR_X: return P.d_X;
+    case AB_PTR_LE: return P.d_LE;
+    case AB_PTR_LI: return P.d_LI;
+    case AB_PTR_KKT: return P.d_kkt;
+    case AB_PTR_FXE: return P.d_fxe;
+    case AB_PTR_FXI: return P.d_fxi;
+    case AB_PTR_PGX: return P.d_pgx;
+    case AB_PTR_AGX: return P.d_agx;
+    case AB_PTR_VAL: return P.d_val;
+    default: return nullptr;
+  }
+}
+void* ab_plan_stream(ab_plan* plan) { return (void*) plan->plan.stream; }
+long long ab_plan_launches(const ab_plan* plan) { return plan->plan.launches; }
+
+}  // extern "C"

@@ -1,0 +1,61 @@
+// Plain-old-data descriptors passed by value to the kernels (kernels.cu) by the plan (plan.cu).
+#pragma once
+#include <stdint.h>
+
+#include "tape.h"
+
+namespace ab {
+
+enum FnRole : int { ROLE_OBJ = 0, ROLE_EQ = 1, ROLE_IQ = 2 };
+
+// What a launch computes, mirroring the per-function methods of the reference's solver interface
+// (/root/reference/src/VectorFunctions/VectorFunctionTypeErasure/SolverInterfaceSpecs.h:41-92).
+enum FnMode : int {
+  FM_VALUES = 0,    // constraints() / objective()
+  FM_GRAD = 1,      // constraints_adjointgradient() / objective_gradient(): values + J^T lambda, no KKT writes
+  FM_JAC = 2,       // constraints_jacobian(): values + Jacobian into KKT
+  FM_JAC_GRAD = 3,  // constraints_jacobian_adjointgradient()
+  FM_ALL = 4        // constraints_jacobian_adjointgradient_adjointhessian() / objective_gradient_hessian()
+};
+
+// One function (all its applications) as the device sees it.
+struct FnDev {
+  const Instr* tape;   // global memory copy of the tape
+  int n_primal;        // instructions of the primal section
+  int n_total;         // instructions of the whole tape
+  int slots_primal;
+  int slots_total;
+  int ir, orows;
+  int nappconst;
+  int role;            // FnRole
+  int linear;          // type-level linear: no Hessian triplets exist
+  int app_begin;       // first application evaluated by this device
+  int app_end;         // one past the last
+  int E;               // KKT triplets per application (depends on role / linear)
+  const int* vindex;   // [nappl][ir]   global variable index of input i
+  const int* cindex;   // [nappl][orows] constraint row (within its own eq / iq block)
+  const double* appconst;  // [nappl][nappconst]
+  const int* kkt_dest;     // [nappl][E]: >=0 CSR value slot written directly; <0: ~idx into stage
+  const int* f_dest;       // [nappl][orows]: >=0 index into FX (eq / iq block); <0: ~idx into stage
+  long long g_stage;       // gradient contributions go to stage[g_stage + app*ir + i]
+  long long v_stage;       // objective value contributions go to stage[v_stage + app]
+};
+
+struct EvalIO {
+  const double* X;
+  const double* L;   // LE or LI for constraints (indexed by cindex); unused for objectives
+  double obj_scale;
+  double* kkt;       // CSR values
+  double* fx;        // FXE or FXI block
+  double* stage;     // staging buffer for every multi-source / reduced output
+};
+
+// Fixed-order segmented gather-sum: out[target[t]] = sum_{s in [ptr[t], ptr[t+1])} stage[src[s]]
+struct GatherDev {
+  int ntargets;
+  const long long* ptr;
+  const int* src;
+  const int* target;
+};
+
+}  // namespace ab

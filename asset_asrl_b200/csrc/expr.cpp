@@ -1,0 +1,597 @@
+#include "expr.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <sstream>
+#include <stdexcept>
+
+namespace ab {
+
+// ---------------------------------------------------------------------------------------------
+// SDag
+// ---------------------------------------------------------------------------------------------
+static inline uint64_t dbits(double v) {
+  uint64_t u;
+  std::memcpy(&u, &v, 8);
+  return u;
+}
+
+int SDag::raw(uint16_t op, int a, int b, int c, double imm) {
+  if (imm == 0.0) imm = 0.0;  // fold -0.0 into +0.0 for consing
+  Key k {op, a, b, c, dbits(imm)};
+  auto it = cons.find(k);
+  if (it != cons.end()) return it->second;
+  n.push_back(SNode {op, a, b, c, imm});
+  int id = (int) n.size() - 1;
+  cons.emplace(k, id);
+  return id;
+}
+
+int SDag::add(int a, int b) {
+  if (is_const(a) && is_const(b)) return constant(cval(a) + cval(b));
+  if (is_const(a)) std::swap(a, b);
+  if (is_const(b)) return addc(a, cval(b));
+  if (a > b) std::swap(a, b);
+  return raw(OP_ADD, a, b, -1, 0.0);
+}
+int SDag::sub(int a, int b) {
+  if (is_const(a) && is_const(b)) return constant(cval(a) - cval(b));
+  if (is_const(b)) return addc(a, -cval(b));
+  if (is_const(a)) return addc(neg(b), cval(a));
+  if (a == b) return constant(0.0);
+  return raw(OP_SUB, a, b, -1, 0.0);
+}
+int SDag::mul(int a, int b) {
+  if (is_const(a) && is_const(b)) return constant(cval(a) * cval(b));
+  if (is_const(a)) std::swap(a, b);
+  if (is_const(b)) return mulc(a, cval(b));
+  if (a == b) return raw(OP_SQUARE, a, -1, -1, 0.0);
+  if (a > b) std::swap(a, b);
+  return raw(OP_MUL, a, b, -1, 0.0);
+}
+int SDag::div(int a, int b) {
+  if (is_const(a) && is_const(b)) return constant(cval(a) / cval(b));
+  if (is_const(b)) return mulc(a, 1.0 / cval(b));
+  if (is_const(a)) {
+    if (cval(a) == 0.0) return constant(0.0);
+    return mulc(unary(OP_INV, b), cval(a));
+  }
+  return raw(OP_DIV, a, b, -1, 0.0);
+}
+int SDag::neg(int a) {
+  if (is_const(a)) return constant(-cval(a));
+  if (n[a].op == OP_NEG) return n[a].a;
+  if (n[a].op == OP_MULC) return mulc(n[a].a, -n[a].imm);
+  return raw(OP_NEG, a, -1, -1, 0.0);
+}
+int SDag::addc(int a, double c) {
+  if (is_const(a)) return constant(cval(a) + c);
+  if (c == 0.0) return a;
+  if (n[a].op == OP_ADDC) return addc(n[a].a, n[a].imm + c);
+  return raw(OP_ADDC, a, -1, -1, c);
+}
+int SDag::mulc(int a, double c) {
+  if (is_const(a)) return constant(cval(a) * c);
+  if (c == 1.0) return a;
+  if (c == 0.0) return constant(0.0);
+  if (c == -1.0) return neg(a);
+  if (n[a].op == OP_MULC) return mulc(n[a].a, n[a].imm * c);
+  if (n[a].op == OP_NEG) return mulc(n[a].a, -c);
+  return raw(OP_MULC, a, -1, -1, c);
+}
+
+static double eval_unary(uint16_t op, double x, double imm) {
+  switch (op) {
+    case OP_SQUARE: return x * x;
+    case OP_INV: return 1.0 / x;
+    case OP_SQRT: return std::sqrt(x);
+    case OP_EXP: return std::exp(x);
+    case OP_LOG: return std::log(x);
+    case OP_SIN: return std::sin(x);
+    case OP_COS: return std::cos(x);
+    case OP_TAN: return std::tan(x);
+    case OP_ASIN: return std::asin(x);
+    case OP_ACOS: return std::acos(x);
+    case OP_ATAN: return std::atan(x);
+    case OP_SINH: return std::sinh(x);
+    case OP_COSH: return std::cosh(x);
+    case OP_TANH: return std::tanh(x);
+    case OP_ASINH: return std::asinh(x);
+    case OP_ACOSH: return std::acosh(x);
+    case OP_ATANH: return std::atanh(x);
+    case OP_ABS: return std::fabs(x);
+    case OP_SIGN: return (x > 0.0) ? 1.0 : ((x < 0.0) ? -1.0 : 0.0);
+    case OP_POWC: return std::pow(x, imm);
+    default: throw std::logic_error("eval_unary: bad op");
+  }
+}
+
+int SDag::unary(uint16_t op, int a, double imm) {
+  if (is_const(a)) return constant(eval_unary(op, cval(a), imm));
+  if (op == OP_POWC) {
+    if (imm == 1.0) return a;
+    if (imm == 0.0) return constant(1.0);
+    if (imm == 2.0) return raw(OP_SQUARE, a, -1, -1, 0.0);
+    if (imm == -1.0) return raw(OP_INV, a, -1, -1, 0.0);
+    if (imm == 0.5) return raw(OP_SQRT, a, -1, -1, 0.0);
+  }
+  if (op == OP_NEG) return neg(a);
+  return raw(op, a, -1, -1, imm);
+}
+int SDag::atan2(int y, int x) {
+  if (is_const(y) && is_const(x)) return constant(std::atan2(cval(y), cval(x)));
+  return raw(OP_ATAN2, y, x, -1, 0.0);
+}
+int SDag::cmp(uint16_t op, int a, int b) {
+  if (is_const(a) && is_const(b)) {
+    bool r = (op == OP_LT) ? (cval(a) < cval(b)) : (cval(a) <= cval(b));
+    return constant(r ? 1.0 : 0.0);
+  }
+  return raw(op, a, b, -1, 0.0);
+}
+int SDag::select(int c, int a, int b) {
+  if (is_const(c)) return (cval(c) != 0.0) ? a : b;
+  if (a == b) return a;
+  return raw(OP_SELECT, c, a, b, 0.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Lowering of vector nodes onto the scalar DAG
+// ---------------------------------------------------------------------------------------------
+static int norm_power(SDag& dag, const std::vector<int>& x, int p, int* norm_out = nullptr) {
+  // ||x||^p following the reference's power cases (Norms.h:77-100): p in {1,2,3,4,-1,-2,-3,-4}
+  int s2 = -1;
+  for (int xi: x) {
+    int sq = dag.mul(xi, xi);
+    s2 = (s2 < 0) ? sq : dag.add(s2, sq);
+  }
+  if (p == 2) return s2;
+  if (p == 4) return dag.mul(s2, s2);
+  if (p == -2) return dag.unary(OP_INV, s2);
+  if (p == -4) return dag.unary(OP_INV, dag.mul(s2, s2));
+  int nrm = dag.unary(OP_SQRT, s2);
+  if (norm_out) *norm_out = nrm;
+  if (p == 1) return nrm;
+  if (p == 3) return dag.mul(s2, nrm);
+  if (p == -1) return dag.unary(OP_INV, nrm);
+  if (p == -3) return dag.unary(OP_INV, dag.mul(s2, nrm));
+  if (p == 5) return dag.mul(dag.mul(s2, s2), nrm);
+  if (p == -5) return dag.unary(OP_INV, dag.mul(dag.mul(s2, s2), nrm));
+  return dag.unary(OP_POWC, nrm, (double) p);
+}
+
+namespace {
+struct LowerCtx {
+  std::map<std::pair<int, std::vector<int>>, std::vector<int>> memo;
+};
+std::vector<int> lower_impl(const Graph& g, int root, const std::vector<int>& in, SDag& dag, LowerCtx& ctx);
+}  // namespace
+
+std::vector<int> lower(const Graph& g, int root, const std::vector<int>& in, SDag& dag) {
+  LowerCtx ctx;
+  return lower_impl(g, root, in, dag, ctx);
+}
+
+namespace {
+std::vector<int> lower_impl(const Graph& g, int root, const std::vector<int>& in, SDag& dag, LowerCtx& ctx) {
+  auto mkey = std::make_pair(root, in);
+  auto mit = ctx.memo.find(mkey);
+  if (mit != ctx.memo.end()) return mit->second;
+  const VNode& nd = g.at(root);
+  if ((int) in.size() != nd.ir)
+    throw std::invalid_argument("lower: input size mismatch (node expects " + std::to_string(nd.ir) + ", got "
+                                + std::to_string(in.size()) + ")");
+  auto L = [&](int k) { return lower_impl(g, nd.ch[k], in, dag, ctx); };
+  std::vector<int> out;
+  switch (nd.kind) {
+    case VK_ARGS: out = in; break;
+    case VK_SEGMENT: {
+      auto c = L(0);
+      out.assign(c.begin() + nd.ip[0], c.begin() + nd.ip[0] + nd.ip[1]);
+    } break;
+    case VK_ELEMENTS: {
+      auto c = L(0);
+      for (int i: nd.ip) out.push_back(c.at(i));
+    } break;
+    case VK_CONSTANT:
+      for (double v: nd.d) out.push_back(dag.constant(v));
+      break;
+    case VK_APPCONST:
+      for (int i = 0; i < nd.orows; i++) out.push_back(dag.appconst(nd.ip[0] + i));
+      break;
+    case VK_STACK:
+      for (size_t k = 0; k < nd.ch.size(); k++) {
+        auto c = L((int) k);
+        out.insert(out.end(), c.begin(), c.end());
+      }
+      break;
+    case VK_SUM: {
+      out = L(0);
+      for (size_t k = 1; k < nd.ch.size(); k++) {
+        auto c = L((int) k);
+        for (size_t i = 0; i < out.size(); i++) out[i] = dag.add(out[i], c[i]);
+      }
+    } break;
+    case VK_DIFF: {
+      auto a = L(0), b = L(1);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.sub(a[i], b[i]));
+    } break;
+    case VK_SCALED: {
+      auto a = L(0);
+      for (int ai: a) out.push_back(dag.mulc(ai, nd.d[0]));
+    } break;
+    case VK_ROWSCALED: {
+      auto a = L(0);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.mulc(a[i], nd.d[i]));
+    } break;
+    case VK_ADDVEC: {
+      auto a = L(0);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.addc(a[i], nd.d[i]));
+    } break;
+    case VK_VECMINUS: {
+      auto a = L(0);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.addc(dag.neg(a[i]), nd.d[i]));
+    } break;
+    case VK_UNARY: {
+      auto a = L(0);
+      uint16_t op = (uint16_t) nd.ip[0];
+      double imm = nd.d.empty() ? 0.0 : nd.d[0];
+      for (int ai: a) out.push_back(dag.unary(op, ai, imm));
+    } break;
+    case VK_NORM: {
+      auto a = L(0);
+      out.push_back(norm_power(dag, a, nd.ip[0]));
+    } break;
+    case VK_NORMALIZED: {
+      auto a = L(0);
+      int inv = norm_power(dag, a, -nd.ip[0]);
+      for (int ai: a) out.push_back(dag.mul(ai, inv));
+    } break;
+    case VK_DOT: {
+      auto a = L(0), b = L(1);
+      int s = -1;
+      for (size_t i = 0; i < a.size(); i++) {
+        int p = dag.mul(a[i], b[i]);
+        s = (s < 0) ? p : dag.add(s, p);
+      }
+      out.push_back(s);
+    } break;
+    case VK_CROSS: {
+      auto a = L(0), b = L(1);
+      out.push_back(dag.sub(dag.mul(a[1], b[2]), dag.mul(a[2], b[1])));
+      out.push_back(dag.sub(dag.mul(a[2], b[0]), dag.mul(a[0], b[2])));
+      out.push_back(dag.sub(dag.mul(a[0], b[1]), dag.mul(a[1], b[0])));
+    } break;
+    case VK_CWISEPROD: {
+      auto a = L(0), b = L(1);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.mul(a[i], b[i]));
+    } break;
+    case VK_CWISEQUOT: {
+      auto a = L(0), b = L(1);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.div(a[i], b[i]));
+    } break;
+    case VK_VSPROD: {
+      auto a = L(0), s = L(1);
+      for (int ai: a) out.push_back(dag.mul(ai, s[0]));
+    } break;
+    case VK_VSDIV: {
+      auto a = L(0), s = L(1);
+      for (int ai: a) out.push_back(dag.div(ai, s[0]));
+    } break;
+    case VK_CWISESUM: {
+      auto a = L(0);
+      int s = a[0];
+      for (size_t i = 1; i < a.size(); i++) s = dag.add(s, a[i]);
+      out.push_back(s);
+    } break;
+    case VK_ATAN2: {
+      auto y = L(0), x = L(1);
+      out.push_back(dag.atan2(y[0], x[0]));
+    } break;
+    case VK_NESTED: {
+      auto inner = lower_impl(g, nd.ch[1], in, dag, ctx);
+      out = lower_impl(g, nd.ch[0], inner, dag, ctx);
+    } break;
+    case VK_COMPARE: {
+      auto a = L(0), b = L(1);
+      switch (nd.ip[0]) {
+        case 0: out.push_back(dag.cmp(OP_LT, a[0], b[0])); break;
+        case 1: out.push_back(dag.cmp(OP_LE, a[0], b[0])); break;
+        case 2: out.push_back(dag.cmp(OP_LT, b[0], a[0])); break;
+        default: out.push_back(dag.cmp(OP_LE, b[0], a[0])); break;
+      }
+    } break;
+    case VK_BOOL: {
+      auto a = L(0), b = L(1);
+      if (nd.ip[0] == 0)
+        out.push_back(dag.mul(a[0], b[0]));
+      else
+        out.push_back(dag.select(a[0], dag.constant(1.0), b[0]));
+    } break;
+    case VK_IFELSE: {
+      auto c = L(0), a = L(1), b = L(2);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.select(c[0], a[i], b[i]));
+    } break;
+    case VK_IOSCALED: {
+      std::vector<int> sin(in.size());
+      for (size_t i = 0; i < in.size(); i++) sin[i] = dag.mulc(in[i], nd.d[i]);
+      auto a = lower_impl(g, nd.ch[0], sin, dag, ctx);
+      for (size_t i = 0; i < a.size(); i++) out.push_back(dag.mulc(a[i], nd.d[nd.ir + i]));
+    } break;
+    case VK_MATVEC: {
+      auto a = L(0);
+      int cols = (int) a.size();
+      for (int r = 0; r < nd.orows; r++) {
+        int s = dag.constant(0.0);
+        for (int c = 0; c < cols; c++) s = dag.add(s, dag.mulc(a[c], nd.d[(size_t) r * cols + c]));
+        out.push_back(s);
+      }
+    } break;
+    default: throw std::invalid_argument("lower: unknown node kind");
+  }
+  if ((int) out.size() != nd.orows) throw std::logic_error("lower: output size mismatch in kind " + std::to_string(nd.kind));
+  ctx.memo.emplace(mkey, out);
+  return out;
+}
+}  // namespace
+
+ScalarFn lower_function(const Graph& g, int root) {
+  ScalarFn f;
+  f.nin = g.at(root).ir;
+  f.nout = g.at(root).orows;
+  std::vector<int> in(f.nin);
+  for (int i = 0; i < f.nin; i++) in[i] = f.dag.input(i);
+  f.outs = lower(g, root, in, f.dag);
+  return f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Symbolic reverse accumulation: grads[i] = d( sum_k lambda_k * f_k ) / d x_i as new DAG nodes.
+// The derivative rules are the scalar content of the reference's cwise operator table
+// (/root/reference/src/VectorFunctions/CommonFunctions/CwiseOperators.h:31-860) and binary products.
+// ---------------------------------------------------------------------------------------------
+void ScalarFn::make_gradient() {
+  const int N0 = (int) dag.n.size();
+  std::vector<int> adj(N0, -1);
+  auto acc = [&](int i, int v) {
+    if (i < 0) return;
+    if (dag.is_const(v) && dag.cval(v) == 0.0) return;
+    adj[i] = (adj[i] < 0) ? v : dag.add(adj[i], v);
+  };
+  for (int k = 0; k < nout; k++) acc(outs[k], dag.lambda(k));
+  for (int i = N0 - 1; i >= 0; i--) {
+    int yb = adj[i];
+    if (yb < 0) continue;
+    const SNode nd = dag.n[i];  // copy: dag.n may reallocate
+    const int a = nd.a, b = nd.b;
+    switch (nd.op) {
+      case OP_CONST:
+      case OP_INPUT:
+      case OP_LAMBDA:
+      case OP_APPCONST:
+      case OP_SIGN:
+      case OP_LT:
+      case OP_LE: break;
+      case OP_ADD:
+        acc(a, yb);
+        acc(b, yb);
+        break;
+      case OP_SUB:
+        acc(a, yb);
+        acc(b, dag.neg(yb));
+        break;
+      case OP_MUL:
+        acc(a, dag.mul(yb, b));
+        acc(b, dag.mul(yb, a));
+        break;
+      case OP_DIV: {
+        int q = dag.div(yb, b);
+        acc(a, q);
+        acc(b, dag.neg(dag.mul(q, i)));
+      } break;
+      case OP_NEG: acc(a, dag.neg(yb)); break;
+      case OP_ADDC: acc(a, yb); break;
+      case OP_MULC: acc(a, dag.mulc(yb, nd.imm)); break;
+      case OP_SQUARE: acc(a, dag.mul(yb, dag.mulc(a, 2.0))); break;
+      case OP_INV: acc(a, dag.neg(dag.mul(yb, dag.mul(i, i)))); break;
+      case OP_SQRT: acc(a, dag.mul(yb, dag.mulc(dag.unary(OP_INV, i), 0.5))); break;
+      case OP_EXP: acc(a, dag.mul(yb, i)); break;
+      case OP_LOG: acc(a, dag.div(yb, a)); break;
+      case OP_SIN: acc(a, dag.mul(yb, dag.unary(OP_COS, a))); break;
+      case OP_COS: acc(a, dag.neg(dag.mul(yb, dag.unary(OP_SIN, a)))); break;
+      case OP_TAN: acc(a, dag.mul(yb, dag.addc(dag.mul(i, i), 1.0))); break;
+      case OP_ASIN: acc(a, dag.div(yb, dag.unary(OP_SQRT, dag.addc(dag.neg(dag.mul(a, a)), 1.0)))); break;
+      case OP_ACOS: acc(a, dag.neg(dag.div(yb, dag.unary(OP_SQRT, dag.addc(dag.neg(dag.mul(a, a)), 1.0))))); break;
+      case OP_ATAN: acc(a, dag.div(yb, dag.addc(dag.mul(a, a), 1.0))); break;
+      case OP_SINH: acc(a, dag.mul(yb, dag.unary(OP_COSH, a))); break;
+      case OP_COSH: acc(a, dag.mul(yb, dag.unary(OP_SINH, a))); break;
+      case OP_TANH: acc(a, dag.mul(yb, dag.addc(dag.neg(dag.mul(i, i)), 1.0))); break;
+      case OP_ASINH: acc(a, dag.div(yb, dag.unary(OP_SQRT, dag.addc(dag.mul(a, a), 1.0)))); break;
+      case OP_ACOSH: acc(a, dag.div(yb, dag.unary(OP_SQRT, dag.addc(dag.mul(a, a), -1.0)))); break;
+      case OP_ATANH: acc(a, dag.div(yb, dag.addc(dag.neg(dag.mul(a, a)), 1.0))); break;
+      case OP_ABS: acc(a, dag.mul(yb, dag.unary(OP_SIGN, a))); break;
+      case OP_POWC: acc(a, dag.mul(yb, dag.mulc(dag.unary(OP_POWC, a, nd.imm - 1.0), nd.imm))); break;
+      case OP_ATAN2: {  // i = atan2(y=a, x=b)
+        int r2 = dag.add(dag.mul(a, a), dag.mul(b, b));
+        int q = dag.div(yb, r2);
+        acc(a, dag.mul(q, b));
+        acc(b, dag.neg(dag.mul(q, a)));
+      } break;
+      case OP_SELECT: {  // i = a ? b : c
+        int zero = dag.constant(0.0);
+        acc(b, dag.select(a, yb, zero));
+        acc(nd.c, dag.select(a, zero, yb));
+      } break;
+      default: throw std::logic_error("make_gradient: unhandled op " + std::to_string(nd.op));
+    }
+  }
+  grads.assign(nin, -1);
+  for (int i = 0; i < nin; i++) {
+    int id = dag.input(i);
+    grads[i] = (id < N0 && adj[id] >= 0) ? adj[id] : dag.constant(0.0);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tape emission with liveness-based slot allocation.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct VInstr {
+  uint16_t op;
+  int dstnode;  // node defined (or -1 for OUT)
+  int outrow;
+  int a, b, c;  // operand nodes (-1 none); for leaf ops `a` is the literal index
+  double imm;
+};
+inline bool leaf_op(uint16_t op) { return op == OP_CONST || op == OP_INPUT || op == OP_LAMBDA || op == OP_APPCONST; }
+}  // namespace
+
+Tape emit_tape(const ScalarFn& f, bool with_adjoint) {
+  const SDag& dag = f.dag;
+  const int N = (int) dag.n.size();
+  std::vector<char> inP(N, 0), inA(N, 0);
+  auto mark = [&](int root, std::vector<char>& set) {
+    std::vector<int> st {root};
+    while (!st.empty()) {
+      int i = st.back();
+      st.pop_back();
+      if (i < 0 || set[i]) continue;
+      set[i] = 1;
+      const SNode& nd = dag.n[i];
+      if (leaf_op(nd.op)) continue;
+      st.push_back(nd.a);
+      if (nd.b >= 0) st.push_back(nd.b);
+      if (nd.c >= 0) st.push_back(nd.c);
+    }
+  };
+  for (int o: f.outs) mark(o, inP);
+  if (with_adjoint) {
+    if ((int) f.grads.size() != f.nin) throw std::logic_error("emit_tape: gradient not built");
+    for (int gnode: f.grads) mark(gnode, inA);
+  }
+  std::vector<VInstr> vi;
+  auto emit_node = [&](int i) {
+    const SNode& nd = dag.n[i];
+    vi.push_back(VInstr {nd.op, i, -1, nd.a, nd.b, nd.c, nd.imm});
+  };
+  for (int i = 0; i < N; i++)
+    if (inP[i]) emit_node(i);
+  for (int k = 0; k < f.nout; k++) vi.push_back(VInstr {OP_OUT_F, -1, k, f.outs[k], -1, -1, 0.0});
+  const int n_primal = (int) vi.size();
+  if (with_adjoint) {
+    // gradient rows whose node already exists in the primal section
+    for (int i = 0; i < f.nin; i++)
+      if (inP[f.grads[i]]) vi.push_back(VInstr {OP_OUT_G, -1, i, f.grads[i], -1, -1, 0.0});
+    for (int i = 0; i < N; i++) {
+      if (!inA[i] || inP[i]) continue;
+      emit_node(i);
+      for (int r = 0; r < f.nin; r++)
+        if (f.grads[r] == i) vi.push_back(VInstr {OP_OUT_G, -1, r, i, -1, -1, 0.0});
+    }
+  }
+  // last use
+  std::vector<int> last(N, -1);
+  for (int p = 0; p < (int) vi.size(); p++) {
+    const VInstr& v = vi[p];
+    if (v.dstnode >= 0 && leaf_op(v.op)) continue;
+    if (v.a >= 0) last[v.a] = p;
+    if (v.b >= 0) last[v.b] = p;
+    if (v.c >= 0) last[v.c] = p;
+  }
+  Tape t;
+  t.nin = f.nin;
+  t.nout = f.nout;
+  t.has_adjoint = with_adjoint;
+  t.n_primal = n_primal;
+  std::vector<int> slot(N, -1);
+  std::vector<int> freelist;
+  int nslots = 0;
+  int maxapp = -1;
+  for (int p = 0; p < (int) vi.size(); p++) {
+    const VInstr& v = vi[p];
+    Instr ins;
+    std::memset(&ins, 0, sizeof(ins));
+    ins.op = v.op;
+    bool leaf = (v.dstnode >= 0 && leaf_op(v.op));
+    auto S = [&](int node) -> uint16_t {
+      if (node < 0) return 0;
+      if (slot[node] < 0) throw std::logic_error("emit_tape: operand has no slot");
+      return (uint16_t) slot[node];
+    };
+    if (leaf) {
+      ins.a = (uint16_t) std::max(v.a, 0);
+      ins.imm = v.imm;
+      if (v.op == OP_APPCONST) maxapp = std::max(maxapp, v.a);
+    } else {
+      ins.a = S(v.a);
+      ins.b = S(v.b);
+      if (v.op == OP_SELECT || v.op == OP_FMA)
+        ins.c = S(v.c);
+      else
+        ins.imm = v.imm;
+    }
+    // release operands that die here (their slot may be reused by dst: operands are read first)
+    if (!leaf) {
+      int ops[3] = {v.a, v.b, v.c};
+      for (int q = 0; q < 3; q++) {
+        int o = ops[q];
+        if (o < 0 || last[o] != p || slot[o] < 0) continue;
+        bool dup = false;
+        for (int r = 0; r < q; r++) dup |= (ops[r] == o);
+        if (!dup) freelist.push_back(slot[o]);
+      }
+    }
+    if (v.dstnode >= 0) {
+      int s;
+      if (last[v.dstnode] < 0) {
+        // value never used (can happen for a dead leaf); still give it a slot and free immediately
+        if (freelist.empty()) freelist.push_back(nslots++);
+        s = freelist.back();
+      } else if (!freelist.empty()) {
+        s = freelist.back();
+        freelist.pop_back();
+      } else {
+        s = nslots++;
+      }
+      slot[v.dstnode] = s;
+      ins.dst = (uint16_t) s;
+    } else {
+      ins.dst = (uint16_t) v.outrow;
+    }
+    if (nslots > 65535) throw std::length_error("emit_tape: more than 65535 live slots");
+    t.code.push_back(ins);
+    if (p == n_primal - 1) t.slots_primal = nslots;
+  }
+  if (n_primal == 0) t.slots_primal = 0;
+  t.slots_total = nslots;
+  t.nappconst = maxapp + 1;
+  return t;
+}
+
+// ---------------------------------------------------------------------------------------------
+// s-expression description (consumed by the CPU oracle in tests; never by the product path)
+// ---------------------------------------------------------------------------------------------
+static const char* kind_name(int k) {
+  static const char* names[] = {"args",     "segment", "elements",  "constant",  "stack",    "sum",     "diff",   "scaled",
+                                "rowscaled", "addvec",  "vecminus",  "unary",     "norm",     "normalized", "dot", "cross",
+                                "cwiseprod", "cwisequot", "vsprod",  "vsdiv",     "cwisesum", "atan2",   "nested", "ifelse",
+                                "compare",  "bool",    "ioscaled",  "appconst",  "matvec"};
+  return names[k];
+}
+
+std::string Graph::describe(int root) const {
+  std::ostringstream os;
+  os.precision(17);
+  const VNode& nd = at(root);
+  os << "(" << kind_name(nd.kind) << " " << nd.ir << " " << nd.orows << " " << (nd.tlin ? 1 : 0) << " [";
+  for (size_t i = 0; i < nd.ip.size(); i++) os << (i ? " " : "") << nd.ip[i];
+  os << "] [";
+  for (size_t i = 0; i < nd.d.size(); i++) os << (i ? " " : "") << nd.d[i];
+  os << "]";
+  for (int c: nd.ch) os << " " << describe(c);
+  os << ")";
+  return os.str();
+}
+
+}  // namespace ab

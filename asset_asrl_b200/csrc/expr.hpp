@@ -1,0 +1,153 @@
+// Host-side expression graph -> scalar DAG -> device tape.
+//
+// The reference builds C++ expression-template types behind type erasure and has no walkable graph
+// (/root/reference/src/VectorFunctions/VectorFunctionTypeErasure/GenericFunction.h:87-405); this
+// build records its own DAG at construction time and lowers it once to the tape of tape.h.
+#pragma once
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "tape.h"
+
+namespace ab {
+
+// ---------------------------------------------------------------------------------------------
+// Vector-level expression nodes (what the Python / C++ user composes).
+// ---------------------------------------------------------------------------------------------
+enum VKind : int {
+  VK_ARGS = 0,      // Arguments(ir): identity
+  VK_SEGMENT,       // child[start : start+size]          ip = {start, size}
+  VK_ELEMENTS,      // child[ip...] gather
+  VK_CONSTANT,      // constant vector d, input size ir
+  VK_STACK,         // concatenate children outputs
+  VK_SUM,           // sum of children (same orows)
+  VK_DIFF,          // ch0 - ch1
+  VK_SCALED,        // ch0 * d[0]
+  VK_ROWSCALED,     // ch0 .* d   (per-output scale)
+  VK_ADDVEC,        // ch0 + d
+  VK_VECMINUS,      // d - ch0
+  VK_UNARY,         // cwise scalar op ip[0] (an ab::Op) on every output of ch0, d[0] = power for POWC
+  VK_NORM,          // ||ch0||^p      ip = {p}
+  VK_NORMALIZED,    // ch0 / ||ch0||^p ip = {p}
+  VK_DOT,           // ch0 . ch1
+  VK_CROSS,         // ch0 x ch1 (3-vectors)
+  VK_CWISEPROD,     // ch0 .* ch1
+  VK_CWISEQUOT,     // ch0 ./ ch1
+  VK_VSPROD,        // vector ch0 * scalar ch1
+  VK_VSDIV,         // vector ch0 / scalar ch1
+  VK_CWISESUM,      // sum of the elements of ch0
+  VK_ATAN2,         // atan2(ch0, ch1), scalars
+  VK_NESTED,        // ch0(ch1(x)): outer evaluated at inner
+  VK_IFELSE,        // ch0 (condition, scalar 0/1) ? ch1 : ch2
+  VK_COMPARE,       // ip[0] in {0:<,1:<=,2:>,3:>=}, ch0 vs ch1 (scalars) -> 0/1
+  VK_BOOL,          // ip[0] in {0:and,1:or}
+  VK_IOSCALED,      // out_scale .* ch0(in_scale .* x)    d = [in_scales(ir) , out_scales(orows)]
+  VK_APPCONST,      // per-application constant vector of size orows, ip = {first index}
+  VK_MATVEC,        // matrix(d, orows x ch.orows, row-major) * ch0
+};
+
+struct VNode {
+  int kind = 0;
+  int ir = 0;     // input rows
+  int orows = 0;  // output rows
+  std::vector<int> ch;
+  std::vector<double> d;
+  std::vector<int> ip;
+  // Type-level linearity exactly as the reference's C++ types would report it (SURVEY.md section 8a,
+  // note L).  `tlin` is the concrete type's static IsLinearFunction; `raw` says the value is NOT
+  // wrapped in a GenericFunction (only Arguments/Segment/Element or C++-built helpers), i.e. a parent
+  // type sees `tlin` rather than GenericFunction's `false` (ComputableBase.h:90).
+  bool tlin = false;
+  bool raw = false;
+};
+
+struct Graph {
+  std::vector<VNode> nodes;
+  int add(const VNode& n) {
+    nodes.push_back(n);
+    return (int) nodes.size() - 1;
+  }
+  const VNode& at(int i) const { return nodes.at(i); }
+  // linearity a parent type observes for child i
+  bool seen_lin(int i) const { return nodes[i].raw && nodes[i].tlin; }
+  std::string describe(int root) const;  // s-expression consumed by the CPU oracle (tests only)
+};
+
+// ---------------------------------------------------------------------------------------------
+// Scalar DAG with hash-consing, constant folding and light algebraic simplification.
+// ---------------------------------------------------------------------------------------------
+struct SNode {
+  uint16_t op;
+  int a, b, c;
+  double imm;
+};
+
+struct SDag {
+  std::vector<SNode> n;
+  struct Key {
+    uint16_t op;
+    int a, b, c;
+    uint64_t imm;
+    bool operator==(const Key& o) const { return op == o.op && a == o.a && b == o.b && c == o.c && imm == o.imm; }
+  };
+  struct KeyHash {
+    size_t operator()(const Key& k) const {
+      uint64_t h = k.op * 0x9E3779B97F4A7C15ull;
+      h ^= (uint64_t) (uint32_t) k.a + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+      h ^= (uint64_t) (uint32_t) k.b + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+      h ^= (uint64_t) (uint32_t) k.c + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+      h ^= k.imm + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2);
+      return (size_t) h;
+    }
+  };
+  std::unordered_map<Key, int, KeyHash> cons;
+
+  int raw(uint16_t op, int a, int b, int c, double imm);
+  bool is_const(int i) const { return n[i].op == OP_CONST; }
+  double cval(int i) const { return n[i].imm; }
+
+  int constant(double v) { return raw(OP_CONST, -1, -1, -1, v); }
+  int input(int k) { return raw(OP_INPUT, k, -1, -1, 0.0); }
+  int lambda(int k) { return raw(OP_LAMBDA, k, -1, -1, 0.0); }
+  int appconst(int k) { return raw(OP_APPCONST, k, -1, -1, 0.0); }
+  int add(int a, int b);
+  int sub(int a, int b);
+  int mul(int a, int b);
+  int div(int a, int b);
+  int neg(int a);
+  int addc(int a, double c);
+  int mulc(int a, double c);
+  int unary(uint16_t op, int a, double imm = 0.0);
+  int atan2(int y, int x);
+  int cmp(uint16_t op, int a, int b);
+  int select(int c, int a, int b);
+};
+
+// A lowered function: outputs and (optionally) the adjoint gradient of lambda . f.
+struct ScalarFn {
+  int nin = 0, nout = 0;
+  SDag dag;
+  std::vector<int> outs;   // nout scalar node ids
+  std::vector<int> grads;  // nin scalar node ids (d(lambda.f)/dx_i), empty until make_gradient()
+  void make_gradient();
+};
+
+// Device tape + bookkeeping.
+struct Tape {
+  std::vector<Instr> code;
+  int n_primal = 0;       // instructions in the primal section (values + Jacobian)
+  int slots_primal = 0;   // slots live in the primal section
+  int slots_total = 0;    // slots for the whole tape
+  int nin = 0, nout = 0, nappconst = 0;
+  bool has_adjoint = false;
+};
+
+std::vector<int> lower(const Graph& g, int root, const std::vector<int>& in, SDag& dag);
+ScalarFn lower_function(const Graph& g, int root);
+Tape emit_tape(const ScalarFn& f, bool with_adjoint);
+
+}  // namespace ab

@@ -1,0 +1,283 @@
+#include "nlp.hpp"
+
+#include <algorithm>
+#include <stdexcept>
+#include <thread>
+
+namespace ab {
+
+namespace {
+
+// Enumerate the KKT triplets of one function in the reference's emission order
+// (DenseFunctionBase.h:1097-1129): per application, per input column i: lower-triangular Hessian
+// rows j>=i (non-linear functions only), then Jacobian rows (constraints only).
+template<class F>
+inline void for_each_triplet(const FuncRec& fn, int conoffset, F&& cb) {
+  const bool hess = !fn.linear;
+  const bool jac = fn.role != 0;
+  const int ir = fn.ir, orr = fn.orows;
+  for (int V = 0; V < fn.nappl; V++) {
+    const int* vi = fn.vindex.data() + (size_t) V * ir;
+    const int* ci = fn.cindex.data() + (size_t) V * orr;
+    for (int i = 0; i < ir; i++) {
+      if (hess)
+        for (int j = i; j < ir; j++) cb(vi[j], vi[i]);
+      if (jac)
+        for (int j = 0; j < orr; j++) cb(ci[j] + conoffset, vi[i]);
+    }
+  }
+}
+
+void build_gather(const std::vector<int>& tgt_of_src,  // target id per source (in ascending stage order)
+                  const std::vector<int>& stage_of_src, int ntargets_total,
+                  const std::vector<int>& out_index,    // output index per target id
+                  const std::vector<char>& keep,        // which target ids get a gather entry
+                  GatherList out[2]) {
+  std::vector<long long> cnt((size_t) ntargets_total + 1, 0);
+  for (int t: tgt_of_src) cnt[(size_t) t + 1]++;
+  for (int t = 0; t < ntargets_total; t++) cnt[(size_t) t + 1] += cnt[t];
+  std::vector<int> sorted(tgt_of_src.size());
+  {
+    std::vector<long long> pos(cnt.begin(), cnt.end() - 1);
+    for (size_t s = 0; s < tgt_of_src.size(); s++) sorted[(size_t) pos[tgt_of_src[s]]++] = stage_of_src[s];
+  }
+  for (int w = 0; w < 2; w++) {
+    out[w].ptr.assign(1, 0);
+    out[w].src.clear();
+    out[w].target.clear();
+  }
+  for (int t = 0; t < ntargets_total; t++) {
+    if (!keep[t]) continue;
+    long long b = cnt[t], e = cnt[(size_t) t + 1];
+    GatherList& gl = out[(e - b) > LARGE_FANIN ? 1 : 0];
+    gl.src.insert(gl.src.end(), sorted.begin() + b, sorted.begin() + e);
+    gl.ptr.push_back((long long) gl.src.size());
+    gl.target.push_back(out_index[t]);
+  }
+}
+
+}  // namespace
+
+void Problem::analyze() {
+  const int PV = nvars, SV = niq, EC = neq, IC = niq;
+  kktdim = PV + SV + EC + IC;
+  const int eqoffset = PV + SV, iqoffset = PV + SV + EC;
+
+  // evaluation order: objectives, equalities, inequalities (Threads = 1 order of getMATSpace)
+  order.clear();
+  for (int role = 0; role < 3; role++)
+    for (int i = 0; i < (int) funcs.size(); i++)
+      if (funcs[i].role == role) order.push_back(i);
+
+  trip_base.assign(funcs.size(), 0);
+  fdest_base.assign(funcs.size(), 0);
+  n_user = 0;
+  long long nf = 0;
+  for (int fi: order) {
+    FuncRec& fn = funcs[fi];
+    if ((long long) fn.vindex.size() != (long long) fn.nappl * fn.ir) throw std::invalid_argument("analyze: bad vindex size in " + fn.name);
+    if (fn.role != 0 && (long long) fn.cindex.size() != (long long) fn.nappl * fn.orows)
+      throw std::invalid_argument("analyze: bad cindex size in " + fn.name);
+    for (int v: fn.vindex)
+      if (v < 0 || v >= PV) throw std::out_of_range("analyze: variable index out of range in " + fn.name);
+    const int nc = (fn.role == 1) ? EC : IC;
+    if (fn.role != 0)
+      for (int c: fn.cindex)
+        if (c < 0 || c >= nc) throw std::out_of_range("analyze: constraint index out of range in " + fn.name);
+    trip_base[fi] = n_user;
+    n_user += (long long) fn.nappl * fn.triplets_per_app();
+    fdest_base[fi] = nf;
+    if (fn.role != 0) nf += (long long) fn.nappl * fn.orows;
+  }
+  n_solver = (long long) SV + PV + SV + EC + IC;
+  const long long T = n_user + n_solver;
+  if (T >= (1ll << 31)) throw std::length_error("analyze: more than 2^31 KKT triplets");
+
+  auto conoff = [&](const FuncRec& fn) { return fn.role == 1 ? eqoffset : (fn.role == 2 ? iqoffset : 0); };
+  // solver-owned entries in the reference's storage order (NonLinearProgram.cpp:198-265)
+  auto for_each_solver = [&](auto&& cb) {
+    for (int i = 0; i < SV; i++) cb(PV + SV + EC + i, PV + i);  // slack Jacobian ones
+    for (int i = 0; i < PV; i++) cb(i, i);                      // primal diagonal
+    for (int i = 0; i < SV; i++) cb(PV + i, PV + i);            // slack diagonal
+    for (int i = 0; i < EC; i++) cb(PV + SV + i, PV + SV + i);  // equality pivots
+    for (int i = 0; i < IC; i++) cb(PV + SV + EC + i, PV + SV + EC + i);
+  };
+
+  // pass 1: count per CSR row (upper triangle: row = min, col = max)
+  std::vector<long long> rowstart((size_t) kktdim + 1, 0);
+  auto count_cb = [&](int r, int c) { rowstart[(size_t) std::min(r, c) + 1]++; };
+  for (int fi: order) for_each_triplet(funcs[fi], conoff(funcs[fi]), count_cb);
+  for_each_solver(count_cb);
+  for (int i = 0; i < kktdim; i++) rowstart[(size_t) i + 1] += rowstart[i];
+  // pass 2: bucket the columns
+  std::vector<int> colbuf((size_t) T);
+  {
+    std::vector<long long> pos(rowstart.begin(), rowstart.end() - 1);
+    auto fill_cb = [&](int r, int c) { colbuf[(size_t) pos[std::min(r, c)]++] = std::max(r, c); };
+    for (int fi: order) for_each_triplet(funcs[fi], conoff(funcs[fi]), fill_cb);
+    for_each_solver(fill_cb);
+  }
+  // pass 3: sort + unique per row (parallel over rows)
+  std::vector<int> rowcnt(kktdim, 0);
+  {
+    unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; t++) {
+      th.emplace_back([&, t]() {
+        int lo = (int) ((long long) kktdim * t / nt), hi = (int) ((long long) kktdim * (t + 1) / nt);
+        for (int r = lo; r < hi; r++) {
+          int* b = colbuf.data() + rowstart[r];
+          int* e = colbuf.data() + rowstart[(size_t) r + 1];
+          std::sort(b, e);
+          rowcnt[r] = (int) (std::unique(b, e) - b);
+        }
+      });
+    }
+    for (auto& x: th) x.join();
+  }
+  long long nnz_ll = 0;
+  for (int r = 0; r < kktdim; r++) nnz_ll += rowcnt[r];
+  if (nnz_ll >= (1ll << 31)) throw std::length_error("analyze: CSR nnz exceeds int32");
+  indptr.assign((size_t) kktdim + 1, 0);
+  indices.resize((size_t) nnz_ll);
+  for (int r = 0; r < kktdim; r++) {
+    indptr[(size_t) r + 1] = indptr[r] + rowcnt[r];
+    std::copy(colbuf.begin() + rowstart[r], colbuf.begin() + rowstart[r] + rowcnt[r], indices.begin() + indptr[r]);
+  }
+  std::vector<int>().swap(colbuf);
+
+  // pass 4: KKTLocations (value-array offset of every triplet)
+  kktloc.resize((size_t) T);
+  {
+    long long k = 0;
+    auto loc_cb = [&](int r, int c) {
+      int rr = std::min(r, c), cc = std::max(r, c);
+      const int* b = indices.data() + indptr[rr];
+      const int* e = indices.data() + indptr[(size_t) rr + 1];
+      kktloc[(size_t) k++] = (int) (std::lower_bound(b, e, cc) - indices.data());
+    };
+    for (int fi: order) for_each_triplet(funcs[fi], conoff(funcs[fi]), loc_cb);
+    for_each_solver(loc_cb);
+  }
+
+  // pass 5: classify slots.  A slot written by exactly one user triplet and no solver entry is stored
+  // directly by the evaluating lane; everything else goes through the fixed-order gather.
+  const int nnz_i = (int) nnz_ll;
+  std::vector<unsigned char> nsrc((size_t) nnz_i, 0);  // saturating count
+  for (long long k = 0; k < T; k++) {
+    unsigned char& c = nsrc[(size_t) kktloc[(size_t) k]];
+    if (k >= n_user)
+      c = 2;
+    else if (c < 2)
+      c++;
+  }
+  kkt_dest.resize((size_t) n_user);
+  long long stage_pos = 0;
+  std::vector<int> tgt_of_src, stage_of_src;
+  for (long long k = 0; k < n_user; k++) {
+    int s = kktloc[(size_t) k];
+    if (nsrc[(size_t) s] == 1) {
+      kkt_dest[(size_t) k] = s;
+    } else {
+      kkt_dest[(size_t) k] = ~(int) stage_pos;
+      tgt_of_src.push_back(s);
+      stage_of_src.push_back((int) stage_pos);
+      stage_pos++;
+    }
+  }
+  stage_solver = stage_pos;
+  for (long long k = 0; k < n_solver; k++) {
+    tgt_of_src.push_back(kktloc[(size_t) (n_user + k)]);
+    stage_of_src.push_back((int) stage_pos);
+    stage_pos++;
+  }
+  {
+    std::vector<char> keep((size_t) nnz_i);
+    std::vector<int> outidx((size_t) nnz_i);
+    for (int s = 0; s < nnz_i; s++) {
+      keep[s] = nsrc[s] >= 2;
+      outidx[s] = s;
+    }
+    build_gather(tgt_of_src, stage_of_src, nnz_i, outidx, keep, g_kkt);
+  }
+
+  // gradients: every application writes its IR gradient entries to private stage slots (the
+  // reference's RHScoeffs, IndexingData.h:96-105), summed per variable in source order.
+  g_stage.assign(funcs.size(), -1);
+  v_stage.assign(funcs.size(), -1);
+  auto grad_gather = [&](int role_lo, int role_hi, GatherList out[2]) {
+    std::vector<int> tg, st;
+    for (int fi: order) {
+      FuncRec& fn = funcs[fi];
+      if (fn.role < role_lo || fn.role > role_hi) continue;
+      g_stage[fi] = stage_pos;
+      for (long long q = 0; q < (long long) fn.nappl * fn.ir; q++) {
+        tg.push_back(fn.vindex[(size_t) q]);
+        st.push_back((int) (stage_pos + q));
+      }
+      stage_pos += (long long) fn.nappl * fn.ir;
+    }
+    std::vector<char> keep((size_t) PV, 1);
+    std::vector<int> outidx((size_t) PV);
+    for (int i = 0; i < PV; i++) outidx[i] = i;
+    build_gather(tg, st, PV, outidx, keep, out);
+  };
+  grad_gather(0, 0, g_pgx);
+  grad_gather(1, 2, g_agx);
+
+  // objective value
+  {
+    std::vector<int> tg, st;
+    for (int fi: order) {
+      FuncRec& fn = funcs[fi];
+      if (fn.role != 0) continue;
+      v_stage[fi] = stage_pos;
+      for (int a = 0; a < fn.nappl; a++) {
+        tg.push_back(0);
+        st.push_back((int) (stage_pos + a));
+      }
+      stage_pos += fn.nappl;
+    }
+    std::vector<char> keep(1, 1);
+    std::vector<int> outidx(1, 0);
+    build_gather(tg, st, 1, outidx, keep, g_val);
+  }
+
+  // constraint values: unique rows are stored directly; accumulated rows are staged and summed
+  f_dest.assign((size_t) nf, 0);
+  for (int role = 1; role <= 2; role++) {
+    const int nc = (role == 1) ? EC : IC;
+    std::vector<int> users((size_t) nc, 0);
+    for (int fi: order)
+      if (funcs[fi].role == role)
+        for (int c: funcs[fi].cindex) users[(size_t) c]++;
+    std::vector<int> tg, st;
+    for (int fi: order) {
+      FuncRec& fn = funcs[fi];
+      if (fn.role != role) continue;
+      for (size_t q = 0; q < fn.cindex.size(); q++) {
+        int c = fn.cindex[q];
+        if (users[(size_t) c] == 1) {
+          f_dest[(size_t) fdest_base[fi] + q] = c;
+        } else {
+          f_dest[(size_t) fdest_base[fi] + q] = ~(int) stage_pos;
+          tg.push_back(c);
+          st.push_back((int) stage_pos);
+          stage_pos++;
+        }
+      }
+    }
+    std::vector<char> keep((size_t) nc);
+    std::vector<int> outidx((size_t) nc);
+    for (int c = 0; c < nc; c++) {
+      keep[c] = users[c] != 1;  // rows nobody writes are zero-filled by the gather
+      outidx[c] = c;
+    }
+    build_gather(tg, st, nc, outidx, keep, role == 1 ? g_fxe : g_fxi);
+  }
+  if (stage_pos >= (1ll << 31)) throw std::length_error("analyze: staging buffer exceeds int32");
+  stage_size = stage_pos;
+  analyzed = true;
+}
+
+}  // namespace ab

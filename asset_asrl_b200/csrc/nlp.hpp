@@ -1,0 +1,76 @@
+// Host-side NLP assembly: function list -> KKT triplets -> upper-triangular CSR pattern -> the
+// segment-to-CSR destination maps and fixed-order gather lists the kernels consume.
+//
+// Restates, without Eigen, what the reference does once per transcription in
+// NonLinearProgram::make_NLP / getMATSpace / analyzeSparsity
+// (/root/reference/src/Solvers/NonLinearProgram.cpp:25-39, :111-175, :198-265, :267-344) and
+// DenseFunctionBase::getKKTSpace (/root/reference/src/VectorFunctions/DenseFunctionBase.h:1097-1129).
+// The canonical triplet order is the reference's Threads=1 order.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "expr.hpp"
+
+namespace ab {
+
+struct FuncRec {
+  int role = 1;  // FnRole: 0 objective, 1 equality, 2 inequality
+  int tape = -1;
+  int ir = 0, orows = 0;
+  bool linear = false;
+  bool unique_constraints = true;  // false for accumulations (PhaseIndexer.cpp:41-76)
+  int nappl = 0;
+  int nappconst = 0;
+  std::vector<int> vindex;       // [nappl][ir]
+  std::vector<int> cindex;       // [nappl][orows]  (row within the eq / iq block)
+  std::vector<double> appconst;  // [nappl][nappconst]
+  std::string name;
+
+  int triplets_per_app() const {
+    int h = linear ? 0 : ir * (ir + 1) / 2;
+    int j = (role == 0) ? 0 : ir * orows;
+    return h + j;
+  }
+};
+
+struct GatherList {
+  std::vector<long long> ptr;  // ntargets + 1
+  std::vector<int> src;        // indices into the staging buffer, ascending per target
+  std::vector<int> target;     // output index per target
+  int ntargets() const { return (int) target.size(); }
+};
+
+struct Problem {
+  std::vector<Tape> tapes;
+  std::vector<FuncRec> funcs;  // in user order; evaluation order is objectives, equalities, inequalities
+  int nvars = 0, neq = 0, niq = 0;
+
+  // ---- filled by analyze() ----
+  int kktdim = 0;
+  long long n_user = 0;    // user triplets
+  long long n_solver = 0;  // solver-owned entries (slack ones, primal diag, slack diag, eq pivots, iq pivots)
+  std::vector<int> order;            // evaluation order of funcs
+  std::vector<long long> trip_base;  // per func (indexed like funcs): first user triplet
+  std::vector<long long> fdest_base; // per func: offset into f_dest
+  std::vector<int> indptr, indices;  // CSR (upper triangle, row-major), bit-exact vs analyzeSparsity
+  std::vector<int> kktloc;           // [n_user + n_solver] == reference KKTLocations
+  std::vector<int> kkt_dest;         // [n_user] >=0 direct CSR slot, <0 ~stage index
+  std::vector<int> f_dest;           // per constraint output
+  // staging layout
+  long long stage_size = 0;
+  long long stage_solver = 0;              // solver coefficients live at stage[stage_solver + i]
+  std::vector<long long> g_stage;          // per func
+  std::vector<long long> v_stage;          // per objective func (else -1)
+  // gather lists: [0] fan-in <= LARGE_FANIN, [1] the rest
+  GatherList g_kkt[2], g_pgx[2], g_agx[2], g_fxe[2], g_fxi[2], g_val[2];
+  bool analyzed = false;
+
+  void analyze();
+  long long nnz() const { return (long long) indices.size(); }
+};
+
+constexpr int LARGE_FANIN = 96;
+
+}  // namespace ab

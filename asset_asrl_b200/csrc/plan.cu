@@ -1,0 +1,195 @@
+#include "plan.hpp"
+
+#include <cstring>
+
+namespace ab {
+
+#define AB_CUDA(call)                                                        \
+  do {                                                                       \
+    cudaError_t e__ = (call);                                                \
+    if (e__ != cudaSuccess) {                                                \
+      last_error = std::string(#call) + ": " + cudaGetErrorString(e__);      \
+      return (int) e__;                                                      \
+    }                                                                        \
+  } while (0)
+
+template<class T>
+T* Plan::dalloc(size_t n) {
+  void* p = nullptr;
+  if (n == 0) n = 1;
+  if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+  owned.push_back(p);
+  return (T*) p;
+}
+template<class T>
+T* Plan::dupload(const std::vector<T>& v) {
+  T* p = dalloc<T>(v.size());
+  if (p && !v.empty()) {
+    if (cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+  }
+  return p;
+}
+
+Plan::~Plan() {
+  for (void* p: owned) cudaFree(p);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
+  for (int w = 0; w < 2; w++) {
+    dg.dev[w].ntargets = gl[w].ntargets();
+    long long* ptr = P.dupload(gl[w].ptr);
+    int* src = P.dupload(gl[w].src);
+    int* tgt = P.dupload(gl[w].target);
+    if (!ptr || !src || !tgt) return false;
+    dg.dev[w].ptr = ptr;
+    dg.dev[w].src = src;
+    dg.dev[w].target = tgt;
+  }
+  return true;
+}
+
+int Plan::build(int dev) {
+  if (!prob.analyzed) prob.analyze();
+  device = dev;
+  AB_CUDA(cudaSetDevice(dev));
+  AB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  // tapes
+  std::vector<Instr*> dtapes;
+  for (const Tape& t: prob.tapes) {
+    Instr* p = dupload(t.code);
+    if (!p) {
+      last_error = "cudaMalloc/cudaMemcpy failed for a tape";
+      return (int) cudaErrorMemoryAllocation;
+    }
+    dtapes.push_back(p);
+  }
+  int* d_kkt_dest = dupload(prob.kkt_dest);
+  int* d_f_dest = dupload(prob.f_dest);
+  if (!d_kkt_dest || !d_f_dest) {
+    last_error = "out of device memory for the destination maps";
+    return (int) cudaErrorMemoryAllocation;
+  }
+  fns.clear();
+  for (int fi: prob.order) {
+    const FuncRec& fr = prob.funcs[fi];
+    const Tape& t = prob.tapes.at(fr.tape);
+    if (t.nin != fr.ir || t.nout != fr.orows) {
+      last_error = "tape/function size mismatch in " + fr.name;
+      return (int) cudaErrorInvalidValue;
+    }
+    if (!fr.linear && !t.has_adjoint) {
+      last_error = "non-linear function " + fr.name + " has a tape without an adjoint section";
+      return (int) cudaErrorInvalidValue;
+    }
+    FnDev f;
+    std::memset(&f, 0, sizeof(f));
+    f.tape = dtapes[fr.tape];
+    f.n_primal = t.n_primal;
+    f.n_total = (int) t.code.size();
+    f.slots_primal = t.slots_primal;
+    f.slots_total = t.slots_total;
+    f.ir = fr.ir;
+    f.orows = fr.orows;
+    f.nappconst = fr.nappconst;
+    f.role = fr.role;
+    f.linear = fr.linear ? 1 : 0;
+    f.app_begin = 0;
+    f.app_end = fr.nappl;
+    f.E = fr.triplets_per_app();
+    f.vindex = dupload(fr.vindex);
+    f.cindex = dupload(fr.cindex);
+    f.appconst = dupload(fr.appconst);
+    if (!f.vindex || !f.cindex || !f.appconst) {
+      last_error = "out of device memory for index maps of " + fr.name;
+      return (int) cudaErrorMemoryAllocation;
+    }
+    f.kkt_dest = d_kkt_dest + prob.trip_base[fi];
+    f.f_dest = d_f_dest + prob.fdest_base[fi];
+    f.g_stage = prob.g_stage[fi];
+    f.v_stage = prob.v_stage[fi];
+    fns.push_back(f);
+  }
+  d_X = dalloc<double>(prob.nvars);
+  d_LE = dalloc<double>(prob.neq);
+  d_LI = dalloc<double>(prob.niq);
+  d_kkt = dalloc<double>((size_t) prob.nnz());
+  d_fxe = dalloc<double>(prob.neq);
+  d_fxi = dalloc<double>(prob.niq);
+  d_pgx = dalloc<double>(prob.nvars);
+  d_agx = dalloc<double>(prob.nvars);
+  d_val = dalloc<double>(1);
+  d_stage = dalloc<double>((size_t) prob.stage_size);
+  if (!d_X || !d_LE || !d_LI || !d_kkt || !d_fxe || !d_fxi || !d_pgx || !d_agx || !d_val || !d_stage) {
+    last_error = "out of device memory for the value arrays";
+    return (int) cudaErrorMemoryAllocation;
+  }
+  AB_CUDA(cudaMemset(d_stage, 0, sizeof(double) * (size_t) std::max<long long>(prob.stage_size, 1)));
+  AB_CUDA(cudaMemset(d_kkt, 0, sizeof(double) * (size_t) std::max<long long>(prob.nnz(), 1)));
+  if (!up_gather(*this, prob.g_kkt, gk) || !up_gather(*this, prob.g_pgx, gp) || !up_gather(*this, prob.g_agx, ga)
+      || !up_gather(*this, prob.g_fxe, ge) || !up_gather(*this, prob.g_fxi, gi) || !up_gather(*this, prob.g_val, gv)) {
+    last_error = "out of device memory for the gather lists";
+    return (int) cudaErrorMemoryAllocation;
+  }
+  AB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int Plan::set_solver_coeffs(const double* host) {
+  AB_CUDA(cudaSetDevice(device));
+  AB_CUDA(cudaMemcpyAsync(d_stage + prob.stage_solver, host, sizeof(double) * (size_t) prob.n_solver,
+                          cudaMemcpyHostToDevice, stream));
+  AB_CUDA(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+int Plan::eval(int mode, double obj_scale) {
+  AB_CUDA(cudaSetDevice(device));
+  int obj_mode = -1, con_mode = -1;
+  bool out_kkt = false, out_pgx = false, out_agx = false, out_fx = false, out_val = false;
+  switch (mode) {
+    case EM_KKT: obj_mode = FM_ALL; con_mode = FM_ALL; out_kkt = out_pgx = out_agx = out_fx = out_val = true; break;
+    case EM_KKTNO: con_mode = FM_ALL; out_kkt = out_agx = out_fx = true; break;
+    case EM_SOE: con_mode = FM_JAC; out_kkt = out_fx = true; break;
+    case EM_AUG: obj_mode = FM_GRAD; con_mode = FM_JAC_GRAD; out_kkt = out_pgx = out_agx = out_fx = out_val = true; break;
+    case EM_RHS: obj_mode = FM_GRAD; con_mode = FM_GRAD; out_pgx = out_agx = out_fx = out_val = true; break;
+    case EM_OGC: obj_mode = FM_GRAD; con_mode = FM_VALUES; out_pgx = out_fx = out_val = true; break;
+    case EM_OCC: obj_mode = FM_VALUES; con_mode = FM_VALUES; out_fx = out_val = true; break;
+    case EM_OBJ: obj_mode = FM_VALUES; out_val = true; break;
+    default: last_error = "unknown eval mode"; return (int) cudaErrorInvalidValue;
+  }
+  launches = 0;
+  if (out_kkt && mode != EM_KKT) {
+    // partial matrix modes: entries this mode does not compute must read as zero
+    AB_CUDA(cudaMemsetAsync(d_kkt, 0, sizeof(double) * (size_t) prob.nnz(), stream));
+    AB_CUDA(cudaMemsetAsync(d_stage, 0, sizeof(double) * (size_t) prob.stage_solver, stream));
+  }
+  for (const FnDev& f: fns) {
+    int fm = (f.role == ROLE_OBJ) ? obj_mode : con_mode;
+    if (fm < 0) continue;
+    EvalIO io;
+    io.X = d_X;
+    io.L = (f.role == ROLE_EQ) ? d_LE : d_LI;
+    io.obj_scale = obj_scale;
+    io.kkt = d_kkt;
+    io.fx = (f.role == ROLE_EQ) ? d_fxe : d_fxi;
+    io.stage = d_stage;
+    AB_CUDA(launch_eval(f, io, fm, stream));
+    launches++;
+  }
+  auto G = [&](DevGather& g, double* out) -> cudaError_t {
+    launches += (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);
+    return launch_gather(g.dev[0], g.dev[1], d_stage, out, stream);
+  };
+  if (out_kkt) AB_CUDA(G(gk, d_kkt));
+  if (out_pgx) AB_CUDA(G(gp, d_pgx));
+  if (out_agx) AB_CUDA(G(ga, d_agx));
+  if (out_fx) {
+    AB_CUDA(G(ge, d_fxe));
+    AB_CUDA(G(gi, d_fxi));
+  }
+  if (out_val) AB_CUDA(G(gv, d_val));
+  return 0;
+}
+
+}  // namespace ab

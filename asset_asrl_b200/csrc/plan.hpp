@@ -1,0 +1,60 @@
+// Device-resident evaluation plan: owns the index maps, tapes and value arrays on one GPU and runs the
+// eight NonLinearProgram::eval* modes (/root/reference/src/Solvers/NonLinearProgram.h:411-478).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "device_types.h"
+#include "nlp.hpp"
+
+namespace ab {
+
+enum EvalMode : int {
+  EM_KKT = 0,    // evalKKT   NonLinearProgram.cpp:473-537
+  EM_KKTNO = 1,  // evalKKTNO :540-583  (no objective)
+  EM_SOE = 2,    // evalSOE   :585-617  (constraints + Jacobian)
+  EM_AUG = 3,    // evalAUG   :618-666
+  EM_RHS = 4,    // evalRHS   :347-382
+  EM_OGC = 5,    // evalOGC   :384-415
+  EM_OCC = 6,    // evalOCC   :417-445
+  EM_OBJ = 7     // evalOBJ   :447-466
+};
+
+struct DevGather {
+  GatherDev dev[2];
+  void* bufs[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+struct Plan {
+  Problem prob;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string last_error;
+
+  std::vector<FnDev> fns;  // in evaluation order
+  std::vector<void*> owned;  // every device allocation, freed in the destructor
+
+  double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;
+  double *d_kkt = nullptr, *d_fxe = nullptr, *d_fxi = nullptr, *d_pgx = nullptr, *d_agx = nullptr, *d_val = nullptr;
+  double* d_stage = nullptr;
+  DevGather gk, gp, ga, ge, gi, gv;
+  long long launches = 0;  // kernels launched by the last eval
+
+  ~Plan();
+  int build(int device);  // upload everything; returns 0 or a cudaError
+  int eval(int mode, double obj_scale);
+  int set_solver_coeffs(const double* host_coeffs);
+
+  template<class T>
+  T* dalloc(size_t n);
+  template<class T>
+  T* dupload(const std::vector<T>& v);
+};
+
+cudaError_t launch_eval(const FnDev& f, const EvalIO& io, int mode, cudaStream_t st);
+cudaError_t launch_gather(const GatherDev& small, const GatherDev& large, const double* stage, double* out,
+                          cudaStream_t st);
+
+}  // namespace ab

@@ -1,0 +1,119 @@
+/*
+ * asset_b200.h -- C ABI of the B200-native KKT evaluation path for ASSET-style collocation NLPs.
+ *
+ * Plain pointers and sizes only; every function returns 0 on success or a non-zero status
+ * (CUDA error code for device failures, AB_ERR_* otherwise) and never throws across the boundary.
+ * ab_last_error() returns the message of the last failure on the calling thread.
+ *
+ * Reference interfaces each group replaces (paths relative to the reference tree):
+ *   ab_graph_*    the expression types behind vf.Arguments / VectorFunction
+ *                 (src/VectorFunctions/VectorFunctionTypeErasure/GenericFunction.h:87-405,
+ *                  src/VectorFunctions/CommonFunctions/ headers) -- recorded as a DAG, lowered to a tape.
+ *   ab_phase_*    ODEPhase transcription: PhaseIndexer (src/OptimalControl/PhaseIndexer.h:63-99,
+ *                 PhaseIndexer.cpp:132-410) and transcribe_phase (ODEPhaseBase.cpp:1364-1381).
+ *   ab_problem_*  NonLinearProgram set-up: make_NLP / getMATSpace / analyzeSparsity
+ *                 (src/Solvers/NonLinearProgram.cpp:25-39, :111-175, :267-344).
+ *   ab_plan_*     the eight NonLinearProgram::eval* entry points PSIOPT calls
+ *                 (src/Solvers/NonLinearProgram.h:411-478; PSIOPT.h:640-726), i.e. the per-function
+ *                 SolverConstraintSpec / SolverObjectiveSpec methods
+ *                 (src/VectorFunctions/VectorFunctionTypeErasure/SolverInterfaceSpecs.h:41-92, :254-277)
+ *                 fused into device launches.
+ */
+#ifndef ASSET_B200_H
+#define ASSET_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ab_graph ab_graph;
+typedef struct ab_phase ab_phase;
+typedef struct ab_problem ab_problem;
+typedef struct ab_plan ab_plan;
+
+enum { AB_OK = 0, AB_ERR_INVALID = -1, AB_ERR_RUNTIME = -2, AB_ERR_NO_DEVICE = -3 };
+
+/* eval modes == NonLinearProgram::evalKKT / KKTNO / SOE / AUG / RHS / OGC / OCC / OBJ */
+enum { AB_EVAL_KKT = 0, AB_EVAL_KKTNO = 1, AB_EVAL_SOE = 2, AB_EVAL_AUG = 3, AB_EVAL_RHS = 4, AB_EVAL_OGC = 5, AB_EVAL_OCC = 6, AB_EVAL_OBJ = 7 };
+/* function roles */
+enum { AB_ROLE_OBJECTIVE = 0, AB_ROLE_EQUALITY = 1, AB_ROLE_INEQUALITY = 2, AB_ROLE_INTEGRAL_OBJECTIVE = 3, AB_ROLE_INTEGRAL_PARAM = 4 };
+/* device pointers handed to a device-resident consumer */
+enum { AB_PTR_X = 0, AB_PTR_LE = 1, AB_PTR_LI = 2, AB_PTR_KKT = 3, AB_PTR_FXE = 4, AB_PTR_FXI = 5, AB_PTR_PGX = 6, AB_PTR_AGX = 7, AB_PTR_VAL = 8 };
+
+const char* ab_last_error(void);
+int ab_version(void);
+int ab_device_count(void);
+
+/* ---------------- expression graph ---------------- */
+ab_graph* ab_graph_create(void);
+void ab_graph_destroy(ab_graph* g);
+/* Adds a node and returns its id (>= 0) or a negative status.  `kind` is an ab::VKind; `tlin` = -1 lets the
+ * library derive the type-level linearity from the reference's rule table, `raw` = 1 marks a value that is
+ * not wrapped in a GenericFunction (Arguments / Segment / Element or a C++-built helper). */
+int ab_graph_node(ab_graph* g, int kind, int ir, int orows, const int* children, int nchildren, const double* dparams,
+                  int ndparams, const int* iparams, int niparams, int tlin, int raw);
+int ab_graph_node_info(const ab_graph* g, int node, int* ir, int* orows, int* tlin, int* raw);
+/* Writes an s-expression description of `node`; returns the full length (call again with a larger buffer). */
+long long ab_graph_describe(const ab_graph* g, int node, char* buf, long long cap);
+
+/* ---------------- problem: tapes + function list + sparsity ---------------- */
+ab_problem* ab_problem_create(int nvars, int neq, int niq);
+void ab_problem_destroy(ab_problem* p);
+int ab_problem_set_dims(ab_problem* p, int nvars, int neq, int niq);
+/* Lowers an expression to a device tape; returns the tape id. */
+int ab_problem_add_tape(ab_problem* p, const ab_graph* g, int node, int with_adjoint);
+/* Adds a function = (tape, Vindex, Cindex); vindex is [nappl][ir], cindex [nappl][orows] (ignored for objectives),
+ * appconst [nappl][nappconst] or NULL.  Returns the function id. */
+int ab_problem_add_function(ab_problem* p, int role, int tape, int linear, int unique_constraints, int nappl,
+                            const int* vindex, const int* cindex, const double* appconst);
+int ab_problem_analyze(ab_problem* p);
+/* out[0..9] = nvars, neq, niq, kktdim, nnz, n_user_triplets, n_solver_entries, stage_size, nfunctions, ntapes */
+int ab_problem_dims(const ab_problem* p, long long out[10]);
+int ab_problem_pattern(const ab_problem* p, int* indptr, int* indices);
+/* KKTLocations of every triplet in canonical (Threads = 1) order: user triplets then solver-owned entries. */
+int ab_problem_kkt_locations(const ab_problem* p, int* out);
+/* out[0..7] = role, tape, ir, orows, linear, unique_constraints, nappl, nappconst */
+int ab_problem_function_info(const ab_problem* p, int f, int out[8]);
+int ab_problem_function_indices(const ab_problem* p, int f, int* vindex, int* cindex);
+/* out[0..7] = n_instr, n_primal, slots_primal, slots_total, nin, nout, nappconst, has_adjoint */
+int ab_problem_tape_info(const ab_problem* p, int t, int out[8]);
+/* copies n_instr 16-byte instructions (see asset_asrl_b200/csrc/tape.h) */
+int ab_problem_tape_code(const ab_problem* p, int t, void* out);
+
+/* ---------------- phase transcription ---------------- */
+ab_phase* ab_phase_create(ab_graph* g, int ode_node, int xv, int uv, int pv, int transcription_mode, int nsegments);
+void ab_phase_destroy(ab_phase* ph);
+int ab_phase_set_control_mode(ab_phase* ph, int mode);
+int ab_phase_set_integral_mode(ab_phase* ph, int mode);
+int ab_phase_set_static_params(ab_phase* ph, int n);
+int ab_phase_set_mesh(ab_phase* ph, int nbins, const double* bin_spacing /* nbins+1 */, const int* defs_per_bin);
+int ab_phase_add_function(ab_phase* ph, int role, int node, int region, const int* xtuv, int nxtuv, const int* opv, int nopv,
+                          const int* spv, int nspv, const int* ext, int next);
+int ab_phase_clear_functions(ab_phase* ph);
+/* out[0..7] = numPhaseVars, numStates, numDefects, cardinalStates, XtUVars, PVars, StaticPVars, blocked */
+int ab_phase_dims(ab_phase* ph, int out[8]);
+int ab_phase_state_spacing(ab_phase* ph, double* out /* numStates */);
+/* Appends the phase's functions to `p` with variable / equality / inequality offsets; out = {numPhaseVars, numEq, numIq}. */
+int ab_phase_transcribe(ab_phase* ph, ab_problem* p, int voff, int eoff, int ioff, int out[3]);
+/* PhaseIndexer::makeSolverInput (PhaseIndexer.cpp:412-445): traj is [numStates][XtUVars + PVars]. */
+int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_params, double* X);
+
+/* ---------------- device plan ---------------- */
+int ab_plan_create(const ab_problem* p, int device, ab_plan** out);
+void ab_plan_destroy(ab_plan* plan);
+int ab_plan_set_inputs(ab_plan* plan, const double* X, const double* LE, const double* LI); /* host -> device */
+int ab_plan_set_solver_coeffs(ab_plan* plan, const double* coeffs /* n_solver_entries */);
+int ab_plan_eval(ab_plan* plan, int mode, double obj_scale); /* asynchronous on the plan's stream */
+int ab_plan_sync(ab_plan* plan);
+int ab_plan_get_outputs(ab_plan* plan, double* val, double* pgx, double* agx, double* fxe, double* fxi, double* kkt_values);
+/* host buffers in, host buffers out: H2D + eval + D2H, the call the reference's NonLinearProgram::eval* maps to */
+int ab_plan_eval_host(ab_plan* plan, int mode, double obj_scale, const double* X, const double* LE, const double* LI,
+                      double* val, double* pgx, double* agx, double* fxe, double* fxi, double* kkt_values);
+void* ab_plan_device_ptr(ab_plan* plan, int which);
+void* ab_plan_stream(ab_plan* plan);
+long long ab_plan_launches(const ab_plan* plan);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

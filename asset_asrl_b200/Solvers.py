@@ -97,6 +97,13 @@ class NonLinearProgram:
                                                    Cc.ctypes.data_as(_lib._ip) if Cc.size else None))
         return V, Cc
 
+    def function_appconst(self, f):
+        fi = self.function_info(f)
+        out = np.zeros((fi["nappl"], fi["nappconst"]))
+        if out.size:
+            _lib.check(lib.ab_problem_function_appconst(self.h, f, _lib.dptr(out)))
+        return out
+
     def tape(self, t):
         out = (C.c_int * 8)()
         _lib.check(lib.ab_problem_tape_info(self.h, t, out))

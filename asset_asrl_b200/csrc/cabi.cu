@@ -249,6 +249,13 @@ int ab_problem_function_indices(const ab_problem* p, int f, int* vindex, int* ci
   return AB_OK;
   AB_CATCH
 }
+int ab_problem_function_appconst(const ab_problem* p, int f, double* out) {
+  AB_TRY
+  const FuncRec& fr = p->p.funcs.at(f);
+  if (!fr.appconst.empty()) std::memcpy(out, fr.appconst.data(), fr.appconst.size() * sizeof(double));
+  return AB_OK;
+  AB_CATCH
+}
 int ab_problem_tape_info(const ab_problem* p, int t, int out[8]) {
   AB_TRY
   const Tape& tp = p->p.tapes.at(t);

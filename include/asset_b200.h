@@ -75,6 +75,7 @@ int ab_problem_kkt_locations(const ab_problem* p, int* out);
 /* out[0..7] = role, tape, ir, orows, linear, unique_constraints, nappl, nappconst */
 int ab_problem_function_info(const ab_problem* p, int f, int out[8]);
 int ab_problem_function_indices(const ab_problem* p, int f, int* vindex, int* cindex);
+int ab_problem_function_appconst(const ab_problem* p, int f, double* out /* [nappl][nappconst] */);
 /* out[0..7] = n_instr, n_primal, slots_primal, slots_total, nin, nout, nappconst, has_adjoint */
 int ab_problem_tape_info(const ab_problem* p, int t, int out[8]);
 /* copies n_instr 16-byte instructions (see asset_asrl_b200/csrc/tape.h) */

@@ -115,6 +115,13 @@ class NonLinearProgram:
             _lib.check(lib.ab_problem_tape_code(self.h, t, code.ctypes.data_as(C.c_void_p)))
         return info, code
 
+    def tape_describe(self, t):
+        """Text form of what tape ``t`` was lowered from (introspection; the CPU oracle in tests/ rebuilds it)."""
+        n = _lib.check(lib.ab_problem_tape_describe(self.h, t, None, 0))
+        buf = C.create_string_buffer(n + 1)
+        _lib.check(lib.ab_problem_tape_describe(self.h, t, buf, n + 1))
+        return buf.value.decode()
+
     # ------------------------------------------------------------------ device
     def to_device(self, device=0):
         if self.plan:

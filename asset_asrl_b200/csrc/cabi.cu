@@ -162,6 +162,7 @@ int ab_problem_add_tape(ab_problem* p, const ab_graph* g, int node, int with_adj
   ScalarFn f = lower_function(g->g, node);
   if (with_adjoint) f.make_gradient();
   p->p.tapes.push_back(emit_tape(f, with_adjoint != 0));
+  p->p.tapes.back().desc = "expr " + g->g.describe(node);
   return (int) p->p.tapes.size() - 1;
   AB_CATCH
 }
@@ -269,6 +270,19 @@ int ab_problem_tape_info(const ab_problem* p, int t, int out[8]) {
   out[7] = tp.has_adjoint;
   return AB_OK;
   AB_CATCH
+}
+long long ab_problem_tape_describe(const ab_problem* p, int t, char* buf, long long cap) {
+  try {
+    const std::string& s = p->p.tapes.at(t).desc;
+    if (buf && cap > 0) {
+      long long n = std::min<long long>(cap - 1, (long long) s.size());
+      std::memcpy(buf, s.data(), (size_t) n);
+      buf[n] = 0;
+    }
+    return (long long) s.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
 }
 int ab_problem_tape_code(const ab_problem* p, int t, void* out) {
   AB_TRY

@@ -144,6 +144,9 @@ struct Tape {
   int slots_total = 0;    // slots for the whole tape
   int nin = 0, nout = 0, nappconst = 0;
   bool has_adjoint = false;
+  // what the tape was lowered from, as text: "expr <s-expression>" or a built-in transcription function with its
+  // sizes.  Introspection only (tests rebuild the same function in the CPU oracle from it).
+  std::string desc;
 };
 
 std::vector<int> lower(const Graph& g, int root, const std::vector<int>& in, SDag& dag);

@@ -255,9 +255,10 @@ std::vector<double> Phase::state_spacing() const {
 }
 
 namespace {
-int add_tape(Problem& prob, ScalarFn& f, bool linear) {
+int add_tape(Problem& prob, ScalarFn& f, bool linear, const std::string& desc) {
   if (!linear) f.make_gradient();
   prob.tapes.push_back(emit_tape(f, !linear));
+  prob.tapes.back().desc = desc;
   return (int) prob.tapes.size() - 1;
 }
 }  // namespace
@@ -305,7 +306,9 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
       f = blk ? make_trap_defect(*g, ode_root, XV, 0, UV + PV) : make_trap_defect(*g, ode_root, XV, UV, PV);
     else
       f = blk ? make_lgl_defect(*g, ode_root, CS, XV, 0, UV + PV) : make_lgl_defect(*g, ode_root, CS, XV, UV, PV);
-    int tp = add_tape(prob, f, false);
+    const std::string sizes = blk ? (std::to_string(CS) + " " + std::to_string(XV) + " 0 " + std::to_string(UV + PV))
+                                  : (std::to_string(CS) + " " + std::to_string(XV) + " " + std::to_string(UV) + " " + std::to_string(PV));
+    int tp = add_tape(prob, f, false, std::string(tmode == TM_TRAPEZOIDAL ? "trap_defect " : "lgl_defect ") + sizes + " " + g->describe(ode_root));
     add_fn(1, tp, false, blk ? R_BLOCKDEFECTPATH : R_DEFECTPATH, stateT, oparT, empty, "defect");
   }
   // (2) axis functions
@@ -313,7 +316,7 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
     std::vector<int> tloc {XV};
     if (tmode == TM_LGL7 || tmode == TM_LGL5) {
       ScalarFn f = make_lgl_mesh_spacing(CS);
-      int tp = add_tape(prob, f, false);
+      int tp = add_tape(prob, f, false, "lgl_mesh_spacing " + std::to_string(CS));
       add_fn(1, tp, false, R_DEFECTPATH, tloc, empty, empty, "lgl_mesh_spacing");
     }
     if (idx.numNodalStates - 2 > 0) {
@@ -340,7 +343,7 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
         start += defs_per_bin[b];
       }
       ScalarFn f = make_single_mesh_spacing();
-      int tp = add_tape(prob, f, true);
+      int tp = add_tape(prob, f, true, "single_mesh_spacing");
       FuncRec& fr = add_fn(1, tp, true, R_FRONTNODALBACKPATH, tloc, empty, empty, "single_mesh_spacing");
       for (int a = 0; a < fr.nappl; a++) fr.appconst[a] = cspace[(size_t) a + 1];
     }
@@ -352,10 +355,11 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
     std::vector<int> tu;
     for (int i = XV; i < idx.XtUV(); i++) tu.push_back(i);
     ScalarFn f = make_control_spline(CS, UV, order);
-    int tp = add_tape(prob, f, false);
+    int tp = add_tape(prob, f, false, "control_spline " + std::to_string(CS) + " " + std::to_string(UV) + " " + std::to_string(order));
     add_fn(1, tp, false, R_DEFECTPAIRWISEPATH, tu, empty, empty, "control_spline");
   }
   // (4) integrals
+  std::string integral_desc;
   auto integral_fn = [&](const StateFn& sf, int& region) {
     int xp = (int) sf.xtuv.size();
     int sop = (int) (sf.opv.size() + sf.spv.size());
@@ -365,6 +369,7 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
       ics = CS;
       region = R_DEFECTPATH;
     }
+    integral_desc = "lgl_integral " + std::to_string(ics) + " " + std::to_string(xp) + " " + std::to_string(sop) + " " + g->describe(sf.root);
     return make_lgl_integral(*g, sf.root, ics, xp, sop);
   };
   for (const StateFn& sf: integrals) {
@@ -374,7 +379,7 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
       region = (tmode == TM_LGL3 || tmode == TM_TRAPEZOIDAL) ? R_DEFECTPATH : R_PAIRWISEPATH;
     std::vector<int> xtrap = sf.xtuv;
     xtrap.push_back(XV);
-    int tp = add_tape(prob, f, false);
+    int tp = add_tape(prob, f, false, integral_desc);
     add_fn(0, tp, false, region, xtrap, sf.opv, sf.spv, "integral_objective");
   }
   for (const StateFn& sf: param_integrals) {
@@ -387,11 +392,11 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
     acc.nin = 1;
     acc.nout = 1;
     acc.outs.push_back(acc.dag.mulc(acc.dag.input(0), -1.0));
-    int tacc = add_tape(prob, acc, true);
+    int tacc = add_tape(prob, acc, true, "expr (scaled 1 1 1 [] [-1] (args 1 1 1 [] []))");
     FuncRec& fa = add_fn(1, tacc, true, R_PARAMS, empty, empty, sf.ext, "accumulation_param");
     fa.unique_constraints = false;
     const int row = fa.cindex[0];
-    int tp = add_tape(prob, f, false);
+    int tp = add_tape(prob, f, false, integral_desc);
     int save = idx.nextEq, saven = idx.numEq;
     FuncRec& fi = add_fn(1, tp, false, region, xtrap, sf.opv, sf.spv, "accumulation_integral");
     idx.nextEq = save;  // the integral claims no rows of its own
@@ -404,7 +409,7 @@ void Phase::transcribe(Problem& prob, int voff, int eoff, int ioff) {
     for (const StateFn& sf: fns) {
       ScalarFn f = lower_function(*g, sf.root);
       const bool lin = g->at(sf.root).tlin;
-      int tp = add_tape(prob, f, lin);
+      int tp = add_tape(prob, f, lin, "expr " + g->describe(sf.root));
       add_fn(role, tp, lin, sf.region, sf.xtuv, sf.opv, sf.spv, nm);
     }
   };

@@ -78,6 +78,9 @@ int ab_problem_function_indices(const ab_problem* p, int f, int* vindex, int* ci
 int ab_problem_function_appconst(const ab_problem* p, int f, double* out /* [nappl][nappconst] */);
 /* out[0..7] = n_instr, n_primal, slots_primal, slots_total, nin, nout, nappconst, has_adjoint */
 int ab_problem_tape_info(const ab_problem* p, int t, int out[8]);
+/* Text form of what tape `t` was lowered from ("expr <s-expression>" or a built-in transcription function with its
+ * sizes); returns the full length.  Introspection for tests: the CPU oracle rebuilds the function from it. */
+long long ab_problem_tape_describe(const ab_problem* p, int t, char* buf, long long cap);
 /* copies n_instr 16-byte instructions (see asset_asrl_b200/csrc/tape.h) */
 int ab_problem_tape_code(const ab_problem* p, int t, void* out);
 

@@ -196,6 +196,45 @@ class NonLinearProgram:
     def evalOBJ(self, ObjScale, X):
         return self._eval(EVAL_OBJ, ObjScale, X, None, None, {"val"})
 
+    # ------------------------------------------------------------------ device-resident interface
+    def set_inputs(self, X, LE, LI):
+        """Host -> device copy of the iterate (asynchronous on the plan's stream)."""
+        self._need_plan()
+        _lib.check0(lib.ab_plan_set_inputs(self.plan, _lib.dptr(X), _lib.dptr(LE), _lib.dptr(LI)))
+
+    def eval_device(self, mode, ObjScale):
+        """Launch one evaluation on the device-resident inputs (asynchronous); outputs stay on the device."""
+        _lib.check0(lib.ab_plan_eval(self.plan, mode, float(ObjScale)))
+
+    def sync(self):
+        _lib.check0(lib.ab_plan_sync(self.plan))
+
+    def stream(self):
+        return int(lib.ab_plan_stream(self.plan) or 0)
+
+    def eval_host(self, mode, ObjScale, X, LE, LI, val, PGX, AGX, FXE, FXI, KKT):
+        """H2D + eval + D2H into caller-owned (ideally pinned) float64 arrays; None skips an output."""
+        g = _lib.dptr
+        _lib.check0(lib.ab_plan_eval_host(self.plan, mode, float(ObjScale), g(X), g(LE), g(LI), g(val), g(PGX), g(AGX),
+                                          g(FXE), g(FXI), g(KKT)))
+
+    def profile(self, enable=True):
+        self._need_plan()
+        _lib.check0(lib.ab_plan_profile(self.plan, int(enable)))
+
+    def profile_times(self):
+        """[(label, ms)] per kernel launch group of the last eval (device time from CUDA events)."""
+        n = _lib.check(lib.ab_plan_profile_read(self.plan, None, 0))
+        buf = (C.c_float * max(n, 1))()
+        n = _lib.check(lib.ab_plan_profile_read(self.plan, buf, n))
+        out = []
+        for k in range(n):
+            ln = lib.ab_plan_profile_label(self.plan, k, None, 0)
+            sb = C.create_string_buffer(ln + 1)
+            lib.ab_plan_profile_label(self.plan, k, sb, ln + 1)
+            out.append((sb.value.decode(), float(buf[k])))
+        return out
+
     def launches(self):
         return int(lib.ab_plan_launches(self.plan)) if self.plan else 0
 

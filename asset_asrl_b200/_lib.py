@@ -76,6 +76,9 @@ SIGNATURES = {
     "ab_plan_sync": (_i, [_vp]),
     "ab_plan_get_outputs": (_i, [_vp, _dp, _dp, _dp, _dp, _dp, _dp]),
     "ab_plan_eval_host": (_i, [_vp, _i, _d, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "ab_plan_profile": (_i, [_vp, _i]),
+    "ab_plan_profile_read": (_i, [_vp, C.POINTER(C.c_float), _i]),
+    "ab_plan_profile_label": (_ll, [_vp, _i, _cp, _ll]),
     "ab_plan_device_ptr": (_vp, [_vp, _i]),
     "ab_plan_stream": (_vp, [_vp]),
     "ab_plan_launches": (_ll, [_vp]),

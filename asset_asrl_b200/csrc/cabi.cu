@@ -509,6 +509,25 @@ void* ab_plan_device_ptr(ab_plan* plan, int which) {
     default: return nullptr;
   }
 }
+int ab_plan_profile(ab_plan* plan, int enable) {
+  plan->plan.profiling = enable;
+  plan->plan.prof_labels.clear();
+  return AB_OK;
+}
+int ab_plan_profile_read(ab_plan* plan, float* ms, int cap) {
+  int n = plan->plan.profile_read(ms, cap);
+  return n;
+}
+long long ab_plan_profile_label(ab_plan* plan, int k, char* buf, long long cap) {
+  if (k < 0 || k >= (int) plan->plan.prof_labels.size()) return fail(AB_ERR_INVALID, "launch index out of range");
+  const std::string& s = plan->plan.prof_labels[k];
+  if (buf && cap > 0) {
+    long long n = std::min<long long>(cap - 1, (long long) s.size());
+    std::memcpy(buf, s.data(), (size_t) n);
+    buf[n] = 0;
+  }
+  return (long long) s.size();
+}
 void* ab_plan_stream(ab_plan* plan) { return (void*) plan->plan.stream; }
 long long ab_plan_launches(const ab_plan* plan) { return plan->plan.launches; }
 

@@ -31,6 +31,7 @@ T* Plan::dupload(const std::vector<T>& v) {
 }
 
 Plan::~Plan() {
+  for (cudaEvent_t e: prof_events) cudaEventDestroy(e);
   for (void* p: owned) cudaFree(p);
   if (stream) cudaStreamDestroy(stream);
 }
@@ -143,6 +144,31 @@ int Plan::set_solver_coeffs(const double* host) {
   return 0;
 }
 
+int Plan::prof_begin(const std::string& label) {
+  if (!profiling) return 0;
+  const size_t k = prof_labels.size();
+  while (prof_events.size() < 2 * (k + 1)) {
+    cudaEvent_t e;
+    AB_CUDA(cudaEventCreate(&e));
+    prof_events.push_back(e);
+  }
+  prof_labels.push_back(label);
+  AB_CUDA(cudaEventRecord(prof_events[2 * k], stream));
+  return 0;
+}
+int Plan::prof_end() {
+  if (!profiling) return 0;
+  AB_CUDA(cudaEventRecord(prof_events[2 * (prof_labels.size() - 1) + 1], stream));
+  return 0;
+}
+int Plan::profile_read(float* ms, int cap) {
+  AB_CUDA(cudaSetDevice(device));
+  AB_CUDA(cudaStreamSynchronize(stream));
+  const int n = (int) prof_labels.size();
+  for (int k = 0; k < n && k < cap; k++) AB_CUDA(cudaEventElapsedTime(&ms[k], prof_events[2 * k], prof_events[2 * k + 1]));
+  return n;
+}
+
 int Plan::eval(int mode, double obj_scale) {
   AB_CUDA(cudaSetDevice(device));
   int obj_mode = -1, con_mode = -1;
@@ -159,6 +185,7 @@ int Plan::eval(int mode, double obj_scale) {
     default: last_error = "unknown eval mode"; return (int) cudaErrorInvalidValue;
   }
   launches = 0;
+  if (profiling != 2) prof_labels.clear();
   if (out_kkt && mode != EM_KKT) {
     // partial matrix modes: entries this mode does not compute must read as zero
     AB_CUDA(cudaMemsetAsync(d_kkt, 0, sizeof(double) * (size_t) prob.nnz(), stream));
@@ -174,21 +201,25 @@ int Plan::eval(int mode, double obj_scale) {
     io.kkt = d_kkt;
     io.fx = (f.role == ROLE_EQ) ? d_fxe : d_fxi;
     io.stage = d_stage;
+    if (int rc = prof_begin(prob.funcs[prob.order[&f - fns.data()]].name)) return rc;
     AB_CUDA(launch_eval(f, io, fm, stream));
+    if (int rc = prof_end()) return rc;
     launches++;
   }
-  auto G = [&](DevGather& g, double* out) -> cudaError_t {
-    launches += (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);
-    return launch_gather(g.dev[0], g.dev[1], d_stage, out, stream);
+  auto G = [&](DevGather& g, double* out, const char* label) -> int {
+    const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);
+    if (n == 0) return 0;
+    if (int rc = prof_begin(label)) return rc;
+    AB_CUDA(launch_gather(g.dev[0], g.dev[1], d_stage, out, stream));
+    launches += n;
+    return prof_end();
   };
-  if (out_kkt) AB_CUDA(G(gk, d_kkt));
-  if (out_pgx) AB_CUDA(G(gp, d_pgx));
-  if (out_agx) AB_CUDA(G(ga, d_agx));
-  if (out_fx) {
-    AB_CUDA(G(ge, d_fxe));
-    AB_CUDA(G(gi, d_fxi));
-  }
-  if (out_val) AB_CUDA(G(gv, d_val));
+  int rc = 0;
+  if (out_kkt && (rc = G(gk, d_kkt, "gather:KKT"))) return rc;
+  if (out_pgx && (rc = G(gp, d_pgx, "gather:PGX"))) return rc;
+  if (out_agx && (rc = G(ga, d_agx, "gather:AGX"))) return rc;
+  if (out_fx && ((rc = G(ge, d_fxe, "gather:FXE")) || (rc = G(gi, d_fxi, "gather:FXI")))) return rc;
+  if (out_val && (rc = G(gv, d_val, "gather:val"))) return rc;
   return 0;
 }
 

@@ -41,6 +41,14 @@ struct Plan {
   double* d_stage = nullptr;
   DevGather gk, gp, ga, ge, gi, gv;
   long long launches = 0;  // kernels launched by the last eval
+  // optional per-launch device timing (cudaEvent pairs on `stream`), used by bench.py for the roofline of the
+  // dominant kernel; labels are "<function name>" for tape launches and "gather:<output>" for the reductions
+  int profiling = 0;  // 0 off, 1 keep the last eval's launches, 2 accumulate over evals until switched
+  std::vector<cudaEvent_t> prof_events;
+  std::vector<std::string> prof_labels;  // one per launch of the last eval
+  int prof_begin(const std::string& label);
+  int prof_end();
+  int profile_read(float* ms, int cap);  // synchronises the stream; returns the number of launches
 
   ~Plan();
   int build(int device);  // upload everything; returns 0 or a cudaError

@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""bench.py -- KKT evaluation throughput of the collocation NLP (constraints + Jacobian + Hessian + scatter).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one rank per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...  # the CPU evaluation (oracle port) on the host cores
+
+A step is one NonLinearProgram::evalKKT over every mesh segment of the workload phase.
+``value`` = segments/s with X, LE, LI resident in HBM when the timed region starts; ``e2e`` = the same through the
+C ABI's host-buffer call (H2D of X/LE/LI and D2H of every output inside the timed region).  The reference's own
+binary cannot be built in this image, so the CPU numbers come from oracle/ (kind "port").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "kkt_eval_segments_per_sec"
+UNIT = "segments/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ode", default="lowthrust", choices=["lowthrust", "vanderpol", "hypersens", "brachistochrone"])
+    ap.add_argument("--mode", default="LGL5", choices=["LGL3", "LGL5", "LGL7", "Trapezoidal"])
+    ap.add_argument("--segments", type=int, default=int(os.environ.get("AB_BENCH_SEGMENTS", 200000)),
+                    help="mesh segments per GPU (weak scaling: each rank owns a contiguous range of the phase)")
+    ap.add_argument("--cpu-segments", type=int, default=20000, help="segments of the bounded CPU sample")
+    ap.add_argument("--no-extras", action="store_true", help="defect constraints only (no bounds / integral objective)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return f"{a.ode}_{a.mode.lower()}" + ("_defect_only" if a.no_extras else "_example_functions")
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [ln.split(",") for (t, ln) in self.lines if t0 - 0.05 <= t <= t1 + 0.15] or [ln.split(",") for (_, ln) in self.lines]
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for k, nm in enumerate(names):
+                    if r[3 + k].strip().lower().startswith("active"):
+                        reasons.add(nm)
+            except (ValueError, IndexError):
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs
+def cpu_eval_rate(a, steps, warmup):
+    """Oracle (CPU port of the reference evaluation) on a bounded sample of the same workload, all host threads."""
+    import asset_asrl_b200  # noqa: F401  (problem set-up runs through the product's host code; no GPU call is made)
+    from asset_asrl_b200 import workloads as W
+    import oracle
+    nseg = min(a.cpu_segments, a.segments)
+    ph = W.make_phase(a.ode, a.mode, nseg, extras=not a.no_extras)
+    nlp = ph.transcribe()
+    X = ph.makeSolverInput()
+    LE, LI = W.multipliers(nlp)
+    orc = oracle.Oracle.from_problem(nlp)
+    threads = max(1, min(oracle.hardware_threads(), os.cpu_count() or 1))
+    times = []
+    for k in range(warmup + steps):
+        t0 = time.perf_counter()
+        orc.eval("KKT", 1.0, X, LE, LI, threads=threads)
+        dt = time.perf_counter() - t0
+        if k >= warmup:
+            times.append(dt)
+    t = float(np.mean(times))
+    return {"value": nseg / t, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{nseg} segments of {workload_name(a)} per step, {steps} timed evalKKT calls, "
+                      f"{threads} threads over contiguous application chunks; oracle/oracle.cpp (reference binary unbuildable here)",
+            "ms_per_step": t * 1e3}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(a.steps, 5)), max(1, min(a.warmup, 2))
+    cb = cpu_eval_rate(a, steps, warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "segments_per_step": min(a.cpu_segments, a.segments), "eval": "evalKKT"},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the KKT path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    import asset_asrl_b200  # noqa: F401
+    from asset_asrl_b200 import workloads as W
+    from asset_asrl_b200.Solvers import EVAL_KKT
+
+    t_setup = time.time()
+    ph = W.make_phase(a.ode, a.mode, a.segments, extras=not a.no_extras, seed=12345 + rank)
+    nlp = ph.transcribe()
+    d = nlp.dims()
+    X = ph.makeSolverInput()
+    LE, LI = W.multipliers(nlp, seed=67890 + rank)
+    nlp.to_device(local)
+    nlp.set_solver_coeffs(np.ones(d["n_solver"]))
+    t_setup = time.time() - t_setup
+    stream = torch.cuda.ExternalStream(nlp.stream(), device=local)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput
+    nlp.set_inputs(X, LE, LI)
+    nlp.sync()
+    for _ in range(a.warmup):
+        nlp.eval_device(EVAL_KKT, 1.0)
+    nlp.sync()
+    nlp.profile(2)  # accumulate per-launch event pairs over the timed region
+    clocks = ClockSampler(local)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    w0 = time.time()
+    e0.record(stream)
+    for _ in range(a.steps):
+        nlp.eval_device(EVAL_KKT, 1.0)
+    e1.record(stream)
+    nlp.sync()
+    barrier()
+    w1 = time.time()
+    ms_total = e0.elapsed_time(e1)
+    launches = nlp.launches() * a.steps
+    prof = nlp.profile_times()
+    nlp.profile(0)
+    clk = clocks.stop(w0, w1)
+    if world > 1:
+        t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / a.steps
+    value = world * a.segments / (ms_step * 1e-3)
+
+    # ---- per-kernel device time (CUDA events on the plan's stream, averaged over the timed region)
+    agg = {}
+    for label, ms in prof:
+        agg.setdefault(label, []).append(ms)
+    kernels = {k: float(np.mean(v)) for k, v in agg.items()}
+    dom = max(kernels, key=kernels.get)
+    ir, orr = None, None
+    for f in range(d["nfuncs"]):
+        fi = nlp.function_info(f)
+        if nlp.tape_describe(fi["tape"]).split(" ", 1)[0] in ("lgl_defect", "trap_defect"):
+            ir, orr = fi["ir"], fi["orows"]
+    cs = W.CARDINALS[a.mode]
+    n = (ir - 0) // cs
+    b_seg_defect = 8 * (2 * (cs - 1) * n + 2 * orr + orr * ir + ir * (ir + 1) // 2 - n * (n + 1) // 2)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    b_alg_eval = W.algorithmic_bytes(nlp)
+    if dom == "defect":
+        bytes_launch = b_seg_defect * a.segments
+    else:  # another kernel dominates: charge it the whole evaluation's algorithmic bytes (upper bound on its share)
+        bytes_launch = b_alg_eval
+    achieved = bytes_launch / (kernels[dom] * 1e-3) / 1e9
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        ent = tj.get(workload_name(a))
+        if ent and ent.get("kernel") == dom:
+            traffic = ent["dram_bytes_per_segment"] * a.segments
+    except (OSError, ValueError, KeyError):
+        pass
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "kernel_ms": kernels[dom], "kernel_share_of_step": kernels[dom] / ms_step,
+                "eval_algorithmic_bytes": b_alg_eval, "eval_frac": b_alg_eval / (ms_step * 1e-3) / 1e9 / peak}
+
+    # ---- end to end through the host-buffer C ABI call (pinned buffers)
+    e2e = None
+    if not a.no_e2e:
+        def pinned(nel):
+            return torch.empty(max(nel, 1), dtype=torch.float64).pin_memory().numpy()[:nel]
+        hX, hLE, hLI = pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"])
+        hX[:], hLE[:], hLI[:] = X, LE, LI
+        out = [pinned(1), pinned(d["nvars"]), pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"]), pinned(d["nnz"])]
+        ksteps = max(1, min(a.steps, 5))
+        for _ in range(2):
+            nlp.eval_host(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(ksteps):
+            nlp.eval_host(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
+        barrier()
+        dt = (time.perf_counter() - t0) / ksteps
+        if world > 1:
+            t = torch.tensor([dt], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * a.segments / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * (d["nvars"] + d["neq"] + d["niq"]),
+               "d2h_bytes_per_step": 8 * (1 + 2 * d["nvars"] + d["neq"] + d["niq"] + d["nnz"]), "ms_per_step": dt * 1e3,
+               "steps": ksteps, "note": "ab_plan_eval_host: pinned host X/LE/LI in, val/PGX/AGX/FXE/FXI/KKT values out"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu:
+        cb = cpu_eval_rate(a, 3, 1)
+        cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": workload_name(a), "segments_per_gpu": a.segments, "segments_total": world * a.segments,
+                           "eval": "evalKKT", "nvars": d["nvars"], "neq": d["neq"], "niq": d["niq"], "nnz": d["nnz"],
+                           "kkt_evals_per_sec": 1e3 / ms_step,
+                           "l2": f"no flush: per-eval working set {b_alg_eval / 1e6:.0f} MB of values (+ index maps) > 126 MB L2",
+                           "setup_s": round(t_setup, 2)},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
+                "kernels_ms": kernels}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -113,6 +113,11 @@ int ab_plan_get_outputs(ab_plan* plan, double* val, double* pgx, double* agx, do
 /* host buffers in, host buffers out: H2D + eval + D2H, the call the reference's NonLinearProgram::eval* maps to */
 int ab_plan_eval_host(ab_plan* plan, int mode, double obj_scale, const double* X, const double* LE, const double* LI,
                       double* val, double* pgx, double* agx, double* fxe, double* fxi, double* kkt_values);
+/* Per-launch device timing of the last eval (cudaEvent pairs on the plan's stream).  ab_plan_profile_read synchronises
+ * the stream, writes up to `cap` durations in ms and returns the number of launches (or a negative status). */
+int ab_plan_profile(ab_plan* plan, int enable); /* 0 off, 1 last eval only, 2 accumulate over evals */
+int ab_plan_profile_read(ab_plan* plan, float* ms, int cap);
+long long ab_plan_profile_label(ab_plan* plan, int k, char* buf, long long cap);
 void* ab_plan_device_ptr(ab_plan* plan, int which);
 void* ab_plan_stream(ab_plan* plan);
 long long ab_plan_launches(const ab_plan* plan);

@@ -1,0 +1,121 @@
+"""Shared builders for the test-suite: a zoo of expressions and of small phases covering every region flag, transcription
+and control mode the hot path supports.  Test-only."""
+import numpy as np
+
+import asset_asrl_b200 as ast
+from asset_asrl_b200 import workloads as W
+
+vf, oc = ast.VectorFunctions, ast.OptimalControl
+
+TOL = 1e-12  # BASELINE.json north_star: 1e-12 relative (fp64) for constraint, Jacobian and Hessian values
+
+
+def rel_err(a, b):
+    """|a-b|_inf relative to the block norm |b|_inf (cancellation in Hessian entries needs a
+    relative-to-block-norm comparison)."""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    if b.size == 0:
+        return 0.0
+    return float(np.abs(a - b).max()) / max(float(np.abs(b).max()), 1e-300)
+
+
+def expression_zoo():
+    """(name, function, sample point generator) over the op table of SURVEY.md section 8a row a16."""
+    A = vf.Arguments
+    z = []
+    x3 = A(3)
+    x4 = A(4)
+    x6 = A(6)
+    pos = lambda n: (lambda rng: rng.uniform(0.5, 1.5, n))  # noqa: E731
+    sym = lambda n: (lambda rng: rng.uniform(-0.9, 0.9, n))  # noqa: E731
+    for nm in ("sin", "cos", "tan", "arcsin", "arccos", "arctan", "sinh", "cosh", "tanh", "arcsinh", "arctanh", "exp", "squared"):
+        z.append((nm, getattr(vf, nm)(x3[0] * x3[1] + x3[2] * 0.3), sym(3)))
+    for nm in ("sqrt", "log", "arccosh"):
+        z.append((nm, getattr(vf, nm)(x3[0] * x3[1] + x3[2] + 1.0), pos(3)))
+    z.append(("abs_sign", vf.stack([vf.abs(x3[0] * x3[1]), vf.sign(x3[2]) * x3[0]]), sym(3)))
+    z.append(("pow", vf.stack([x3[0] ** 3, x3[1] ** 2.5, x3[2] ** -1.5, (x3[0] * x3[1]) ** 0.5]), pos(3)))
+    z.append(("inverse", (x3[0] * x3[1] + x3[2]).inverse(), pos(3)))
+    z.append(("norms", vf.stack([x4.norm(), x4.squared_norm(), x4.cubed_norm(), x4.inverse_norm(), x4.inverse_squared_norm(),
+                                 x4.inverse_cubed_norm(), x4.inverse_four_norm()]), pos(4)))
+    z.append(("normalized", vf.stack([x3.normalized(), x3.normalized_power2(), x3.normalized_power3(), x3.normalized_power4(),
+                                      x3.normalized_power5()]), pos(3)))
+    z.append(("dot_cross", vf.stack([x6.head3().dot(x6.tail3()), x6.head3().cross(x6.tail3())]), sym(6)))
+    z.append(("cwise", vf.stack([x6.head3().cwiseProduct(x6.tail3()), x6.head3().cwiseQuotient(x6.tail3())]), pos(6)))
+    z.append(("vec_scalar", vf.stack([x4.head3() * x4[3], x4.head3() / x4[3], x4[3] / x4[0]]), pos(4)))
+    z.append(("arctan2", vf.arctan2(x3[0] * x3[2], x3[1] + x3[2]), pos(3)))
+    z.append(("sum_diff", vf.sum([x6.head3(), x6.tail3(), x6.segment(1, 3)]) - x6.segment(2, 3) * 2.0 + np.array([1.0, 2.0, 3.0]), sym(6)))
+    z.append(("nested", vf.Arguments(2).normalized_power3().eval(vf.stack([x3[0] * x3[1], x3[2] + 2.0])), pos(3)))
+    z.append(("ifelse", vf.ifelse(x3[0] < x3[1], x3[0] * x3[2], vf.sin(x3[1]) * x3[2]), sym(3)))
+    z.append(("ifelse_and_or", vf.ifelse(((x3[0] < x3[1]) & (x3[1] <= x3[2])) | (x3[2] > 0.5), x3.norm(), x3.squared_norm() * 2.0), sym(3)))
+    z.append(("matmul", vf.matmul(np.arange(6.0).reshape(2, 3) - 2.0, vf.sin(x3)), sym(3)))
+    z.append(("ioscaled", vf.ioscaled(x3.normalized_power3(), [2.0, 0.5, 3.0], [0.1, 10.0, -2.0]), pos(3)))
+    z.append(("cwise_sum_elements", (vf.sin(x6).sum()) * x6[[0, 3, 5]].norm(), pos(6)))
+    z.append(("two_body", vf.stack([x6.tail3(), x6.head3().normalized_power3() * (-1.0)]), pos(6)))
+    return z
+
+
+def vdp_param_ode():
+    """VanDerPol with mu as an ODE parameter (PV = 1)."""
+    args = oc.ODEArguments(2, 1, 1)
+    x0, x1, u, mu = args.XVar(0), args.XVar(1), args.UVar(0), args.PVar(0)
+    return oc.ODEBase(vf.stack([x1, (1.0 - x0 * x0) * x1 * mu - x0 + u]), 2, 1, 1)
+
+
+def phase_zoo():
+    """name -> builder returning a phase; small meshes, every region flag / transcription / control mode."""
+    zoo = {}
+    for mode in ("LGL3", "LGL5", "LGL7", "Trapezoidal"):
+        zoo[f"lowthrust_{mode}"] = (lambda mode=mode: W.make_phase("lowthrust", mode, 7))
+        zoo[f"vanderpol_{mode}"] = (lambda mode=mode: W.make_phase("vanderpol", mode, 9))
+    zoo["hypersens_LGL5"] = lambda: W.make_phase("hypersens", "LGL5", 11)
+    zoo["brachistochrone_LGL3"] = lambda: W.make_phase("brachistochrone", "LGL3", 8)
+    zoo["lowthrust_LGL7_highest_order_spline"] = lambda: W.make_phase("lowthrust", "LGL7", 5, control_mode="HighestOrderSpline")
+    zoo["lowthrust_LGL5_block_constant"] = lambda: W.make_phase("lowthrust", "LGL5", 6, control_mode="BlockConstant")
+    zoo["lowthrust_LGL3_no_spline_defect_only"] = lambda: W.make_phase("lowthrust", "LGL3", 5, control_mode="NoSpline", extras=False)
+
+    def regions(mode="LGL5", control_mode=None, nseg=6):
+        rng = np.random.default_rng(7)
+        ode = vdp_param_ode()
+        S = (W.CARDINALS[mode] - 1) * nseg + 1
+        t = np.linspace(0.0, 2.0, S)
+        T = np.stack([np.cos(t), -np.sin(t), t, 0.1 * np.sin(2 * t), np.full(S, 0.8)], axis=1)
+        T[:, [0, 1, 3]] += 0.01 * rng.uniform(-1, 1, (S, 3))
+        ph = ode.phase(mode)
+        if control_mode:
+            ph.setControlMode(control_mode)
+        ph.setStaticParams([0.3, 1.7])
+        ph.setTraj(T, nseg)
+        A = vf.Arguments
+        ph.addBoundaryValue("Front", [0, 1, 2], T[0, :3])
+        ph.addEqualCon("Back", A(3).head2().squared_norm() - A(3)[2] * 0.1, [0, 1], [0], [])
+        ph.addEqualCon("FrontandBack", A(4)[0] * A(4)[2] - A(4)[1] * A(4)[3], [0, 1])
+        ph.addEqualCon("BackandFront", A(2)[0] - A(2)[1], [2])
+        ph.addInequalCon("Path", vf.sin(A(3)[0]) * A(3)[1] - A(3)[2], [0, 3], [], [1])
+        ph.addInequalCon("InnerPath", A(2).squared_norm() - 4.0, [0, 1])
+        ph.addInequalCon("NodalPath", A(2)[0] * A(2)[1] - 1.0, [1, 3])
+        ph.addInequalCon("PairWisePath", (A(4).head2() - A(4).tail2()).squared_norm() - 9.0, [0, 1])
+        ph.addEqualCon("StaticParams", A(2)[0] * A(2)[1] - 0.51, [], [], [0, 1])
+        ph.addEqualCon("ODEParams", vf.exp(A(1)[0]) - 2.2, [], [0], [])
+        ph.addLUVarBound("Path", 3, -1.0, 1.0, 2.0)
+        ph.addLUNormBound("Path", [0, 1], 0.01, 5.0)
+        ph.addIntegralObjective(A(2).squared_norm() * A(2)[0], [1, 3])
+        ph.addIntegralParamFunction(A(1)[0] * A(1)[0], [3], 1)
+        ph.addStateObjective("Back", A(2)[0] * A(2)[1], [0, 2])
+        ph.addDeltaTimeObjective(0.5)
+        ph.addValueObjective("Front", 1, -1.0)
+        return ph
+
+    for mode in ("LGL3", "LGL5", "LGL7", "Trapezoidal"):
+        zoo[f"regions_{mode}"] = (lambda mode=mode: regions(mode))
+    zoo["regions_LGL5_block_constant"] = lambda: regions("LGL5", "BlockConstant")
+    zoo["regions_LGL7_highest_order_spline"] = lambda: regions("LGL7", "HighestOrderSpline")
+    return zoo
+
+
+def problem_inputs(nlp, seed=3):
+    d = nlp.dims()
+    rng = np.random.default_rng(seed)
+    LE = 100.0 * rng.uniform(-1, 1, d["neq"])
+    LI = 100.0 * rng.uniform(-1, 1, d["niq"])
+    sc = rng.uniform(0.5, 1.5, d["n_solver"])
+    return LE, LI, sc

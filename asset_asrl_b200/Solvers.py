@@ -115,6 +115,21 @@ class NonLinearProgram:
             _lib.check(lib.ab_problem_tape_code(self.h, t, code.ctypes.data_as(C.c_void_p)))
         return info, code
 
+    def program_stats(self, f, mode=4):
+        """Size of the device program of function ``f`` in an evaluation mode (4 = values + Jacobian + Hessian)."""
+        out = (C.c_longlong * 8)()
+        _lib.check(lib.ab_problem_program_stats(self.h, f, mode, out))
+        return dict(zip(["ops", "fma", "special", "loads", "outs", "bundles", "slots", "consts"], [int(v) for v in out]))
+
+    def program(self, f, mode=4):
+        """(stats, code, consts) of the unlinked device program: code is a structured array of 16-byte instructions."""
+        st = self.program_stats(f, mode)
+        dt = np.dtype([("d", "<u4"), ("a", "<u4"), ("b", "<u4"), ("c", "<u4")])
+        code = np.zeros(4 * st["bundles"], dtype=dt)
+        consts = np.zeros(st["consts"])
+        _lib.check(lib.ab_problem_program_code(self.h, f, mode, code.ctypes.data_as(C.c_void_p), _lib.dptr(consts)))
+        return st, code, consts
+
     def tape_describe(self, t):
         """Text form of what tape ``t`` was lowered from (introspection; the CPU oracle in tests/ rebuilds it)."""
         n = _lib.check(lib.ab_problem_tape_describe(self.h, t, None, 0))

@@ -55,6 +55,8 @@ SIGNATURES = {
     "ab_problem_function_appconst": (_i, [_vp, _i, _dp]),
     "ab_problem_tape_info": (_i, [_vp, _i, _ip]),
     "ab_problem_tape_describe": (_ll, [_vp, _i, _cp, _ll]),
+    "ab_problem_program_stats": (_i, [_vp, _i, _i, _llp]),
+    "ab_problem_program_code": (_i, [_vp, _i, _i, _vp, _dp]),
     "ab_problem_tape_code": (_i, [_vp, _i, _vp]),
     "ab_phase_create": (_vp, [_vp, _i, _i, _i, _i, _i, _i]),
     "ab_phase_destroy": (None, [_vp]),

@@ -163,6 +163,7 @@ int ab_problem_add_tape(ab_problem* p, const ab_graph* g, int node, int with_adj
   if (with_adjoint) f.make_gradient();
   p->p.tapes.push_back(emit_tape(f, with_adjoint != 0));
   p->p.tapes.back().desc = "expr " + g->g.describe(node);
+  p->p.tapes.back().fn = std::make_shared<ScalarFn>(f);
   return (int) p->p.tapes.size() - 1;
   AB_CATCH
 }
@@ -283,6 +284,42 @@ long long ab_problem_tape_describe(const ab_problem* p, int t, char* buf, long l
   } catch (const std::exception& e) {
     return fail(AB_ERR_INVALID, e.what());
   }
+}
+static Program program_of(const ab_problem* p, int fidx, int mode) {
+  const FuncRec& fr = p->p.funcs.at(fidx);
+  const Tape& tp = p->p.tapes.at(fr.tape);
+  if (!tp.fn) throw std::invalid_argument("tape has no lowered function");
+  if (mode < 0 || mode > 4) throw std::invalid_argument("mode must be 0..4");
+  ProgramSpec sp;
+  sp.is_objective = fr.role == 0;
+  sp.linear = fr.linear;
+  sp.want_g = (mode == FM_GRAD || mode == FM_JAC_GRAD || mode == FM_ALL);
+  sp.want_j = (mode >= FM_JAC);
+  sp.want_h = (mode == FM_ALL);
+  ScalarFn copy = *tp.fn;
+  return emit_program(copy, sp);
+}
+int ab_problem_program_code(const ab_problem* p, int fidx, int mode, void* code, double* consts) {
+  AB_TRY
+  Program P = program_of(p, fidx, mode);
+  if (code) std::memcpy(code, P.code.data(), P.code.size() * sizeof(PInstr));
+  if (consts) std::memcpy(consts, P.consts.data(), P.consts.size() * sizeof(double));
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_program_stats(const ab_problem* p, int fidx, int mode, long long out[8]) {
+  AB_TRY
+  Program P = program_of(p, fidx, mode);
+  out[0] = P.n_ops;
+  out[1] = P.n_fma;
+  out[2] = P.n_special;
+  out[3] = P.n_load;
+  out[4] = P.n_out;
+  out[5] = P.bundles();
+  out[6] = P.nslots;
+  out[7] = (long long) P.consts.size();
+  return AB_OK;
+  AB_CATCH
 }
 int ab_problem_tape_code(const ab_problem* p, int t, void* out) {
   AB_TRY

@@ -1,6 +1,7 @@
 // Plain-old-data descriptors passed by value to the kernels (kernels.cu) by the plan (plan.cu).
 #pragma once
 #include <stdint.h>
+#include <vector_types.h>
 
 #include "tape.h"
 
@@ -18,13 +19,20 @@ enum FnMode : int {
   FM_ALL = 4        // constraints_jacobian_adjointgradient_adjointhessian() / objective_gradient_hessian()
 };
 
+// A linked device program (expr.hpp: Program) for one block size.
+struct ProgDev {
+  const uint4* code;     // 4 x 16-byte instructions per bundle
+  const double* consts;  // shared constants, copied to shared memory by the block
+  int nconst;
+  int nslots;            // lane-private 8-byte slots per thread
+  int nthreads;          // block size the operand offsets were linked for
+  int nbundles;
+  unsigned smem_bytes;
+};
+
 // One function (all its applications) as the device sees it.
 struct FnDev {
-  const Instr* tape;   // global memory copy of the tape
-  int n_primal;        // instructions of the primal section
-  int n_total;         // instructions of the whole tape
-  int slots_primal;
-  int slots_total;
+  ProgDev prog;        // program of the evaluation mode being launched
   int ir, orows;
   int nappconst;
   int role;            // FnRole

@@ -133,11 +133,15 @@ struct ScalarFn {
   SDag dag;
   std::vector<int> outs;   // nout scalar node ids
   std::vector<int> grads;  // nin scalar node ids (d(lambda.f)/dx_i), empty until make_gradient()
+  std::vector<int> jac;    // nout*nin node ids dF_k/dx_j (row-major), empty until make_second_order()
+  std::vector<int> hess;   // nin*nin node ids dg_i/dx_j (row-major; symmetric, the emitter uses j <= i)
   void make_gradient();
+  void make_second_order();  // deriv.cpp: symbolic sparse forward sweep over outs and grads
 };
 
 // Device tape + bookkeeping.
 struct Tape {
+  std::shared_ptr<ScalarFn> fn;  // the lowered function the device programs are generated from (plan build)
   std::vector<Instr> code;
   int n_primal = 0;       // instructions in the primal section (values + Jacobian)
   int slots_primal = 0;   // slots live in the primal section
@@ -148,6 +152,51 @@ struct Tape {
   // sizes.  Introspection only (tests rebuild the same function in the CPU oracle from it).
   std::string desc;
 };
+
+// ---------------------------------------------------------------------------------------------
+// Scalar program: what the device actually runs (program.cpp / kernels.cu).  One thread evaluates one function
+// application; the 32 lanes of a warp are 32 applications (mesh segments) executing the same instruction, so decode is
+// amortised over the warp and every value lives in a lane-private shared-memory slot.  Instructions are grouped in
+// bundles of four mutually independent operations of one kind (instruction-level parallelism for the interpreter).
+// ---------------------------------------------------------------------------------------------
+enum PKind : uint32_t { PK_FMA = 0, PK_LOAD = 1, PK_OUT = 2, PK_SPECIAL = 3, PK_END = 4 };
+enum POut : uint32_t { PO_F = 0, PO_J = 1, PO_G = 2, PO_H = 3 };
+enum PLoad : uint32_t { PL_X = 0, PL_LAMBDA = 1, PL_APPCONST = 2 };
+// Operand word: bit0 = 1 lane-private slot / 0 shared constant, bit1 = negate, bits[31:3] = index (unlinked) or
+// byte offset (linked for a block size).  The destination word of the first instruction of a bundle carries the
+// bundle kind in bits[31:28] and the number of live instructions in bits[27:24].
+struct PInstr {
+  uint32_t d, a, b, c;
+};
+static_assert(sizeof(PInstr) == 16, "PInstr must be 16 bytes");
+constexpr uint32_t P_SLOT = 1u, P_NEG = 2u;
+
+struct Program {
+  std::vector<PInstr> code;  // 4 instructions per bundle, PK_END bundle last
+  std::vector<double> consts;
+  int nslots = 0;
+  int nin = 0, nout = 0, nappconst = 0;
+  int n_ops = 0;       // live instructions (for reporting)
+  int n_fma = 0, n_special = 0, n_load = 0, n_out = 0;
+  int bundles() const { return (int) code.size() / 4; }
+};
+
+// what a program computes; mirrors FnMode in device_types.h
+struct ProgramSpec {
+  bool want_f = true, want_j = false, want_g = false, want_h = false;
+  bool is_objective = false;  // objectives scatter no Jacobian triplets
+  bool linear = false;        // type-level linear: no Hessian triplets exist
+};
+// Triplet offset of (row, col i) inside one application's block, DenseFunctionBase::getKKTSpace order.
+int triplet_offset_h(int i, int j, int ir, int orows, bool lay_h, bool lay_j);
+int triplet_offset_j(int i, int k, int ir, int orows, bool lay_h, bool lay_j);
+Program emit_program(ScalarFn& f, const ProgramSpec& spec);
+struct LinkedProgram {
+  std::vector<PInstr> code;
+  int nthreads = 0, nslots = 0;
+  unsigned smem_bytes = 0;
+};
+LinkedProgram link_program(const Program& P, unsigned smem_budget);
 
 std::vector<int> lower(const Graph& g, int root, const std::vector<int>& in, SDag& dag);
 ScalarFn lower_function(const Graph& g, int root);

@@ -259,6 +259,7 @@ int add_tape(Problem& prob, ScalarFn& f, bool linear, const std::string& desc) {
   if (!linear) f.make_gradient();
   prob.tapes.push_back(emit_tape(f, !linear));
   prob.tapes.back().desc = desc;
+  prob.tapes.back().fn = std::make_shared<ScalarFn>(f);
   return (int) prob.tapes.size() - 1;
 }
 }  // namespace

@@ -55,16 +55,6 @@ int Plan::build(int dev) {
   device = dev;
   AB_CUDA(cudaSetDevice(dev));
   AB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-  // tapes
-  std::vector<Instr*> dtapes;
-  for (const Tape& t: prob.tapes) {
-    Instr* p = dupload(t.code);
-    if (!p) {
-      last_error = "cudaMalloc/cudaMemcpy failed for a tape";
-      return (int) cudaErrorMemoryAllocation;
-    }
-    dtapes.push_back(p);
-  }
   int* d_kkt_dest = dupload(prob.kkt_dest);
   int* d_f_dest = dupload(prob.f_dest);
   if (!d_kkt_dest || !d_f_dest) {
@@ -72,24 +62,50 @@ int Plan::build(int dev) {
     return (int) cudaErrorMemoryAllocation;
   }
   fns.clear();
+  progs.clear();
   for (int fi: prob.order) {
     const FuncRec& fr = prob.funcs[fi];
     const Tape& t = prob.tapes.at(fr.tape);
-    if (t.nin != fr.ir || t.nout != fr.orows) {
+    if (t.nin != fr.ir || t.nout != fr.orows || !t.fn) {
       last_error = "tape/function size mismatch in " + fr.name;
-      return (int) cudaErrorInvalidValue;
-    }
-    if (!fr.linear && !t.has_adjoint) {
-      last_error = "non-linear function " + fr.name + " has a tape without an adjoint section";
       return (int) cudaErrorInvalidValue;
     }
     FnDev f;
     std::memset(&f, 0, sizeof(f));
-    f.tape = dtapes[fr.tape];
-    f.n_primal = t.n_primal;
-    f.n_total = (int) t.code.size();
-    f.slots_primal = t.slots_primal;
-    f.slots_total = t.slots_total;
+    // device programs: one per evaluation mode this role can be asked for
+    std::array<ProgDev, 5> pd;
+    std::memset(pd.data(), 0, sizeof(ProgDev) * 5);
+    try {
+      ScalarFn work = *t.fn;
+      for (int mode = 0; mode < 5; mode++) {
+        if (fr.role == ROLE_OBJ && (mode == FM_JAC || mode == FM_JAC_GRAD)) continue;
+        ProgramSpec sp;
+        sp.is_objective = fr.role == ROLE_OBJ;
+        sp.linear = fr.linear;
+        sp.want_g = (mode == FM_GRAD || mode == FM_JAC_GRAD || mode == FM_ALL);
+        sp.want_j = (mode >= FM_JAC);
+        sp.want_h = (mode == FM_ALL);
+        Program P = emit_program(work, sp);
+        LinkedProgram L = link_program(P, 220u * 1024u);
+        std::vector<uint4> code(L.code.size());
+        std::memcpy(code.data(), L.code.data(), L.code.size() * sizeof(PInstr));
+        pd[mode].code = dupload(code);
+        pd[mode].consts = dupload(P.consts);
+        if (!pd[mode].code || !pd[mode].consts) {
+          last_error = "out of device memory for the program of " + fr.name;
+          return (int) cudaErrorMemoryAllocation;
+        }
+        pd[mode].nconst = (int) P.consts.size();
+        pd[mode].nslots = L.nslots;
+        pd[mode].nthreads = L.nthreads;
+        pd[mode].nbundles = P.bundles();
+        pd[mode].smem_bytes = L.smem_bytes;
+      }
+    } catch (const std::exception& e) {
+      last_error = std::string(e.what()) + " (" + fr.name + ")";
+      return (int) cudaErrorInvalidValue;
+    }
+    progs.push_back(pd);
     f.ir = fr.ir;
     f.orows = fr.orows;
     f.nappconst = fr.nappconst;
@@ -202,7 +218,13 @@ int Plan::eval(int mode, double obj_scale) {
     io.fx = (f.role == ROLE_EQ) ? d_fxe : d_fxi;
     io.stage = d_stage;
     if (int rc = prof_begin(prob.funcs[prob.order[&f - fns.data()]].name)) return rc;
-    AB_CUDA(launch_eval(f, io, fm, stream));
+    FnDev fd = f;
+    fd.prog = progs[&f - fns.data()][fm];
+    if (fd.prog.nthreads == 0) {
+      last_error = "no device program for this mode";
+      return (int) cudaErrorInvalidValue;
+    }
+    AB_CUDA(launch_eval(fd, stream, io));
     if (int rc = prof_end()) return rc;
     launches++;
   }

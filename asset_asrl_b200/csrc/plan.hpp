@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <array>
 #include <string>
 #include <vector>
 
@@ -34,6 +35,7 @@ struct Plan {
   std::string last_error;
 
   std::vector<FnDev> fns;  // in evaluation order
+  std::vector<std::array<ProgDev, 5>> progs;  // per function, per FnMode (nthreads == 0: mode not generated)
   std::vector<void*> owned;  // every device allocation, freed in the destructor
 
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;
@@ -61,7 +63,7 @@ struct Plan {
   T* dupload(const std::vector<T>& v);
 };
 
-cudaError_t launch_eval(const FnDev& f, const EvalIO& io, int mode, cudaStream_t st);
+cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io);
 cudaError_t launch_gather(const GatherDev& small, const GatherDev& large, const double* stage, double* out,
                           cudaStream_t st);
 

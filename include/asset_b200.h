@@ -81,6 +81,11 @@ int ab_problem_tape_info(const ab_problem* p, int t, int out[8]);
 /* Text form of what tape `t` was lowered from ("expr <s-expression>" or a built-in transcription function with its
  * sizes); returns the full length.  Introspection for tests: the CPU oracle rebuilds the function from it. */
 long long ab_problem_tape_describe(const ab_problem* p, int t, char* buf, long long cap);
+/* Size of the device program of function `f` in an evaluation mode (0 values, 1 +gradient, 2 +Jacobian, 3 both, 4 all):
+ * out[0..7] = operations, fused multiply-adds, special ops, loads, output stores, bundles, lane-private slots, constants */
+int ab_problem_program_stats(const ab_problem* p, int f, int mode, long long out[8]);
+/* Copies the (unlinked) program: 4 * bundles 16-byte instructions (asset_asrl_b200/csrc/expr.hpp: PInstr) and the constants. */
+int ab_problem_program_code(const ab_problem* p, int f, int mode, void* code, double* consts);
 /* copies n_instr 16-byte instructions (see asset_asrl_b200/csrc/tape.h) */
 int ab_problem_tape_code(const ab_problem* p, int t, void* out);
 

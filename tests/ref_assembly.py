@@ -6,21 +6,22 @@ compared entry by entry.  Small problems only.
 """
 import numpy as np
 
-from tape_ref import run_tape
+from prog_ref import run_program, dense_blocks
 
 
 def tape_block_eval(nlp):
-    tapes = {}
+    """Per-application evaluator running the unlinked device program (mode 4 = values + Jacobian + gradient + Hessian)."""
+    progs = {}
 
     def ev(f, fi, x, lam, appc):
-        t = fi["tape"]
-        if t not in tapes:
-            tapes[t] = nlp.tape(t)
-        info, code = tapes[t]
-        fx, J, g, H = run_tape(info, code, x, lam, appc, full=not fi["linear"])
-        if H is None:
-            H = np.zeros((fi["ir"], fi["ir"]))
-        return fx, J, H
+        if f not in progs:
+            progs[f] = nlp.program(f, 4)
+        st, code, consts = progs[f]
+        F, G, T = run_program(st, code, consts, x, lam, appc)
+        fx, jx, gx, hx = dense_blocks(fi, F, G, T)
+        if fi["role"] == 0:  # objectives scatter no Jacobian triplets: recover the gradient row from G (= lam * df/dx)
+            jx = (gx / lam[0]).reshape(1, -1) if lam[0] != 0 else jx
+        return fx, jx, hx
 
     return ev
 

@@ -10,7 +10,7 @@ import pytest
 import oracle
 from helpers import expression_zoo, phase_zoo, problem_inputs, rel_err, TOL
 from ref_assembly import assemble
-from tape_ref import run_tape
+from prog_ref import run_program, dense_blocks
 from asset_asrl_b200.Solvers import NonLinearProgram
 
 GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "collocation_functions.json")))
@@ -20,14 +20,24 @@ ZOO = phase_zoo()
 @pytest.mark.parametrize("name,fun,gen", expression_zoo(), ids=[z[0] for z in expression_zoo()])
 def test_tape_matches_oracle(name, fun, gen):
     rng = np.random.default_rng(5)
-    nlp = NonLinearProgram()
+    ir, orr = fun.IRows(), fun.ORows()
+    nlp = NonLinearProgram(ir, orr, 0)
     t = nlp.add_tape(fun, True)
-    info, code = nlp.tape(t)
-    for _ in range(3):
-        x, lam = gen(rng), rng.uniform(-1, 1, fun.ORows())
-        f, J, g, H = run_tape(info, code, x, lam)
-        fx, jx, gx, hx = oracle.computeall("expr " + fun.describe(), x, lam)
-        assert rel_err(f, fx) < TOL and rel_err(J, jx) < TOL and rel_err(g, gx) < TOL and rel_err(H, hx) < TOL
+    nlp.add_function(1, t, False, np.arange(ir, dtype=np.int32).reshape(1, ir), np.arange(orr, dtype=np.int32).reshape(1, orr))
+    fi = nlp.function_info(0)
+    for mode in (4, 3, 1, 0):
+        st, code, consts = nlp.program(0, mode)
+        for _ in range(3):
+            x, lam = gen(rng), rng.uniform(-1, 1, orr)
+            f, J, g, H = dense_blocks(fi, *run_program(st, code, consts, x, lam))
+            fx, jx, gx, hx = oracle.computeall("expr " + fun.describe(), x, lam)
+            assert rel_err(f, fx) < TOL
+            if mode >= 3:
+                assert rel_err(J, jx) < TOL
+            if mode in (1, 3, 4):
+                assert rel_err(g, gx) < TOL
+            if mode == 4:
+                assert rel_err(H, hx) < TOL
 
 
 @pytest.mark.parametrize("name", sorted(ZOO), ids=sorted(ZOO))
@@ -68,8 +78,8 @@ def test_tape_matches_golden_defects():
         ph = ode.phase(c["mode"], T, 1)
         nlp = ph.transcribe()
         fi = nlp.function_info(0)
-        info, code = nlp.tape(fi["tape"])
-        f, J, g, H = run_tape(info, code, x, np.array(c["lam"]))
+        st, code, consts = nlp.program(0, 4)
+        f, J, g, H = dense_blocks(fi, *run_program(st, code, consts, x, np.array(c["lam"])))
         assert rel_err(f, c["fx"]) < TOL and rel_err(J, c["jx"]) < TOL and rel_err(H, c["hx"]) < TOL, c["name"]
 
 

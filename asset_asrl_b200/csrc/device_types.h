@@ -37,6 +37,8 @@ struct FnDev {
   int nappconst;
   int role;            // FnRole
   int linear;          // type-level linear: no Hessian triplets exist
+  int aff_begin;       // applications [aff_begin, aff_end) use the affine index maps linked into the program
+  int aff_end;
   int app_begin;       // first application evaluated by this device
   int app_end;         // one past the last
   int E;               // KKT triplets per application (depends on role / linear)

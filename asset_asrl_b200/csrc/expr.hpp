@@ -170,6 +170,8 @@ struct PInstr {
 };
 static_assert(sizeof(PInstr) == 16, "PInstr must be 16 bytes");
 constexpr uint32_t P_SLOT = 1u, P_NEG = 2u;
+// the block streams the program through two shared-memory buffers of this many bundles (cp.async double buffering)
+constexpr uint32_t PROG_CHUNK_BUNDLES = 64u;
 
 struct Program {
   std::vector<PInstr> code;  // 4 instructions per bundle, PK_END bundle last
@@ -196,7 +198,17 @@ struct LinkedProgram {
   int nthreads = 0, nslots = 0;
   unsigned smem_bytes = 0;
 };
-LinkedProgram link_program(const Program& P, unsigned smem_budget);
+// Affine index maps of one function over its bulk application range [a0, a1): for those applications every gather /
+// scatter index is base + (app - a0) * stride, so the kernel computes addresses instead of loading index arrays.
+// Applications outside the range (mesh ends) use the explicit maps.  |stride| < 2^23.
+struct AffineMaps {
+  int a0 = 0, a1 = 0;
+  std::vector<int> vbase, vstride;  // per input: global variable index
+  std::vector<int> cbase, cstride;  // per output: multiplier (constraint row) index; empty for objectives
+  std::vector<int> fbase, fstride;  // per output: f_dest (>= 0 direct, < 0 ~stage); empty for objectives
+  std::vector<int> kbase, kstride;  // per triplet: kkt_dest
+};
+LinkedProgram link_program(const Program& P, unsigned smem_budget, const AffineMaps* am = nullptr);
 
 std::vector<int> lower(const Graph& g, int root, const std::vector<int>& in, SDag& dag);
 ScalarFn lower_function(const Graph& g, int root);

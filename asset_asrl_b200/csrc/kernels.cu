@@ -74,6 +74,13 @@ __device__ __forceinline__ double special_op(unsigned op, double a, double b, do
   }
 }
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const unsigned d = (unsigned) __cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+
+// shared memory: [constants][2 x program chunk][lane-private slots]; operand offsets are linked against this layout
 __global__ void __launch_bounds__(256) k_eval_prog(const FnDev f, const EvalIO io) {
   extern __shared__ __align__(16) unsigned char smem[];
   const ProgDev& P = f.prog;
@@ -81,93 +88,119 @@ __global__ void __launch_bounds__(256) k_eval_prog(const FnDev f, const EvalIO i
     double* sc = reinterpret_cast<double*>(smem);
     for (int i = threadIdx.x; i < P.nconst; i += blockDim.x) sc[i] = P.consts[i];
   }
-  __syncthreads();
+  const unsigned const_bytes = ((unsigned) P.nconst * 8u + 15u) & ~15u;
+  uint4* const cbuf = reinterpret_cast<uint4*>(smem + const_bytes);  // 2 x PROG_CHUNK_BUNDLES x 4 uint4
+  constexpr int CH = (int) PROG_CHUNK_BUNDLES;
+  const int nb = P.nbundles;
+  const int nchunks = (nb + CH - 1) / CH;
   const unsigned tid8 = threadIdx.x * 8u;
   const int ir = f.ir, orows = f.orows;
   const long long napp = (long long) f.app_end - f.app_begin;
   const long long ntiles = (napp + blockDim.x - 1) / blockDim.x;
   const uint4* __restrict__ code = P.code;
+  auto fetch_chunk = [&](int c) {
+    const int n16 = min(CH, nb - c * CH) * 4;
+    const uint4* src = code + (size_t) c * CH * 4;
+    uint4* dst = cbuf + (c & 1) * CH * 4;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) cp_async16(dst + i, src + i);
+  };
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     long long app = f.app_begin + tile * blockDim.x + threadIdx.x;
     const bool active = app < f.app_end;
     if (!active) app = f.app_end - 1;
+    const bool aff = app >= f.aff_begin && app < f.aff_end;
+    const int rel = (int) (app - f.aff_begin);
     const int* __restrict__ vidx = f.vindex + app * ir;
     const int* __restrict__ cidx = f.cindex + app * orows;
     const double* __restrict__ appc = f.appconst + app * f.nappconst;
     const int* __restrict__ kdest = f.kkt_dest + app * f.E;
 
-    // software pipeline: the next bundle is fetched while the current one executes
-    uint4 n0 = __ldg(code + 0), n1 = __ldg(code + 1), n2 = __ldg(code + 2), n3 = __ldg(code + 3);
-    for (int pc = 1;; pc++) {
-      const uint4 i0 = n0, i1 = n1, i2 = n2, i3 = n3;
-      const unsigned kind = i0.x >> 28;
-      if (kind == PK_END) break;
-      n0 = __ldg(code + 4 * pc + 0);
-      n1 = __ldg(code + 4 * pc + 1);
-      n2 = __ldg(code + 4 * pc + 2);
-      n3 = __ldg(code + 4 * pc + 3);
-      const unsigned cnt = (i0.x >> 24) & 15u;
-      if (kind == PK_FMA) {
-        // unused instructions of a short bundle are encoded as scratch = 0 * 0 + 0 (see link_program), so all four run
-        const double a0 = ld_opnd(smem, i0.y, tid8), b0 = lds(smem, op_addr(i0.z, tid8)), c0 = ld_opnd(smem, i0.w, tid8);
-        const double a1 = ld_opnd(smem, i1.y, tid8), b1 = lds(smem, op_addr(i1.z, tid8)), c1 = ld_opnd(smem, i1.w, tid8);
-        const double a2 = ld_opnd(smem, i2.y, tid8), b2 = lds(smem, op_addr(i2.z, tid8)), c2 = ld_opnd(smem, i2.w, tid8);
-        const double a3 = ld_opnd(smem, i3.y, tid8), b3 = lds(smem, op_addr(i3.z, tid8)), c3 = ld_opnd(smem, i3.w, tid8);
-        const double r0 = fma(a0, b0, c0), r1 = fma(a1, b1, c1), r2 = fma(a2, b2, c2), r3 = fma(a3, b3, c3);
-        *reinterpret_cast<double*>(smem + op_addr(i0.x & 0x00FFFFFFu, tid8)) = r0;
-        *reinterpret_cast<double*>(smem + op_addr(i1.x, tid8)) = r1;
-        *reinterpret_cast<double*>(smem + op_addr(i2.x, tid8)) = r2;
-        *reinterpret_cast<double*>(smem + op_addr(i3.x, tid8)) = r3;
-      } else if (kind == PK_OUT) {
-        const uint4 ins[4] = {i0, i1, i2, i3};
+    __syncthreads();  // every thread is done with the previous tile's last chunk (and the constants are visible)
+    fetch_chunk(0);
+    for (int c = 0; c < nchunks; c++) {
+      cp_async_wait_all();
+      __syncthreads();  // chunk c is visible; every thread has finished chunk c-1, whose buffer is refilled next
+      if (c + 1 < nchunks) fetch_chunk(c + 1);
+      const uint4* __restrict__ cb = cbuf + (c & 1) * CH * 4;
+      const int nbc = min(CH, nb - c * CH);
+      // software pipeline: the next bundle is read from shared memory while the current one executes
+      uint4 n0 = cb[0], n1 = cb[1], n2 = cb[2], n3 = cb[3];
+      for (int pc = 1; pc <= nbc; pc++) {
+        const uint4 i0 = n0, i1 = n1, i2 = n2, i3 = n3;
+        const unsigned kind = i0.x >> 28;
+        if (kind == PK_END) break;
+        if (pc < nbc) {
+          n0 = cb[4 * pc + 0];
+          n1 = cb[4 * pc + 1];
+          n2 = cb[4 * pc + 2];
+          n3 = cb[4 * pc + 3];
+        }
+        const unsigned cnt = (i0.x >> 24) & 15u;
+        if (kind == PK_FMA) {
+          // unused instructions of a short bundle are encoded as scratch = 0 * 0 + 0 (see link_program), so all four run
+          const double a0 = ld_opnd(smem, i0.y, tid8), b0 = lds(smem, op_addr(i0.z, tid8)), c0 = ld_opnd(smem, i0.w, tid8);
+          const double a1 = ld_opnd(smem, i1.y, tid8), b1 = lds(smem, op_addr(i1.z, tid8)), c1 = ld_opnd(smem, i1.w, tid8);
+          const double a2 = ld_opnd(smem, i2.y, tid8), b2 = lds(smem, op_addr(i2.z, tid8)), c2 = ld_opnd(smem, i2.w, tid8);
+          const double a3 = ld_opnd(smem, i3.y, tid8), b3 = lds(smem, op_addr(i3.z, tid8)), c3 = ld_opnd(smem, i3.w, tid8);
+          const double r0 = fma(a0, b0, c0), r1 = fma(a1, b1, c1), r2 = fma(a2, b2, c2), r3 = fma(a3, b3, c3);
+          *reinterpret_cast<double*>(smem + op_addr(i0.x & 0x00FFFFFFu, tid8)) = r0;
+          *reinterpret_cast<double*>(smem + op_addr(i1.x, tid8)) = r1;
+          *reinterpret_cast<double*>(smem + op_addr(i2.x, tid8)) = r2;
+          *reinterpret_cast<double*>(smem + op_addr(i3.x, tid8)) = r3;
+        } else if (kind == PK_OUT) {
+          const uint4 ins[4] = {i0, i1, i2, i3};
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-          if (q < cnt) {
-            const double v = ld_opnd(smem, ins[q].y, tid8);
-            const unsigned ok = ins[q].z, idx = ins[q].w;
-            if (active) {
-              if (ok == PO_F) {
-                if (f.role == ROLE_OBJ) {
+          for (int q = 0; q < 4; q++) {
+            if (q < cnt) {
+              const double v = ld_opnd(smem, ins[q].y, tid8);
+              const unsigned ok = ins[q].z & 15u, idx = ins[q].z >> 4;
+              const int base = (int) ins[q].w, stride = ((int) (ins[q].x << 8)) >> 8;
+              if (active) {
+                if (ok == PO_G) {
+                  io.stage[f.g_stage + app * ir + idx] = v;
+                } else if (ok == PO_F && f.role == ROLE_OBJ) {
                   io.stage[f.v_stage + app] = v * io.obj_scale;
                 } else {
-                  const int fd = __ldg(f.f_dest + app * orows + idx);
-                  if (fd >= 0)
-                    io.fx[fd] = v;
+                  int d;
+                  if (aff)
+                    d = base + rel * stride;
                   else
-                    io.stage[~fd] = v;
+                    d = (ok == PO_F) ? __ldg(f.f_dest + app * orows + idx) : __ldg(kdest + idx);
+                  double* tgt = (ok == PO_F) ? io.fx : io.kkt;
+                  if (d >= 0)
+                    tgt[d] = v;
+                  else
+                    io.stage[~d] = v;
                 }
-              } else if (ok == PO_G) {
-                io.stage[f.g_stage + app * ir + idx] = v;
-              } else {
-                put(io, kdest, idx, v);
               }
             }
           }
-        }
-      } else if (kind == PK_LOAD) {
-        const uint4 ins[4] = {i0, i1, i2, i3};
+        } else if (kind == PK_LOAD) {
+          const uint4 ins[4] = {i0, i1, i2, i3};
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-          if (q < cnt) {
-            const unsigned idx = ins[q].y, ty = ins[q].z;
-            double v;
-            if (ty == PL_X)
-              v = __ldg(io.X + __ldg(vidx + idx));
-            else if (ty == PL_LAMBDA)
-              v = (f.role == ROLE_OBJ) ? io.obj_scale : __ldg(io.L + __ldg(cidx + idx));
-            else
-              v = __ldg(appc + idx);
-            *reinterpret_cast<double*>(smem + op_addr(ins[q].x & 0x00FFFFFFu, tid8)) = v;
+          for (int q = 0; q < 4; q++) {
+            if (q < cnt) {
+              const unsigned idx = ins[q].y & 0x0FFFFFFFu, ty = ins[q].y >> 28;
+              const int gi = (int) ins[q].z + rel * (int) ins[q].w;
+              double v;
+              if (ty == PL_X)
+                v = __ldg(io.X + (aff ? gi : __ldg(vidx + idx)));
+              else if (ty == PL_LAMBDA)
+                v = (f.role == ROLE_OBJ) ? io.obj_scale : __ldg(io.L + (aff ? gi : __ldg(cidx + idx)));
+              else
+                v = __ldg(appc + idx);
+              *reinterpret_cast<double*>(smem + op_addr(ins[q].x & 0x00FFFFFFu, tid8)) = v;
+            }
           }
+        } else {  // PK_SPECIAL: one operation
+          const unsigned op = i0.w & 0xFFu;
+          const double a = ld_opnd(smem, i0.y, tid8);
+          const double b = ld_opnd(smem, i0.z, tid8);
+          const double c3 = ld_opnd(smem, i1.y, tid8);
+          const double imm = lds(smem, (i0.w >> 8) * 8u);
+          *reinterpret_cast<double*>(smem + op_addr(i0.x & 0x00FFFFFFu, tid8)) = special_op(op, a, b, c3, imm);
         }
-      } else {  // PK_SPECIAL: one operation
-        const unsigned op = i0.w & 0xFFu;
-        const double a = ld_opnd(smem, i0.y, tid8);
-        const double b = ld_opnd(smem, i0.z, tid8);
-        const double c = ld_opnd(smem, i1.y, tid8);
-        const double imm = lds(smem, (i0.w >> 8) * 8u);
-        *reinterpret_cast<double*>(smem + op_addr(i0.x & 0x00FFFFFFu, tid8)) = special_op(op, a, b, c, imm);
       }
     }
   }

@@ -36,6 +36,48 @@ Plan::~Plan() {
   if (stream) cudaStreamDestroy(stream);
 }
 
+// Largest application range around the middle of the function over which every index map is affine in the application
+// number (true for all interior mesh segments of a phase: the transcription and the CSR pattern are periodic there).
+static AffineMaps find_affine(const int* V, int ir, const int* C, int orr, const int* FD, const int* KD, int E, int napp) {
+  AffineMaps am;
+  if (napp < 8) return am;
+  const long long mid = napp / 2;
+  struct Col {
+    const int* p;
+    int w;
+    std::vector<int>*base, *stride;
+  };
+  std::vector<Col> cols;
+  cols.push_back({V, ir, &am.vbase, &am.vstride});
+  if (C) cols.push_back({C, orr, &am.cbase, &am.cstride});
+  if (FD) cols.push_back({FD, orr, &am.fbase, &am.fstride});
+  cols.push_back({KD, E, &am.kbase, &am.kstride});
+  for (Col& c: cols) {
+    c.base->resize(c.w);
+    c.stride->resize(c.w);
+    for (int q = 0; q < c.w; q++) {
+      const long long st = (long long) c.p[(mid + 1) * c.w + q] - c.p[mid * c.w + q];
+      if (st >= (1 << 23) || st <= -(1 << 23)) return AffineMaps();
+      (*c.stride)[q] = (int) st;
+    }
+  }
+  auto row_ok = [&](long long a) {
+    for (const Col& c: cols)
+      for (int q = 0; q < c.w; q++)
+        if ((long long) c.p[a * c.w + q] != (long long) c.p[mid * c.w + q] + (a - mid) * (*c.stride)[q]) return false;
+    return true;
+  };
+  long long a0 = mid, a1 = mid + 1;
+  while (a0 > 0 && row_ok(a0 - 1)) a0--;
+  while (a1 < napp && row_ok(a1)) a1++;
+  if (a1 - a0 < 4) return AffineMaps();
+  for (Col& c: cols)
+    for (int q = 0; q < c.w; q++) (*c.base)[q] = c.p[a0 * c.w + q];
+  am.a0 = (int) a0;
+  am.a1 = (int) a1;
+  return am;
+}
+
 static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
   for (int w = 0; w < 2; w++) {
     dg.dev[w].ntargets = gl[w].ntargets();
@@ -75,6 +117,11 @@ int Plan::build(int dev) {
     // device programs: one per evaluation mode this role can be asked for
     std::array<ProgDev, 5> pd;
     std::memset(pd.data(), 0, sizeof(ProgDev) * 5);
+    AffineMaps am;
+    if (fr.nappl >= 8)
+      am = find_affine(fr.vindex.data(), fr.ir, fr.role ? fr.cindex.data() : nullptr, fr.orows,
+                       fr.role ? prob.f_dest.data() + prob.fdest_base[fi] : nullptr, prob.kkt_dest.data() + prob.trip_base[fi],
+                       fr.triplets_per_app(), fr.nappl);
     try {
       ScalarFn work = *t.fn;
       for (int mode = 0; mode < 5; mode++) {
@@ -86,7 +133,7 @@ int Plan::build(int dev) {
         sp.want_j = (mode >= FM_JAC);
         sp.want_h = (mode == FM_ALL);
         Program P = emit_program(work, sp);
-        LinkedProgram L = link_program(P, 220u * 1024u);
+        LinkedProgram L = link_program(P, 220u * 1024u, &am);
         std::vector<uint4> code(L.code.size());
         std::memcpy(code.data(), L.code.data(), L.code.size() * sizeof(PInstr));
         pd[mode].code = dupload(code);
@@ -106,6 +153,8 @@ int Plan::build(int dev) {
       return (int) cudaErrorInvalidValue;
     }
     progs.push_back(pd);
+    f.aff_begin = am.a0;
+    f.aff_end = am.a1;
     f.ir = fr.ir;
     f.orows = fr.orows;
     f.nappconst = fr.nappconst;

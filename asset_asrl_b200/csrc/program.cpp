@@ -374,21 +374,22 @@ Program emit_program(ScalarFn& f, const ProgramSpec& spec) {
 // Rewrites operand words from (index << 3 | flags) to (shared-memory byte offset | flags) for a block of `nthreads`
 // lane-private slots laid out [slot][thread] after the shared constants, and pads short FMA bundles with
 // scratch = 0 * 0 + 0 so the interpreter can always run four operations.
-LinkedProgram link_program(const Program& P, unsigned smem_budget) {
+LinkedProgram link_program(const Program& P, unsigned smem_budget, const AffineMaps* am) {
   LinkedProgram L;
   const unsigned const_bytes = (unsigned) ((P.consts.size() * 8 + 15) / 16 * 16);
   const unsigned per_thread = (unsigned) (P.nslots + 1) * 8u;  // +1: scratch slot
-  if (const_bytes + per_thread * 32u > smem_budget)
+  const unsigned code_bytes = 2u * PROG_CHUNK_BUNDLES * 64u;
+  if (const_bytes + code_bytes + per_thread * 32u > smem_budget)
     throw std::length_error("function needs " + std::to_string(P.nslots) + " live values per application: too large for the "
                             "shared-memory interpreter (no CPU fallback on this path)");
-  unsigned nt = (smem_budget - const_bytes) / per_thread / 32u * 32u;
+  unsigned nt = (smem_budget - const_bytes - code_bytes) / per_thread / 32u * 32u;
   nt = std::min(nt, 256u);
   L.nthreads = (int) nt;
-  L.smem_bytes = const_bytes + per_thread * nt;
+  L.smem_bytes = const_bytes + code_bytes + per_thread * nt;
   L.nslots = P.nslots + 1;
   auto lk = [&](uint32_t w) -> uint32_t {
     const uint32_t flags = w & 7u, idx = w >> 3;
-    if (flags & P_SLOT) return (const_bytes + idx * nt * 8u) | flags;
+    if (flags & P_SLOT) return (const_bytes + code_bytes + idx * nt * 8u) | flags;
     return (idx * 8u) | flags;
   };
   const uint32_t scratch = lk(((uint32_t) P.nslots << 3) | P_SLOT);
@@ -413,10 +414,42 @@ LinkedProgram link_program(const Program& P, unsigned smem_budget) {
         }
         break;
       case PK_LOAD:
-        for (uint32_t q = 0; q < cnt; q++) ins[q].d = lk(ins[q].d);
+        // linked form: a = index | type << 28, b = affine base, c = affine stride (per application, from app a0)
+        for (uint32_t q = 0; q < cnt; q++) {
+          ins[q].d = lk(ins[q].d);
+          const uint32_t idx = ins[q].a, ty = ins[q].b;
+          ins[q].a = idx | (ty << 28);
+          ins[q].b = ins[q].c = 0u;
+          if (am && am->a1 > am->a0) {
+            if (ty == PL_X) {
+              ins[q].b = (uint32_t) am->vbase.at(idx);
+              ins[q].c = (uint32_t) am->vstride.at(idx);
+            } else if (ty == PL_LAMBDA && !am->cbase.empty()) {
+              ins[q].b = (uint32_t) am->cbase.at(idx);
+              ins[q].c = (uint32_t) am->cstride.at(idx);
+            }
+          }
+        }
         break;
       case PK_OUT:
-        for (uint32_t q = 0; q < cnt; q++) ins[q].a = lk(ins[q].a);
+        // linked form: b = out kind | index << 4, c = affine destination base, d[23:0] = signed affine stride
+        for (uint32_t q = 0; q < cnt; q++) {
+          ins[q].a = lk(ins[q].a);
+          const uint32_t ok = ins[q].b, idx = ins[q].c;
+          ins[q].b = ok | (idx << 4);
+          int base = 0, stride = 0;
+          if (am && am->a1 > am->a0) {
+            if (ok == PO_F && !am->fbase.empty()) {
+              base = am->fbase.at(idx);
+              stride = am->fstride.at(idx);
+            } else if (ok == PO_J || ok == PO_H) {
+              base = am->kbase.at(idx);
+              stride = am->kstride.at(idx);
+            }
+          }
+          ins[q].c = (uint32_t) base;
+          ins[q].d = (ins[q].d & 0xFF000000u) | ((uint32_t) stride & 0x00FFFFFFu);
+        }
         break;
       case PK_SPECIAL:
         ins[0].d = lk(ins[0].d);
@@ -426,8 +459,8 @@ LinkedProgram link_program(const Program& P, unsigned smem_budget) {
         break;
       default: break;
     }
-    if (ins[0].d & 0xFF000000u) throw std::length_error("link_program: shared-memory offset exceeds 24 bits");
-    ins[0].d |= head;
+    if (kind != PK_OUT && (ins[0].d & 0xFF000000u)) throw std::length_error("link_program: shared-memory offset exceeds 24 bits");
+    ins[0].d = (ins[0].d & 0x00FFFFFFu) | head;
   }
   return L;
 }

@@ -130,6 +130,22 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_program_code(self.h, f, mode, code.ctypes.data_as(C.c_void_p), _lib.dptr(consts)))
         return st, code, consts
 
+    def kernel_ptx(self, f, mode=4):
+        """PTX of the specialised kernel for function ``f`` (None if it has no affine application range)."""
+        n = _lib.check(lib.ab_problem_kernel_ptx(self.h, f, mode, None, 0))
+        if n == 0:
+            return None
+        buf = C.create_string_buffer(n + 1)
+        _lib.check(lib.ab_problem_kernel_ptx(self.h, f, mode, buf, n + 1))
+        return buf.value.decode()
+
+    @staticmethod
+    def assemble_ptx(ptx):
+        """Assemble PTX for sm_100a in-process (no GPU needed): {cubin_bytes, registers, spill_bytes}."""
+        out = (C.c_longlong * 3)()
+        _lib.check(lib.ab_ptx_assemble(ptx.encode(), out))
+        return {"cubin_bytes": int(out[0]), "registers": int(out[1]), "spill_bytes": int(out[2])}
+
     def tape_describe(self, t):
         """Text form of what tape ``t`` was lowered from (introspection; the CPU oracle in tests/ rebuilds it)."""
         n = _lib.check(lib.ab_problem_tape_describe(self.h, t, None, 0))
@@ -252,6 +268,15 @@ class NonLinearProgram:
 
     def launches(self):
         return int(lib.ab_plan_launches(self.plan)) if self.plan else 0
+
+    def specialised_launches(self):
+        """How many launches of the last eval were specialised (run-time assembled) kernels."""
+        return int(lib.ab_plan_specialised_launches(self.plan)) if self.plan else 0
+
+    def kernel_info(self, k, mode=4):
+        out = (C.c_int * 4)()
+        _lib.check(lib.ab_plan_kernel_info(self.plan, k, mode, out))
+        return dict(zip(["state", "registers", "spill_bytes", "affine_apps"], [int(v) for v in out]))
 
     def NLPTest(self, X, n, seed=67890):
         """NLPTest protocol (NonLinearProgram.cpp:686-820): multipliers 100*U(-1,1), n repetitions of evalKKT;

@@ -57,6 +57,8 @@ SIGNATURES = {
     "ab_problem_tape_describe": (_ll, [_vp, _i, _cp, _ll]),
     "ab_problem_program_stats": (_i, [_vp, _i, _i, _llp]),
     "ab_problem_program_code": (_i, [_vp, _i, _i, _vp, _dp]),
+    "ab_problem_kernel_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
+    "ab_ptx_assemble": (_i, [_cp, _llp]),
     "ab_problem_tape_code": (_i, [_vp, _i, _vp]),
     "ab_phase_create": (_vp, [_vp, _i, _i, _i, _i, _i, _i]),
     "ab_phase_destroy": (None, [_vp]),
@@ -84,6 +86,8 @@ SIGNATURES = {
     "ab_plan_device_ptr": (_vp, [_vp, _i]),
     "ab_plan_stream": (_vp, [_vp]),
     "ab_plan_launches": (_ll, [_vp]),
+    "ab_plan_specialised_launches": (_ll, [_vp]),
+    "ab_plan_kernel_info": (_i, [_vp, _i, _i, _ip]),
 }
 for _name, (_res, _args) in SIGNATURES.items():
     _fn = getattr(lib, _name)

@@ -321,6 +321,45 @@ int ab_problem_program_stats(const ab_problem* p, int fidx, int mode, long long 
   return AB_OK;
   AB_CATCH
 }
+long long ab_problem_kernel_ptx(const ab_problem* p, int fidx, int mode, char* buf, long long cap) {
+  try {
+    if (!p->p.analyzed) throw std::invalid_argument("ab_problem_analyze() first");
+    const FuncRec& fr = p->p.funcs.at(fidx);
+    Program P = program_of(p, fidx, mode);
+    const AffineMaps am = function_affine(p->p, fidx);
+    if (am.a1 <= am.a0) return 0;
+    JitSpec sp;
+    sp.name = "ab_seg_f" + std::to_string(fidx) + "_m" + std::to_string(mode);
+    sp.role = fr.role;
+    sp.ir = fr.ir;
+    sp.orows = fr.orows;
+    sp.nappconst = fr.nappconst;
+    sp.g_stage = p->p.g_stage.at(fidx);
+    sp.v_stage = p->p.v_stage.at(fidx);
+    sp.nthreads = 64;
+    const std::string s = emit_ptx(P, sp, am);
+    if (buf && cap > 0) {
+      const size_t n = std::min<size_t>(s.size(), (size_t) cap - 1);
+      std::memcpy(buf, s.data(), n);
+      buf[n] = 0;
+    }
+    return (long long) s.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
+int ab_ptx_assemble(const char* ptx, long long out[3]) {
+  AB_TRY
+  std::vector<char> cubin;
+  std::string log;
+  int nregs = 0, spill = 0;
+  if (!assemble_ptx(ptx, cubin, log, &nregs, &spill)) throw std::runtime_error(log);
+  out[0] = (long long) cubin.size();
+  out[1] = nregs;
+  out[2] = spill;
+  return AB_OK;
+  AB_CATCH
+}
 int ab_problem_tape_code(const ab_problem* p, int t, void* out) {
   AB_TRY
   const Tape& tp = p->p.tapes.at(t);
@@ -567,5 +606,17 @@ long long ab_plan_profile_label(ab_plan* plan, int k, char* buf, long long cap) 
 }
 void* ab_plan_stream(ab_plan* plan) { return (void*) plan->plan.stream; }
 long long ab_plan_launches(const ab_plan* plan) { return plan->plan.launches; }
+long long ab_plan_specialised_launches(const ab_plan* plan) { return plan->plan.jit_launches; }
+int ab_plan_kernel_info(const ab_plan* plan, int k, int mode, int out[4]) {
+  AB_TRY
+  const Plan& P = plan->plan;
+  if (mode < 0 || mode > 4) throw std::invalid_argument("mode must be 0..4");
+  out[0] = P.jit_state.at(k)[mode];
+  out[1] = P.jits.at(k)[mode].nregs;
+  out[2] = P.jits.at(k)[mode].spill_bytes;
+  out[3] = P.affs.at(k).a1 - P.affs.at(k).a0;
+  return AB_OK;
+  AB_CATCH
+}
 
 }  // extern "C"

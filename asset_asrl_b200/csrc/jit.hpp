@@ -1,0 +1,67 @@
+// Kernel specialiser: turns the scalar device program of one function (expr.hpp: Program) into a straight-line
+// sm_100a kernel, written as PTX and assembled in-process with the static PTX compiler of the CUDA toolkit.
+//
+// Why: the program of a collocation defect is a few thousand fused multiply-adds on a few hundred live values
+// (LGL5 two-body low thrust: 4302 DFMA, 867 outputs).  Interpreted, every DFMA costs three shared-memory loads, a
+// store and ~25 integer instructions of decode; specialised, the values live in registers and the kernel is DFMA and
+// output stores only, which is what lets the evaluation approach the HBM write roofline.  The C++ front end of nvcc
+// / NVRTC needs minutes for one 5000-statement basic block, ptxas about a second, hence PTX and not CUDA C.
+//
+// A specialised kernel covers the *affine* application range of a function (all interior mesh segments, where every
+// gather/scatter index is base + segment * stride, see AffineMaps); the few applications at the mesh ends and all
+// single-application functions stay on the interpreter (kernels.cu), which reads explicit index maps.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "expr.hpp"
+
+namespace ab {
+
+struct JitSpec {
+  std::string name;       // kernel entry name ([A-Za-z0-9_])
+  int role = 1;           // FnRole
+  int ir = 0, orows = 0;
+  int nappconst = 0;
+  long long g_stage = 0;  // gradient contributions go to stage[g_stage + app*ir + i]
+  long long v_stage = 0;  // objective value contributions go to stage[v_stage + app]
+  int nthreads = 128;     // block size (.maxntid)
+};
+
+// Kernel parameters, in order (see launch_jit): X, L, kkt, fx, stage, appconst (u64 each), obj_scale (f64),
+// rel_begin, rel_end (s32: application range relative to the first affine application am.a0).
+struct JitArgs {
+  const double* X;
+  const double* L;
+  double* kkt;
+  double* fx;
+  double* stage;
+  const double* appconst;
+  double obj_scale;
+  int rel_begin, rel_end;
+};
+
+// PTX text of the kernel; throws std::runtime_error when the function cannot be specialised (mixed direct/staged
+// destinations inside the affine range, offsets out of range).
+std::string emit_ptx(const Program& P, const JitSpec& spec, const AffineMaps& am);
+
+// Assembles PTX for sm_100a.  Works without a GPU (used by the CPU-side tests).  Returns false and fills `log` on error.
+bool assemble_ptx(const std::string& ptx, std::vector<char>& cubin, std::string& log, int* nregs = nullptr,
+                  int* spill_bytes = nullptr);
+
+struct JitKernel {
+  cudaLibrary_t lib = nullptr;
+  cudaKernel_t kern = nullptr;
+  int nthreads = 0;
+  int nregs = 0;        // from the assembler's report (0 if unknown)
+  int spill_bytes = 0;  // spill stores + loads per thread
+  bool ok() const { return kern != nullptr; }
+};
+
+cudaError_t load_jit(const std::vector<char>& cubin, const std::string& name, JitKernel& out);
+void unload_jit(JitKernel& k);
+cudaError_t launch_jit(const JitKernel& k, const JitArgs& a, cudaStream_t st);
+
+}  // namespace ab

@@ -1,6 +1,9 @@
 #include "plan.hpp"
 
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <unordered_map>
 
 namespace ab {
 
@@ -31,6 +34,8 @@ T* Plan::dupload(const std::vector<T>& v) {
 }
 
 Plan::~Plan() {
+  for (auto& a: jits)
+    for (JitKernel& k: a) unload_jit(k);
   for (cudaEvent_t e: prof_events) cudaEventDestroy(e);
   for (void* p: owned) cudaFree(p);
   if (stream) cudaStreamDestroy(stream);
@@ -78,6 +83,14 @@ static AffineMaps find_affine(const int* V, int ir, const int* C, int orr, const
   return am;
 }
 
+AffineMaps function_affine(const Problem& prob, int fi) {
+  const FuncRec& fr = prob.funcs.at(fi);
+  if (fr.nappl < 8) return AffineMaps();
+  return find_affine(fr.vindex.data(), fr.ir, fr.role ? fr.cindex.data() : nullptr, fr.orows,
+                     fr.role ? prob.f_dest.data() + prob.fdest_base[fi] : nullptr, prob.kkt_dest.data() + prob.trip_base[fi],
+                     fr.triplets_per_app(), fr.nappl);
+}
+
 static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
   for (int w = 0; w < 2; w++) {
     dg.dev[w].ntargets = gl[w].ntargets();
@@ -105,6 +118,12 @@ int Plan::build(int dev) {
   }
   fns.clear();
   progs.clear();
+  affs.clear();
+  host_progs.clear();
+  jits.clear();
+  jit_state.clear();
+  if (const char* e = getenv("ASSET_B200_JIT")) use_jit = std::atoi(e) != 0;
+  if (const char* e = getenv("ASSET_B200_JIT_MIN")) jit_min_apps = std::max(1, std::atoi(e));
   for (int fi: prob.order) {
     const FuncRec& fr = prob.funcs[fi];
     const Tape& t = prob.tapes.at(fr.tape);
@@ -117,11 +136,8 @@ int Plan::build(int dev) {
     // device programs: one per evaluation mode this role can be asked for
     std::array<ProgDev, 5> pd;
     std::memset(pd.data(), 0, sizeof(ProgDev) * 5);
-    AffineMaps am;
-    if (fr.nappl >= 8)
-      am = find_affine(fr.vindex.data(), fr.ir, fr.role ? fr.cindex.data() : nullptr, fr.orows,
-                       fr.role ? prob.f_dest.data() + prob.fdest_base[fi] : nullptr, prob.kkt_dest.data() + prob.trip_base[fi],
-                       fr.triplets_per_app(), fr.nappl);
+    std::array<Program, 5> hp;
+    const AffineMaps am = function_affine(prob, fi);
     try {
       ScalarFn work = *t.fn;
       for (int mode = 0; mode < 5; mode++) {
@@ -147,12 +163,17 @@ int Plan::build(int dev) {
         pd[mode].nthreads = L.nthreads;
         pd[mode].nbundles = P.bundles();
         pd[mode].smem_bytes = L.smem_bytes;
+        hp[mode] = std::move(P);
       }
     } catch (const std::exception& e) {
       last_error = std::string(e.what()) + " (" + fr.name + ")";
       return (int) cudaErrorInvalidValue;
     }
     progs.push_back(pd);
+    host_progs.push_back(std::move(hp));
+    affs.push_back(am);
+    jits.emplace_back();
+    jit_state.push_back({0, 0, 0, 0, 0});
     f.aff_begin = am.a0;
     f.aff_end = am.a1;
     f.ir = fr.ir;
@@ -234,6 +255,74 @@ int Plan::profile_read(float* ms, int cap) {
   return n;
 }
 
+// Process-wide cache of assembled kernels keyed by their PTX text: plans of the same problem (tests, mesh iterations
+// that keep N) share the cubin instead of assembling it again.
+namespace {
+struct CubinEntry {
+  std::vector<char> cubin;
+  int nregs = 0, spill = 0;
+};
+std::mutex g_cubin_mu;
+std::unordered_map<std::string, CubinEntry> g_cubins;
+}  // namespace
+
+int Plan::ensure_jit(size_t k, int fm) {
+  if (!use_jit) return 0;
+  signed char& st = jit_state[k][fm];
+  if (st != 0) return st > 0 ? 1 : 0;
+  st = -1;
+  const AffineMaps& am = affs[k];
+  if (am.a1 - am.a0 < jit_min_apps) return 0;
+  const FuncRec& fr = prob.funcs[prob.order[k]];
+  JitSpec sp;
+  sp.name = "ab_seg_f" + std::to_string(k) + "_m" + std::to_string(fm);
+  sp.role = fr.role;
+  sp.ir = fr.ir;
+  sp.orows = fr.orows;
+  sp.nappconst = fr.nappconst;
+  sp.g_stage = fns[k].g_stage;
+  sp.v_stage = fns[k].v_stage;
+  sp.nthreads = 64;
+  std::string ptx;
+  try {
+    ptx = emit_ptx(host_progs[k][fm], sp, am);
+  } catch (const std::exception& e) {
+    jit_log = std::string(e.what()) + " (" + fr.name + ")";
+    return 0;
+  }
+  CubinEntry ce;
+  bool have = false;
+  {
+    std::lock_guard<std::mutex> lk(g_cubin_mu);
+    auto it = g_cubins.find(ptx);
+    if (it != g_cubins.end()) {
+      ce = it->second;
+      have = true;
+    }
+  }
+  if (!have) {
+    std::string log;
+    if (!assemble_ptx(ptx, ce.cubin, log, &ce.nregs, &ce.spill)) {
+      // a program the assembler rejects is a bug of the emitter: fail loudly rather than fall back silently
+      last_error = "specialised kernel of " + fr.name + ": " + log;
+      return -(int) cudaErrorInvalidPtx;
+    }
+    std::lock_guard<std::mutex> lk(g_cubin_mu);
+    g_cubins.emplace(ptx, ce);
+  }
+  JitKernel& jk = jits[k][fm];
+  cudaError_t e = load_jit(ce.cubin, sp.name, jk);
+  if (e != cudaSuccess) {
+    last_error = "loading the specialised kernel of " + fr.name + ": " + cudaGetErrorString(e);
+    return -(int) e;
+  }
+  jk.nthreads = sp.nthreads;
+  jk.nregs = ce.nregs;
+  jk.spill_bytes = ce.spill;
+  st = 1;
+  return 1;
+}
+
 int Plan::eval(int mode, double obj_scale) {
   AB_CUDA(cudaSetDevice(device));
   int obj_mode = -1, con_mode = -1;
@@ -250,6 +339,7 @@ int Plan::eval(int mode, double obj_scale) {
     default: last_error = "unknown eval mode"; return (int) cudaErrorInvalidValue;
   }
   launches = 0;
+  jit_launches = 0;
   if (profiling != 2) prof_labels.clear();
   if (out_kkt && mode != EM_KKT) {
     // partial matrix modes: entries this mode does not compute must read as zero
@@ -273,9 +363,51 @@ int Plan::eval(int mode, double obj_scale) {
       last_error = "no device program for this mode";
       return (int) cudaErrorInvalidValue;
     }
-    AB_CUDA(launch_eval(fd, stream, io));
+    const size_t k = (size_t) (&f - fns.data());
+    const int jr = ensure_jit(k, fm);
+    if (jr < 0) return -jr;
+    if (jr > 0) {
+      // interior segments on the specialised kernel, mesh ends on the interpreter
+      const int a0 = affs[k].a0, a1 = affs[k].a1;
+      const int jb = std::max(a0, f.app_begin), je = std::min(a1, f.app_end);
+      JitArgs ja;
+      ja.X = io.X;
+      ja.L = io.L;
+      ja.kkt = io.kkt;
+      ja.fx = io.fx;
+      ja.stage = io.stage;
+      ja.appconst = f.appconst;
+      ja.obj_scale = obj_scale;
+      ja.rel_begin = jb - a0;
+      ja.rel_end = je - a0;
+      if (je > jb) {
+        AB_CUDA(launch_jit(jits[k][fm], ja, stream));
+        launches++;
+        jit_launches++;
+      }
+      const int hb = f.app_begin, he = std::min(f.app_end, std::max(jb, f.app_begin));
+      if (je <= jb) {
+        AB_CUDA(launch_eval(fd, stream, io));
+        launches++;
+      } else {
+        if (he > hb) {
+          FnDev h = fd;
+          h.app_end = he;
+          AB_CUDA(launch_eval(h, stream, io));
+          launches++;
+        }
+        if (f.app_end > je) {
+          FnDev t = fd;
+          t.app_begin = je;
+          AB_CUDA(launch_eval(t, stream, io));
+          launches++;
+        }
+      }
+    } else {
+      AB_CUDA(launch_eval(fd, stream, io));
+      launches++;
+    }
     if (int rc = prof_end()) return rc;
-    launches++;
   }
   auto G = [&](DevGather& g, double* out, const char* label) -> int {
     const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);

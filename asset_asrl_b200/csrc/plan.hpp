@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "device_types.h"
+#include "jit.hpp"
 #include "nlp.hpp"
 
 namespace ab {
@@ -37,6 +38,17 @@ struct Plan {
   std::vector<FnDev> fns;  // in evaluation order
   std::vector<std::array<ProgDev, 5>> progs;  // per function, per FnMode (nthreads == 0: mode not generated)
   std::vector<void*> owned;  // every device allocation, freed in the destructor
+  // Specialised kernels (jit.hpp): compiled on first use of a (function, mode) pair for the affine application range
+  // of the function; the mesh ends and functions without such a range run on the interpreter.
+  bool use_jit = true;    // ASSET_B200_JIT=0 switches the specialiser off (interpreter only)
+  int jit_min_apps = 32;  // ASSET_B200_JIT_MIN: smallest affine range worth a specialised kernel
+  std::vector<AffineMaps> affs;                        // per function
+  std::vector<std::array<Program, 5>> host_progs;      // unlinked programs, kept for the specialiser
+  std::vector<std::array<JitKernel, 5>> jits;          // per function, per FnMode
+  std::vector<std::array<signed char, 5>> jit_state;   // 0 not tried, 1 ready, -1 not specialisable
+  std::string jit_log;                                 // why the last refused specialisation was refused
+  int ensure_jit(size_t k, int fm);                    // returns 1 ready, 0 use the interpreter, < 0 CUDA error (negated)
+  long long jit_launches = 0;                          // specialised-kernel launches of the last eval
 
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;
   double *d_kkt = nullptr, *d_fxe = nullptr, *d_fxi = nullptr, *d_pgx = nullptr, *d_agx = nullptr, *d_val = nullptr;
@@ -63,6 +75,8 @@ struct Plan {
   T* dupload(const std::vector<T>& v);
 };
 
+// Largest application range of function `fi` over which every index map is affine in the application number.
+AffineMaps function_affine(const Problem& prob, int fi);
 cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io);
 cudaError_t launch_gather(const GatherDev& small, const GatherDev& large, const double* stage, double* out,
                           cudaStream_t st);

@@ -130,13 +130,14 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_program_code(self.h, f, mode, code.ctypes.data_as(C.c_void_p), _lib.dptr(consts)))
         return st, code, consts
 
-    def kernel_ptx(self, f, mode=4):
-        """PTX of the specialised kernel for function ``f`` (None if it has no affine application range)."""
-        n = _lib.check(lib.ab_problem_kernel_ptx(self.h, f, mode, None, 0))
+    def kernel_ptx(self, f, mode=4, indexed=False):
+        """PTX of the specialised kernel for function ``f``: the affine variant (None if the function has no affine
+        application range) or the indexed variant that reads explicit index maps."""
+        n = _lib.check(lib.ab_problem_kernel_ptx(self.h, f, mode, int(indexed), None, 0))
         if n == 0:
             return None
         buf = C.create_string_buffer(n + 1)
-        _lib.check(lib.ab_problem_kernel_ptx(self.h, f, mode, buf, n + 1))
+        _lib.check(lib.ab_problem_kernel_ptx(self.h, f, mode, int(indexed), buf, n + 1))
         return buf.value.decode()
 
     @staticmethod

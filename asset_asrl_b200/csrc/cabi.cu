@@ -321,15 +321,17 @@ int ab_problem_program_stats(const ab_problem* p, int fidx, int mode, long long 
   return AB_OK;
   AB_CATCH
 }
-long long ab_problem_kernel_ptx(const ab_problem* p, int fidx, int mode, char* buf, long long cap) {
+long long ab_problem_kernel_ptx(const ab_problem* p, int fidx, int mode, int indexed, char* buf, long long cap) {
   try {
     if (!p->p.analyzed) throw std::invalid_argument("ab_problem_analyze() first");
     const FuncRec& fr = p->p.funcs.at(fidx);
     Program P = program_of(p, fidx, mode);
     const AffineMaps am = function_affine(p->p, fidx);
-    if (am.a1 <= am.a0) return 0;
+    if (!indexed && am.a1 <= am.a0) return 0;
     JitSpec sp;
-    sp.name = "ab_seg_f" + std::to_string(fidx) + "_m" + std::to_string(mode);
+    sp.name = std::string(indexed ? "ab_idx_f" : "ab_seg_f") + std::to_string(fidx) + "_m" + std::to_string(mode);
+    sp.indexed = indexed != 0;
+    sp.E = fr.triplets_per_app();
     sp.role = fr.role;
     sp.ir = fr.ir;
     sp.orows = fr.orows;
@@ -611,9 +613,9 @@ int ab_plan_kernel_info(const ab_plan* plan, int k, int mode, int out[4]) {
   AB_TRY
   const Plan& P = plan->plan;
   if (mode < 0 || mode > 4) throw std::invalid_argument("mode must be 0..4");
-  out[0] = P.jit_state.at(k)[mode];
-  out[1] = P.jits.at(k)[mode].nregs;
-  out[2] = P.jits.at(k)[mode].spill_bytes;
+  out[0] = P.jit_state[0].at(k)[mode];
+  out[1] = P.jits[0].at(k)[mode].nregs;
+  out[2] = P.jits[0].at(k)[mode].spill_bytes;
   out[3] = P.affs.at(k).a1 - P.affs.at(k).a0;
   return AB_OK;
   AB_CATCH

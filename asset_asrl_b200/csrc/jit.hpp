@@ -25,13 +25,18 @@ struct JitSpec {
   int role = 1;           // FnRole
   int ir = 0, orows = 0;
   int nappconst = 0;
+  int E = 0;              // KKT triplets per application
+  // false: affine variant, addresses are base + rel*stride with the AffineMaps baked in as immediates (bulk of the
+  // mesh); true: indexed variant, every gather/scatter index is read from the explicit maps (mesh ends, functions
+  // without an affine range, single-application functions)
+  bool indexed = false;
   long long g_stage = 0;  // gradient contributions go to stage[g_stage + app*ir + i]
   long long v_stage = 0;  // objective value contributions go to stage[v_stage + app]
   int nthreads = 128;     // block size (.maxntid)
 };
 
-// Kernel parameters, in order (see launch_jit): X, L, kkt, fx, stage, appconst (u64 each), obj_scale (f64),
-// rel_begin, rel_end (s32: application range relative to the first affine application am.a0).
+// Kernel parameters, in order (see launch_jit).  begin/end: application range, relative to the first affine
+// application am.a0 for the affine variant, absolute for the indexed variant.
 struct JitArgs {
   const double* X;
   const double* L;
@@ -39,13 +44,27 @@ struct JitArgs {
   double* fx;
   double* stage;
   const double* appconst;
+  const int* vindex;
+  const int* cindex;
+  const int* kkt_dest;
+  const int* f_dest;
+  const long long* out_base;  // affine variant: absolute byte address of output slot k for rel = 0
+  const int* out_stride;      // affine variant: byte stride of output slot k per application
   double obj_scale;
-  int rel_begin, rel_end;
+  int begin, end;
+};
+
+// Destination of one output of the affine variant, in emission order: element base + rel*stride of array `arr`
+// (0 X, 1 L, 2 KKT values, 3 FX block, 4 staging buffer).  The plan turns these into the absolute address table.
+struct JitOut {
+  int arr;
+  long long base, stride;
 };
 
 // PTX text of the kernel; throws std::runtime_error when the function cannot be specialised (mixed direct/staged
 // destinations inside the affine range, offsets out of range).
-std::string emit_ptx(const Program& P, const JitSpec& spec, const AffineMaps& am);
+std::string emit_ptx(const Program& P, const JitSpec& spec, const AffineMaps& am /* unused when spec.indexed */,
+                     std::vector<JitOut>* outs = nullptr);
 
 // Assembles PTX for sm_100a.  Works without a GPU (used by the CPU-side tests).  Returns false and fills `log` on error.
 bool assemble_ptx(const std::string& ptx, std::vector<char>& cubin, std::string& log, int* nregs = nullptr,
@@ -55,6 +74,8 @@ struct JitKernel {
   cudaLibrary_t lib = nullptr;
   cudaKernel_t kern = nullptr;
   int nthreads = 0;
+  long long* out_base = nullptr;  // device tables of the affine variant (owned by the plan)
+  int* out_stride = nullptr;
   int nregs = 0;        // from the assembler's report (0 if unknown)
   int spill_bytes = 0;  // spill stores + loads per thread
   bool ok() const { return kern != nullptr; }

@@ -34,8 +34,12 @@ T* Plan::dupload(const std::vector<T>& v) {
 }
 
 Plan::~Plan() {
-  for (auto& a: jits)
-    for (JitKernel& k: a) unload_jit(k);
+  for (auto& v: jits)
+    for (auto& a: v)
+      for (JitKernel& k: a) unload_jit(k);
+  if (ev_fork) cudaEventDestroy(ev_fork);
+  if (ev_join) cudaEventDestroy(ev_join);
+  if (side) cudaStreamDestroy(side);
   for (cudaEvent_t e: prof_events) cudaEventDestroy(e);
   for (void* p: owned) cudaFree(p);
   if (stream) cudaStreamDestroy(stream);
@@ -120,8 +124,13 @@ int Plan::build(int dev) {
   progs.clear();
   affs.clear();
   host_progs.clear();
-  jits.clear();
-  jit_state.clear();
+  for (int v = 0; v < 2; v++) {
+    jits[v].clear();
+    jit_state[v].clear();
+  }
+  AB_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+  AB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  AB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   if (const char* e = getenv("ASSET_B200_JIT")) use_jit = std::atoi(e) != 0;
   if (const char* e = getenv("ASSET_B200_JIT_MIN")) jit_min_apps = std::max(1, std::atoi(e));
   for (int fi: prob.order) {
@@ -172,8 +181,10 @@ int Plan::build(int dev) {
     progs.push_back(pd);
     host_progs.push_back(std::move(hp));
     affs.push_back(am);
-    jits.emplace_back();
-    jit_state.push_back({0, 0, 0, 0, 0});
+    for (int v = 0; v < 2; v++) {
+      jits[v].emplace_back();
+      jit_state[v].push_back({0, 0, 0, 0, 0});
+    }
     f.aff_begin = am.a0;
     f.aff_end = am.a1;
     f.ir = fr.ir;
@@ -266,26 +277,29 @@ std::mutex g_cubin_mu;
 std::unordered_map<std::string, CubinEntry> g_cubins;
 }  // namespace
 
-int Plan::ensure_jit(size_t k, int fm) {
+int Plan::ensure_jit(size_t k, int fm, int variant) {
   if (!use_jit) return 0;
-  signed char& st = jit_state[k][fm];
+  signed char& st = jit_state[variant][k][fm];
   if (st != 0) return st > 0 ? 1 : 0;
   st = -1;
   const AffineMaps& am = affs[k];
-  if (am.a1 - am.a0 < jit_min_apps) return 0;
+  if (variant == 0 && am.a1 - am.a0 < jit_min_apps) return 0;
   const FuncRec& fr = prob.funcs[prob.order[k]];
   JitSpec sp;
-  sp.name = "ab_seg_f" + std::to_string(k) + "_m" + std::to_string(fm);
+  sp.name = std::string(variant ? "ab_idx_f" : "ab_seg_f") + std::to_string(k) + "_m" + std::to_string(fm);
   sp.role = fr.role;
   sp.ir = fr.ir;
   sp.orows = fr.orows;
   sp.nappconst = fr.nappconst;
+  sp.E = fr.triplets_per_app();
+  sp.indexed = variant == 1;
   sp.g_stage = fns[k].g_stage;
   sp.v_stage = fns[k].v_stage;
   sp.nthreads = 64;
   std::string ptx;
+  std::vector<JitOut> outs;
   try {
-    ptx = emit_ptx(host_progs[k][fm], sp, am);
+    ptx = emit_ptx(host_progs[k][fm], sp, am, &outs);
   } catch (const std::exception& e) {
     jit_log = std::string(e.what()) + " (" + fr.name + ")";
     return 0;
@@ -310,11 +324,29 @@ int Plan::ensure_jit(size_t k, int fm) {
     std::lock_guard<std::mutex> lk(g_cubin_mu);
     g_cubins.emplace(ptx, ce);
   }
-  JitKernel& jk = jits[k][fm];
+  JitKernel& jk = jits[variant][k][fm];
   cudaError_t e = load_jit(ce.cubin, sp.name, jk);
   if (e != cudaSuccess) {
     last_error = "loading the specialised kernel of " + fr.name + ": " + cudaGetErrorString(e);
     return -(int) e;
+  }
+  if (variant == 0) {
+    // absolute destination table of the cooperative stores (padded to whole 32-output tiles)
+    const size_t n = (outs.size() + 31) / 32 * 32;
+    std::vector<long long> tb(n, 0);
+    std::vector<int> ts(n, 0);
+    for (size_t q = 0; q < outs.size(); q++) {
+      const JitOut& w = outs[q];
+      double* arr = (w.arr == 2) ? d_kkt : (w.arr == 3) ? ((fr.role == ROLE_EQ) ? d_fxe : d_fxi) : d_stage;
+      tb[q] = (long long) (uintptr_t) arr + w.base * 8;
+      ts[q] = (int) (w.stride * 8);
+    }
+    jk.out_base = dupload(tb);
+    jk.out_stride = dupload(ts);
+    if (!jk.out_base || !jk.out_stride) {
+      last_error = "out of device memory for the output table of " + fr.name;
+      return -(int) cudaErrorMemoryAllocation;
+    }
   }
   jk.nthreads = sp.nthreads;
   jk.nregs = ce.nregs;
@@ -346,9 +378,25 @@ int Plan::eval(int mode, double obj_scale) {
     AB_CUDA(cudaMemsetAsync(d_kkt, 0, sizeof(double) * (size_t) prob.nnz(), stream));
     AB_CUDA(cudaMemsetAsync(d_stage, 0, sizeof(double) * (size_t) prob.stage_solver, stream));
   }
+  // Every function writes its own outputs (shared entries go through the staging buffer), so the launches are
+  // independent: the bulk kernels run back to back on `stream`, the small ones (mesh ends, functions with a handful of
+  // applications) overlap them on `side`.  With per-launch profiling on everything is serialised on `stream`.
+  const bool overlap = !profiling;
+  bool forked = false;
+  auto small_stream = [&]() -> cudaStream_t {
+    if (!overlap) return stream;
+    if (!forked) {
+      cudaEventRecord(ev_fork, stream);
+      cudaStreamWaitEvent(side, ev_fork, 0);
+      forked = true;
+    }
+    return side;
+  };
   for (const FnDev& f: fns) {
     int fm = (f.role == ROLE_OBJ) ? obj_mode : con_mode;
     if (fm < 0) continue;
+    const size_t k = (size_t) (&f - fns.data());
+    const std::string& name = prob.funcs[prob.order[k]].name;
     EvalIO io;
     io.X = d_X;
     io.L = (f.role == ROLE_EQ) ? d_LE : d_LI;
@@ -356,58 +404,72 @@ int Plan::eval(int mode, double obj_scale) {
     io.kkt = d_kkt;
     io.fx = (f.role == ROLE_EQ) ? d_fxe : d_fxi;
     io.stage = d_stage;
-    if (int rc = prof_begin(prob.funcs[prob.order[&f - fns.data()]].name)) return rc;
     FnDev fd = f;
-    fd.prog = progs[&f - fns.data()][fm];
+    fd.prog = progs[k][fm];
     if (fd.prog.nthreads == 0) {
       last_error = "no device program for this mode";
       return (int) cudaErrorInvalidValue;
     }
-    const size_t k = (size_t) (&f - fns.data());
-    const int jr = ensure_jit(k, fm);
-    if (jr < 0) return -jr;
-    if (jr > 0) {
-      // interior segments on the specialised kernel, mesh ends on the interpreter
-      const int a0 = affs[k].a0, a1 = affs[k].a1;
-      const int jb = std::max(a0, f.app_begin), je = std::min(a1, f.app_end);
-      JitArgs ja;
-      ja.X = io.X;
-      ja.L = io.L;
-      ja.kkt = io.kkt;
-      ja.fx = io.fx;
-      ja.stage = io.stage;
-      ja.appconst = f.appconst;
-      ja.obj_scale = obj_scale;
-      ja.rel_begin = jb - a0;
-      ja.rel_end = je - a0;
-      if (je > jb) {
-        AB_CUDA(launch_jit(jits[k][fm], ja, stream));
-        launches++;
+    JitArgs ja;
+    ja.X = io.X;
+    ja.L = io.L;
+    ja.kkt = io.kkt;
+    ja.fx = io.fx;
+    ja.stage = io.stage;
+    ja.appconst = f.appconst;
+    ja.vindex = f.vindex;
+    ja.cindex = f.cindex;
+    ja.kkt_dest = f.kkt_dest;
+    ja.f_dest = f.f_dest;
+    ja.out_base = nullptr;
+    ja.out_stride = nullptr;
+    ja.obj_scale = obj_scale;
+    // applications [b, e) that are not covered by the affine kernel: indexed kernel, else the interpreter
+    auto rest = [&](int b, int e, const char* suffix) -> int {
+      if (e <= b) return 0;
+      if (int rc = prof_begin(name + suffix)) return rc;
+      const int jr = ensure_jit(k, fm, 1);
+      if (jr < 0) return -jr;
+      cudaStream_t st = (e - b <= 4096) ? small_stream() : stream;
+      if (jr > 0) {
+        JitArgs a = ja;
+        a.begin = b;
+        a.end = e;
+        AB_CUDA(launch_jit(jits[1][k][fm], a, st));
         jit_launches++;
-      }
-      const int hb = f.app_begin, he = std::min(f.app_end, std::max(jb, f.app_begin));
-      if (je <= jb) {
-        AB_CUDA(launch_eval(fd, stream, io));
-        launches++;
       } else {
-        if (he > hb) {
-          FnDev h = fd;
-          h.app_end = he;
-          AB_CUDA(launch_eval(h, stream, io));
-          launches++;
-        }
-        if (f.app_end > je) {
-          FnDev t = fd;
-          t.app_begin = je;
-          AB_CUDA(launch_eval(t, stream, io));
-          launches++;
-        }
+        FnDev h = fd;
+        h.app_begin = b;
+        h.app_end = e;
+        AB_CUDA(launch_eval(h, st, io));
       }
-    } else {
-      AB_CUDA(launch_eval(fd, stream, io));
       launches++;
+      return prof_end();
+    };
+    const int jr = ensure_jit(k, fm, 0);
+    if (jr < 0) return -jr;
+    const int a0 = affs[k].a0, a1 = affs[k].a1;
+    const int jb = std::max(a0, f.app_begin), je = std::min(a1, f.app_end);
+    if (jr > 0 && je > jb) {
+      if (int rc = prof_begin(name)) return rc;
+      JitArgs a = ja;
+      a.begin = jb - a0;
+      a.end = je - a0;
+      a.out_base = jits[0][k][fm].out_base;
+      a.out_stride = jits[0][k][fm].out_stride;
+      AB_CUDA(launch_jit(jits[0][k][fm], a, stream));
+      launches++;
+      jit_launches++;
+      if (int rc = prof_end()) return rc;
+      if (int rc = rest(f.app_begin, jb, ":ends")) return rc;
+      if (int rc = rest(je, f.app_end, ":ends")) return rc;
+    } else {
+      if (int rc = rest(f.app_begin, f.app_end, "")) return rc;
     }
-    if (int rc = prof_end()) return rc;
+  }
+  if (forked) {
+    AB_CUDA(cudaEventRecord(ev_join, side));
+    AB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
   }
   auto G = [&](DevGather& g, double* out, const char* label) -> int {
     const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);

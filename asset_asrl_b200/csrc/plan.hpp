@@ -44,10 +44,13 @@ struct Plan {
   int jit_min_apps = 32;  // ASSET_B200_JIT_MIN: smallest affine range worth a specialised kernel
   std::vector<AffineMaps> affs;                        // per function
   std::vector<std::array<Program, 5>> host_progs;      // unlinked programs, kept for the specialiser
-  std::vector<std::array<JitKernel, 5>> jits;          // per function, per FnMode
-  std::vector<std::array<signed char, 5>> jit_state;   // 0 not tried, 1 ready, -1 not specialisable
-  std::string jit_log;                                 // why the last refused specialisation was refused
-  int ensure_jit(size_t k, int fm);                    // returns 1 ready, 0 use the interpreter, < 0 CUDA error (negated)
+  // [0] affine variant (bulk of the mesh), [1] indexed variant (mesh ends, functions without an affine range)
+  std::vector<std::array<JitKernel, 5>> jits[2];          // per function, per FnMode
+  std::vector<std::array<signed char, 5>> jit_state[2];   // 0 not tried, 1 ready, -1 not specialisable
+  std::string jit_log;                                    // why the last refused specialisation was refused
+  int ensure_jit(size_t k, int fm, int variant);  // returns 1 ready, 0 use the interpreter, < 0 CUDA error (negated)
+  cudaStream_t side = nullptr;  // the small launches (mesh ends, single applications) overlap the bulk kernels here
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   long long jit_launches = 0;                          // specialised-kernel launches of the last eval
 
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;

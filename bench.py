@@ -175,7 +175,6 @@ def run_b200(a):
     for _ in range(a.warmup):
         nlp.eval_device(EVAL_KKT, 1.0)
     nlp.sync()
-    nlp.profile(2)  # accumulate per-launch event pairs over the timed region
     clocks = ClockSampler(local)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -190,9 +189,15 @@ def run_b200(a):
     w1 = time.time()
     ms_total = e0.elapsed_time(e1)
     launches = nlp.launches() * a.steps
+    specialised = nlp.specialised_launches() * a.steps
+    clk = clocks.stop(w0, w1)
+    # per-launch device times: a second pass with an event pair around every launch (this serialises the small
+    # launches that overlap the bulk kernels in the timed region above, so it is kept out of it)
+    nlp.profile(2)
+    for _ in range(max(1, min(a.steps, 5))):
+        nlp.eval_device(EVAL_KKT, 1.0)
     prof = nlp.profile_times()
     nlp.profile(0)
-    clk = clocks.stop(w0, w1)
     if world > 1:
         t = torch.tensor([ms_total], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -278,7 +283,7 @@ def run_b200(a):
                            "kkt_evals_per_sec": 1e3 / ms_step,
                            "l2": f"no flush: per-eval working set {b_alg_eval / 1e6:.0f} MB of values (+ index maps) > 126 MB L2",
                            "setup_s": round(t_setup, 2)},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "specialised_launches": specialised, "clocks": clk,
                 "kernels_ms": kernels}
         print(json.dumps(line), flush=True)
     if world > 1:

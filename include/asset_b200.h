@@ -86,11 +86,12 @@ long long ab_problem_tape_describe(const ab_problem* p, int t, char* buf, long l
 int ab_problem_program_stats(const ab_problem* p, int f, int mode, long long out[8]);
 /* Copies the (unlinked) program: 4 * bundles 16-byte instructions (asset_asrl_b200/csrc/expr.hpp: PInstr) and the constants. */
 int ab_problem_program_code(const ab_problem* p, int f, int mode, void* code, double* consts);
-/* PTX text of the specialised kernel the plan would assemble for function `f` in `mode` (asset_asrl_b200/csrc/jit.hpp);
+/* PTX text of the specialised kernel the plan would assemble for function `f` in `mode` (asset_asrl_b200/csrc/jit.hpp):
+ * `indexed` = 0 the affine variant run over the bulk of the mesh, 1 the indexed variant run over the mesh ends;
  * returns the full length, 0 if the function has no affine application range, or a negative status.
  * ab_problem_analyze() must have run.  ab_ptx_assemble assembles PTX for sm_100a in-process (no GPU needed):
  * out[0..2] = cubin bytes, registers per thread, spill bytes per thread. */
-long long ab_problem_kernel_ptx(const ab_problem* p, int f, int mode, char* buf, long long cap);
+long long ab_problem_kernel_ptx(const ab_problem* p, int f, int mode, int indexed, char* buf, long long cap);
 int ab_ptx_assemble(const char* ptx, long long out[3]);
 /* copies n_instr 16-byte instructions (see asset_asrl_b200/csrc/tape.h) */
 int ab_problem_tape_code(const ab_problem* p, int t, void* out);

@@ -33,6 +33,13 @@ struct JitSpec {
   long long g_stage = 0;  // gradient contributions go to stage[g_stage + app*ir + i]
   long long v_stage = 0;  // objective value contributions go to stage[v_stage + app]
   int nthreads = 128;     // block size (.maxntid)
+  int reg_budget = 96;    // affine variant: values kept in registers; the rest are parked in shared memory
+};
+
+struct JitStats {
+  unsigned smem_bytes = 0;  // dynamic shared memory per block (transposition tile + parked values)
+  int parked_slots = 0;     // lane-private shared-memory slots
+  int parks = 0, reloads = 0;
 };
 
 // Kernel parameters, in order (see launch_jit).  begin/end: application range, relative to the first affine
@@ -64,7 +71,7 @@ struct JitOut {
 // PTX text of the kernel; throws std::runtime_error when the function cannot be specialised (mixed direct/staged
 // destinations inside the affine range, offsets out of range).
 std::string emit_ptx(const Program& P, const JitSpec& spec, const AffineMaps& am /* unused when spec.indexed */,
-                     std::vector<JitOut>* outs = nullptr);
+                     std::vector<JitOut>* outs = nullptr, JitStats* stats = nullptr);
 
 // Assembles PTX for sm_100a.  Works without a GPU (used by the CPU-side tests).  Returns false and fills `log` on error.
 bool assemble_ptx(const std::string& ptx, std::vector<char>& cubin, std::string& log, int* nregs = nullptr,
@@ -74,6 +81,7 @@ struct JitKernel {
   cudaLibrary_t lib = nullptr;
   cudaKernel_t kern = nullptr;
   int nthreads = 0;
+  unsigned smem_bytes = 0;        // dynamic shared memory per block (set before load_jit)
   long long* out_base = nullptr;  // device tables of the affine variant (owned by the plan)
   int* out_stride = nullptr;
   int nregs = 0;        // from the assembler's report (0 if unknown)

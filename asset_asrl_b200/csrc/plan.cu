@@ -1,5 +1,6 @@
 #include "plan.hpp"
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -298,8 +299,10 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
   sp.nthreads = 64;
   std::string ptx;
   std::vector<JitOut> outs;
+  JitStats js;
+  if (const char* e = getenv("ASSET_B200_JIT_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
   try {
-    ptx = emit_ptx(host_progs[k][fm], sp, am, &outs);
+    ptx = emit_ptx(host_progs[k][fm], sp, am, &outs, &js);
   } catch (const std::exception& e) {
     jit_log = std::string(e.what()) + " (" + fr.name + ")";
     return 0;
@@ -325,6 +328,7 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
     g_cubins.emplace(ptx, ce);
   }
   JitKernel& jk = jits[variant][k][fm];
+  jk.smem_bytes = js.smem_bytes;
   cudaError_t e = load_jit(ce.cubin, sp.name, jk);
   if (e != cudaSuccess) {
     last_error = "loading the specialised kernel of " + fr.name + ": " + cudaGetErrorString(e);
@@ -348,6 +352,10 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
       return -(int) cudaErrorMemoryAllocation;
     }
   }
+  if (getenv("ASSET_B200_JIT_VERBOSE"))
+    fprintf(stderr, "[asset_b200] %s (%s): %d regs, %d B assembler spill, %u B smem/block, %d parked slots, %d parks, %d reloads, cubin %zu B\n",
+            sp.name.c_str(), fr.name.c_str(), ce.nregs, ce.spill, js.smem_bytes, js.parked_slots, js.parks, js.reloads,
+            ce.cubin.size());
   jk.nthreads = sp.nthreads;
   jk.nregs = ce.nregs;
   jk.spill_bytes = ce.spill;

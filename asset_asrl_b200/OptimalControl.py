@@ -412,33 +412,242 @@ class ODEPhase:
         return nlp.NLPTest(self.makeSolverInput(), n)
 
 
+class LinkFlags(_Enum):
+    """OptimalControlFlags.h LinkFlags: which phase regions a two-phase link function reads."""
+    BackToFront, BackToBack, FrontToBack, FrontToFront, ParamsToParams, PathToPath, LinkParams, ReadRegions = range(8)
+    _regions = {0: (2, 1), 1: (2, 2), 2: (1, 2), 3: (1, 1), 4: (12, 12), 5: (5, 5), 6: ()}
+
+
+class _LinkFunction:
+    """LinkFunction<FuncType> (/root/reference/src/OptimalControl/LinkFunction.h:11-300): a function applied once per
+    entry of ``ptl`` to the concatenation of one region of each listed phase and some link parameters."""
+
+    def __init__(self, fun, flag, regs, ptl, xtv, opv, spv, lv):
+        self.fun, self.flag, self.regs = fun, flag, [PhaseRegionFlags.parse(r) for r in regs]
+        self.ptl = [[int(p) for p in col] for col in ptl]
+        self.xtv, self.opv, self.spv = [_idx(v) for v in xtv], [_idx(v) for v in opv], [_idx(v) for v in spv]
+        self.lv = [_idx(v) for v in lv]
+        ncols = max(len(self.ptl), len(self.lv))
+        if not self.lv:
+            self.lv = [[] for _ in range(ncols)]
+        if not self.ptl:
+            self.ptl = [[] for _ in range(ncols)]
+        for col in self.ptl:
+            if len(col) != len(self.regs):
+                raise ValueError("every entry of PhasesToLink must name one phase per region")
+        if not (len(self.xtv) == len(self.opv) == len(self.spv) == len(self.regs)):
+            raise ValueError("one XtUVars / OPVars / SPVars list per linked region is required")
+
+
 class OptimalControlProblem:
-    """Multi-phase problem: phase offsets and one shared NonLinearProgram (OptimalControlProblem.cpp:115-155)."""
+    """Multi-phase problem: phase offsets, link parameters, link functions and one shared NonLinearProgram
+    (OptimalControlProblem.cpp:115-155 transcribe_phases, :271-387 transcribe_links, :659-764 make_link_Vindex_Cindex).
+    Variable order: every phase's variables, then the link parameters; link constraint rows follow all phase rows."""
 
     def __init__(self):
         self.Phases = []
         self.nlp = None
+        self._linkparams = np.zeros(0)
+        self._links = {1: [], 2: [], 0: []}  # role -> [_LinkFunction]; insertion order (the reference's std::map by index)
 
     def addPhase(self, ph):
         self.Phases.append(ph)
         return len(self.Phases) - 1
+
+    def getPhaseNum(self, ph):
+        if isinstance(ph, (int, np.integer)):
+            n = int(ph)
+            return n + len(self.Phases) if n < 0 else n
+        for k, q in enumerate(self.Phases):
+            if q is ph:
+                return k
+        raise ValueError("phase is not part of this OptimalControlProblem")
+
+    # ------------------------------------------------------------------ link parameters
+    def setLinkParams(self, parm, units=None):
+        self._linkparams = np.asarray(parm, dtype=np.float64).ravel().copy()
+        self.nlp = None
+
+    def returnLinkParams(self):
+        return self._linkparams.copy()
+
+    # ------------------------------------------------------------------ link functions
+    def _make_link(self, fun, *a):
+        """Argument forms of the reference (OptimalControlProblem.h:371-493, :685-817):
+        (fun, packs, lv) with packs = [(phase, region, XtUVars, OPVars, SPVars), ...];
+        (fun, p0, reg0, v0, p1, reg1, v1[, lv]);  (fun, p0, reg0, XtUV0, OPV0, SPV0, p1, reg1, XtUV1, OPV1, SPV1[, lv]);
+        (fun, LinkFlag, PTL, XtUVars[, OPVars, SPVars][, LinkParams]) -- the flag/PTL interface with many columns."""
+        if not isinstance(fun, VectorFunction):
+            raise TypeError("expected a VectorFunction")
+        if a and isinstance(a[0], (list, tuple)) and a[0] and isinstance(a[0][0], (list, tuple)) and len(a[0][0]) == 5:
+            packs, lv = a[0], (a[1] if len(a) > 1 else [])
+            phs = [self.getPhaseNum(pk[0]) for pk in packs]
+            return _LinkFunction(fun, LinkFlags.ReadRegions, [pk[1] for pk in packs], [phs], [pk[2] for pk in packs],
+                                 [pk[3] for pk in packs], [pk[4] for pk in packs], [lv])
+        def is_seq(q):
+            return isinstance(q, (list, tuple, range, np.ndarray))
+        flag_form = bool(a) and len(a) >= 2 and is_seq(a[1]) and len(a[1]) > 0 and is_seq(a[1][0]) and (
+            (isinstance(a[0], str) and a[0] in LinkFlags.__dict__) or isinstance(a[0], (int, np.integer)))
+        if flag_form:
+            flag = LinkFlags.parse(a[0])
+            regs = LinkFlags._regions[flag]
+            ptl = [[self.getPhaseNum(p) for p in col] for col in a[1]]
+            rest = list(a[2:])
+            nreg = len(regs)
+
+            def per_region(v):
+                v = list(v)
+                if nreg and len(v) == nreg and all(isinstance(q, (list, tuple, range, np.ndarray)) for q in v):
+                    return [list(q) for q in v]
+                return [list(v) for _ in range(nreg)]
+            xtv = per_region(rest[0]) if rest else [[] for _ in range(nreg)]
+            opv = per_region(rest[1]) if len(rest) >= 4 else [[] for _ in range(nreg)]
+            spv = per_region(rest[2]) if len(rest) >= 4 else [[] for _ in range(nreg)]
+            lv = rest[3] if len(rest) >= 4 else (rest[1] if len(rest) == 2 else [])
+            return _LinkFunction(fun, flag, regs, ptl, xtv, opv, spv, lv)
+        if len(a) in (6, 7):
+            p0, r0, v0, p1, r1, v1 = a[:6]
+            lv = a[6] if len(a) == 7 else []
+
+            def split(reg, v):
+                reg = PhaseRegionFlags.parse(reg)
+                if reg == PhaseRegionFlags.ODEParams:
+                    return [], v, []
+                if reg == PhaseRegionFlags.StaticParams:
+                    return [], [], v
+                return v, [], []
+            x0, o0, s0 = split(r0, v0)
+            x1, o1, s1 = split(r1, v1)
+            return self._make_link(fun, [(p0, r0, x0, o0, s0), (p1, r1, x1, o1, s1)], lv)
+        if len(a) in (10, 11):
+            lv = a[10] if len(a) == 11 else []
+            return self._make_link(fun, [tuple(a[0:5]), tuple(a[5:10])], lv)
+        raise TypeError("unrecognised link function arguments")
+
+    def _add_link(self, role, lf):
+        self._links[role].append(lf)
+        self.nlp = None
+        return len(self._links[role]) - 1
+
+    def addLinkEqualCon(self, fun, *a):
+        return self._add_link(1, self._make_link(fun, *a))
+
+    def addLinkInequalCon(self, fun, *a):
+        return self._add_link(2, self._make_link(fun, *a))
+
+    def addLinkObjective(self, fun, *a):
+        if fun.ORows() != 1:
+            raise ValueError("a link objective must be scalar")
+        return self._add_link(0, self._make_link(fun, *a))
+
+    def _lp_link(self, fun, lpvs):
+        lpvs = list(lpvs)
+        if lpvs and not isinstance(lpvs[0], (list, tuple, range, np.ndarray)):
+            lpvs = [lpvs]
+        return _LinkFunction(fun, LinkFlags.LinkParams, [], [], [], [], [], lpvs)
+
+    def addLinkParamEqualCon(self, fun, lpvs):
+        """fun applied to link parameters only, once per entry of lpvs (OptimalControlProblem.h:671-680, :825-834)."""
+        return self._add_link(1, self._lp_link(fun, lpvs))
+
+    def addLinkParamInequalCon(self, fun, lpvs):
+        return self._add_link(2, self._lp_link(fun, lpvs))
+
+    def addLinkParamObjective(self, fun, lpvs):
+        return self._add_link(0, self._lp_link(fun, lpvs))
+
+    def addForwardLinkEqualCon(self, iphase, fphase, vars_):
+        """x_back(phase i) - x_front(phase i+1) = 0 for i in [iphase, fphase) (OptimalControlProblem.h:580-610)."""
+        i0, i1 = self.getPhaseNum(iphase), self.getPhaseNum(fphase)
+        v = _idx(vars_)
+        args = Arguments(2 * len(v))
+        fun = args.head(len(v)) - args.tail(len(v))
+        return [self.addLinkEqualCon(fun, i, "Last", v, i + 1, "First", v) for i in range(i0, i1)]
+
+    def addDirectLinkEqualCon(self, *a):
+        """(p0, reg0, v0, p1, reg1, v1): v0 of region reg0 of p0 equals v1 of reg1 of p1 (OptimalControlProblem.h:614-635);
+        (fun, p0, reg0, v0, p1, reg1, v1) is the same as addLinkEqualCon."""
+        if isinstance(a[0], VectorFunction):
+            return self.addLinkEqualCon(*a)
+        p0, r0, v0, p1, r1, v1 = a
+        n = len(_idx(v0))
+        args = Arguments(2 * n)
+        return self.addLinkEqualCon(args.head(n) - args.tail(n), p0, r0, v0, p1, r1, v1)
+
+    # ------------------------------------------------------------------ transcription
+    def _region_vindex(self, pnum, reg, x, o, s):
+        ph = self.Phases[pnum]
+        xa, xp = _lib.iarr(x)
+        oa, op = _lib.iarr(o)
+        sa, sp = _lib.iarr(s)
+        dims = (C.c_int * 2)()
+        _lib.check(lib.ab_phase_region_vindex(ph.h, reg, xp, len(xa), op, len(oa), sp, len(sa), None, 0, dims))
+        V = np.zeros((dims[0], dims[1]), dtype=np.int32)
+        if V.size:
+            _lib.check(lib.ab_phase_region_vindex(ph.h, reg, xp, len(xa), op, len(oa), sp, len(sa),
+                                                  V.ctypes.data_as(C.POINTER(C.c_int)), V.size, dims))
+        return V
+
+    def _link_vindex(self, lf, lp0):
+        """make_link_Vindex_Cindex (OptimalControlProblem.cpp:659-764): [napplications][IRows] variable indices."""
+        if lf.flag == LinkFlags.PathToPath:
+            cols = []
+            for col in lf.ptl:
+                parts = [self._region_vindex(col[j], lf.regs[j], lf.xtv[j], lf.opv[j], lf.spv[j]) for j in range(len(lf.regs))]
+                if any(p.shape[0] != parts[0].shape[0] for p in parts):
+                    raise ValueError("Phases cannot be linked path to path")
+                cols.append(np.concatenate(parts, axis=1))
+            return np.concatenate(cols, axis=0)
+        rows = []
+        for i in range(max(len(lf.ptl), len(lf.lv))):
+            parts = []
+            for j in range(len(lf.regs)):
+                V = self._region_vindex(lf.ptl[i][j], lf.regs[j], lf.xtv[j], lf.opv[j], lf.spv[j])
+                if V.shape[0] != 1:
+                    raise ValueError("link functions read single-application regions (Front, Back, Params, ...)")
+                parts.append(V[0])
+            lv = np.asarray(lf.lv[i], dtype=np.int32)
+            if lv.size and (lv.min() < 0 or lv.max() >= self._linkparams.size):
+                raise ValueError("link function references a non-existent link parameter")
+            parts.append(lp0 + lv)
+            rows.append(np.concatenate(parts).astype(np.int32))
+        return np.stack(rows, axis=0)
 
     def transcribe(self, showstats=False, showfuns=False):
         nlp = NonLinearProgram()
         v = e = i = 0
         self.offsets = []
         for ph in self.Phases:
+            if not ph.h:
+                raise RuntimeError("setTraj must be called on every phase before transcribe")
             out = (C.c_int * 3)()
             _lib.check(lib.ab_phase_transcribe(ph.h, nlp.h, v, e, i, out))
             self.offsets.append((v, e, i))
             v, e, i = v + out[0], e + out[1], i + out[2]
-        nlp.set_dims(v, e, i)
+        self.LinkParamLocs = v + np.arange(self._linkparams.size)
+        lp0 = v
+        v += self._linkparams.size
+        nxt = {1: e, 2: i}
+        # equalities, inequalities, objectives -- the order of transcribe_links; rows are numbered application-major
+        for role in (1, 2, 0):
+            for lf in self._links[role]:
+                V = self._link_vindex(lf, lp0)
+                if V.shape[1] != lf.fun.IRows():
+                    raise ValueError(f"link function expects {lf.fun.IRows()} inputs but its regions supply {V.shape[1]}")
+                tape = nlp.add_tape(lf.fun)
+                cidx = None
+                if role:
+                    n = V.shape[0] * lf.fun.ORows()
+                    cidx = (nxt[role] + np.arange(n, dtype=np.int32)).reshape(V.shape[0], lf.fun.ORows())
+                    nxt[role] += n
+                nlp.add_function(role, tape, lf.fun.is_linear(), V, cidx)
+        nlp.set_dims(v, nxt[1], nxt[2])
         nlp.analyze()
         self.nlp = nlp
         return nlp
 
     def makeSolverInput(self):
-        return np.concatenate([ph.makeSolverInput() for ph in self.Phases])
+        return np.concatenate([ph.makeSolverInput() for ph in self.Phases] + [self._linkparams])
 
     def optimize(self, *a, **k):
         raise NotImplementedError("PSIOPT is out of scope for this build; use ocp.transcribe() and nlp.evalKKT(...)")

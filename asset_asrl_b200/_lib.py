@@ -71,6 +71,7 @@ SIGNATURES = {
     "ab_phase_dims": (_i, [_vp, _ip]),
     "ab_phase_state_spacing": (_i, [_vp, _dp]),
     "ab_phase_transcribe": (_i, [_vp, _vp, _i, _i, _i, _ip]),
+    "ab_phase_region_vindex": (_i, [_vp, _i, _ip, _i, _ip, _i, _ip, _i, _ip, _i, _ip]),
     "ab_phase_make_input": (_i, [_vp, _dp, _dp, _dp]),
     "ab_plan_create": (_i, [_vp, _i, C.POINTER(_vp)]),
     "ab_plan_destroy": (None, [_vp]),

@@ -482,6 +482,23 @@ int ab_phase_transcribe(ab_phase* ph, ab_problem* p, int voff, int eoff, int iof
   return AB_OK;
   AB_CATCH
 }
+int ab_phase_region_vindex(ab_phase* ph, int region, const int* xtuv, int nxtuv, const int* opv, int nopv, const int* spv,
+                           int nspv, int* vindex, int cap, int out[2]) {
+  AB_TRY
+  // PhaseIndexer::make_Vindex_Cindex(reg, xtv, opv, spv, 1)[0] as OptimalControlProblem::make_link_Vindex_Cindex calls it
+  // (OptimalControlProblem.cpp:688-689, :745-746); valid after ab_phase_transcribe, which fixed the phase's offsets.
+  std::vector<int> x(xtuv, xtuv + nxtuv), o(opv, opv + nopv), s(spv, spv + nspv), V, Cx;
+  int next = 0, nappl = 0;
+  ph->ph.idx.make_vindex_cindex(region, x, o, s, 0, next, V, Cx, nappl);
+  out[0] = nappl;
+  out[1] = nappl > 0 ? (int) (V.size() / (size_t) nappl) : 0;
+  if (vindex) {
+    if ((size_t) cap < V.size()) return fail(AB_ERR_INVALID, "ab_phase_region_vindex: buffer too small");
+    std::memcpy(vindex, V.data(), V.size() * sizeof(int));
+  }
+  return AB_OK;
+  AB_CATCH
+}
 int ab_phase_make_input(ab_phase* ph, const double* traj, const double* sp, double* X) {
   AB_TRY
   ph->ph.init_indexing();

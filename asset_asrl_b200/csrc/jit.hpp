@@ -34,6 +34,9 @@ struct JitSpec {
   long long v_stage = 0;  // objective value contributions go to stage[v_stage + app]
   int nthreads = 128;     // block size (.maxntid)
   int reg_budget = 96;    // affine variant: values kept in registers; the rest are parked in shared memory
+  bool lockstep = false;        // bar.sync at every output flush: the warps of a block share instruction-cache fills
+  bool prefetch_table = true;   // output-table entries of the next flush are loaded one flush ahead
+  bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)
 };
 
 struct JitStats {

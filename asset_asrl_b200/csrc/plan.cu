@@ -301,6 +301,10 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
   std::vector<JitOut> outs;
   JitStats js;
   if (const char* e = getenv("ASSET_B200_JIT_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
+  if (const char* e = getenv("ASSET_B200_JIT_THREADS")) sp.nthreads = std::max(32, std::atoi(e) / 32 * 32);
+  if (const char* e = getenv("ASSET_B200_JIT_LOCKSTEP")) sp.lockstep = std::atoi(e) != 0;
+  if (const char* e = getenv("ASSET_B200_JIT_PREFETCH")) sp.prefetch_table = std::atoi(e) != 0;
+  if (const char* e = getenv("ASSET_B200_JIT_HOIST")) sp.hoist_loads = std::atoi(e) != 0;
   try {
     ptx = emit_ptx(host_progs[k][fm], sp, am, &outs, &js);
   } catch (const std::exception& e) {

@@ -112,6 +112,11 @@ int ab_phase_state_spacing(ab_phase* ph, double* out /* numStates */);
 /* Appends the phase's functions to `p` with variable / equality / inequality offsets; out = {numPhaseVars, numEq, numIq}. */
 int ab_phase_transcribe(ab_phase* ph, ab_problem* p, int voff, int eoff, int ioff, int out[3]);
 /* PhaseIndexer::makeSolverInput (PhaseIndexer.cpp:412-445): traj is [numStates][XtUVars + PVars]. */
+/* Global variable indices of a phase region ([nappl][ir], out = {nappl, ir}); vindex == NULL only sizes.  Replaces
+ * PhaseIndexer::make_Vindex_Cindex as called for link functions (src/OptimalControl/OptimalControlProblem.cpp:659-764).
+ * Valid after ab_phase_transcribe (the phase's variable offset is fixed there). */
+int ab_phase_region_vindex(ab_phase* ph, int region, const int* xtuv, int nxtuv, const int* opv, int nopv, const int* spv,
+                           int nspv, int* vindex, int cap, int out[2]);
 int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_params, double* X);
 
 /* ---------------- device plan ---------------- */

@@ -109,6 +109,65 @@ def phase_zoo():
         zoo[f"regions_{mode}"] = (lambda mode=mode: regions(mode))
     zoo["regions_LGL5_block_constant"] = lambda: regions("LGL5", "BlockConstant")
     zoo["regions_LGL7_highest_order_spline"] = lambda: regions("LGL7", "HighestOrderSpline")
+
+    def ocp_multispacecraft(nphase=3, nseg=5):
+        """Config 4 of BASELINE.json (examples/MultiSpacecraftOptimization.py:60-121): one BlockConstant LGL5 two-body
+        phase per spacecraft, the back state and time of each tied to 7 free link parameters, plus a link-parameter
+        constraint."""
+        args = oc.ODEArguments(6, 3)
+        r, v, u = args.head3(), args.segment3(3), args.tail3()
+        ode = oc.ODEBase(vf.stack([v, r.normalized_power3() * (-1.0) + u * 0.01]), 6, 3)
+        ocp = oc.OptimalControlProblem()
+        rng = np.random.default_rng(11)
+        for k in range(nphase):
+            S = 2 * nseg + 1
+            th = np.linspace(0.1 * k, 0.1 * k + 1.5, S)
+            T = np.zeros((S, 10))
+            T[:, 0], T[:, 1], T[:, 3], T[:, 4], T[:, 6] = np.cos(th), np.sin(th), -np.sin(th), np.cos(th), th
+            T[:, 7:] = 0.3
+            T[:, :6] += 0.01 * rng.uniform(-1, 1, (S, 6))
+            ph = ode.phase("LGL5")
+            ph.setControlMode("BlockConstant")
+            ph.setTraj(T, nseg)
+            ph.addBoundaryValue("Front", range(7), T[0, :7])
+            ph.addLUNormBound("Path", [7, 8, 9], 0.01, 1.0)
+            ph.addIntegralObjective(vf.Arguments(3).norm() * 0.1, [7, 8, 9])
+            ocp.addPhase(ph)
+        ocp.setLinkParams(np.array([0.1, 1.0, 0.02, -1.0, 0.1, 0.01, 1.6]))
+        A = vf.Arguments
+        link = A(14).head(7) - A(14).tail(7)
+        for k in range(nphase):
+            ocp.addLinkEqualCon(link, [(k, "Back", range(7), [], [])], range(7))
+        ocp.addLinkParamEqualCon(A(6).head3().dot(A(6).tail3()), range(6))
+        ocp.addLinkParamObjective(A(1)[0] * 0.5, [6])
+        return ocp
+
+    def ocp_forward_links():
+        """Phases of different transcriptions chained by addForwardLinkEqualCon / addDirectLinkEqualCon, a flag-interface
+        link over several phase pairs, a non-linear link inequality and a link objective."""
+        ocp = oc.OptimalControlProblem()
+        ode = vdp_param_ode()
+        rng = np.random.default_rng(5)
+        for k, (mode, nseg) in enumerate([("LGL3", 4), ("LGL5", 3), ("Trapezoidal", 5)]):
+            S = (W.CARDINALS[mode] - 1) * nseg + 1
+            t = np.linspace(k, k + 1.0, S)
+            T = np.stack([np.cos(t), -np.sin(t), t, 0.1 * np.sin(2 * t), np.full(S, 0.8 + 0.1 * k)], axis=1)
+            T[:, [0, 1, 3]] += 0.01 * rng.uniform(-1, 1, (S, 3))
+            ph = ode.phase(mode)
+            ph.setTraj(T, nseg)
+            ph.addLUVarBound("Path", 3, -1.0, 1.0)
+            ph.addIntegralObjective(vf.Arguments(1).squared_norm(), [3])
+            ocp.addPhase(ph)
+        A = vf.Arguments
+        ocp.addForwardLinkEqualCon(0, -1, [0, 1, 2])
+        ocp.addDirectLinkEqualCon(0, "ODEParams", [0], 1, "ODEParams", [0])
+        ocp.addLinkEqualCon(A(2)[0] * A(2)[1] - 0.7, "BackToFront", [[0, 1], [1, 2]], [3])
+        ocp.addLinkInequalCon(vf.sin(A(4)[0]) * A(4)[3] - A(4)[1] * A(4)[2], 0, "Front", [0, 1], 2, "Back", [0, 1])
+        ocp.addLinkObjective(A(2)[1] - A(2)[0], 0, "Front", [2], 2, "Back", [2])
+        return ocp
+
+    zoo["ocp_multispacecraft_LGL5_block_constant"] = ocp_multispacecraft
+    zoo["ocp_forward_links_mixed_transcriptions"] = ocp_forward_links
     return zoo
 
 

@@ -92,3 +92,45 @@ def test_linearity_rules():
     assert (a * 2.0).is_linear()                     # Scaled<Arguments>
     assert not vf.sin(a).is_linear()
     assert vf.stack([a[0], a[1]]).is_linear()
+
+
+def test_link_index_maps_follow_the_reference_layout():
+    """make_link_Vindex_Cindex (OptimalControlProblem.cpp:659-764) on a hand-computed case: phase variables are
+    [(x,t,u) per node ; p], phases are laid out back to back, link parameters follow the last phase, link constraint
+    rows follow every phase's rows in insertion order, application-major."""
+    ocp = ZOO["ocp_forward_links_mixed_transcriptions"]()
+    nlp = ocp.transcribe()
+    nv = [5 * 4 + 1, 7 * 4 + 1, 6 * 4 + 1]  # LGL3/4 segments, LGL5/3, Trapezoidal/5; XtU = 4, PV = 1
+    off = np.concatenate([[0], np.cumsum(nv)])
+    assert [o[0] for o in ocp.offsets] == list(off[:3])
+    d = nlp.dims()
+    assert d["nvars"] == off[3]
+    back = lambda p, v: off[p] + (nv[p] - 1) - 4 + v  # noqa: E731  last node's variable v
+    front = lambda p, v: off[p] + v  # noqa: E731
+    par = lambda p: off[p] + nv[p] - 1  # noqa: E731
+    links = []
+    for f in range(d["nfuncs"]):
+        fi = nlp.function_info(f)
+        V, Cx = nlp.function_indices(f)
+        links.append((fi, V, Cx))
+    eq_links = [(fi, V, Cx) for (fi, V, Cx) in links if fi["role"] == 1][-4:]
+    # addForwardLinkEqualCon(0, -1, [0,1,2]) -> two functions; direct ODEParams link; flag-interface link with two columns
+    assert np.array_equal(eq_links[0][1], [[back(0, 0), back(0, 1), back(0, 2), front(1, 0), front(1, 1), front(1, 2)]])
+    assert np.array_equal(eq_links[1][1], [[back(1, 0), back(1, 1), back(1, 2), front(2, 0), front(2, 1), front(2, 2)]])
+    assert np.array_equal(eq_links[2][1], [[par(0), par(1)]])
+    assert np.array_equal(eq_links[3][1], [[back(0, 3), front(1, 3)], [back(1, 3), front(2, 3)]])
+    rows = np.concatenate([c.ravel() for (_, _, c) in eq_links[:4]])
+    assert np.array_equal(rows, np.arange(d["neq"] - rows.size, d["neq"])) and rows.size == 3 + 3 + 1 + 2
+    iq = [(fi, V, Cx) for (fi, V, Cx) in links if fi["role"] == 2][-1]
+    assert np.array_equal(iq[1], [[front(0, 0), front(0, 1), back(2, 0), back(2, 1)]]) and iq[2][0, 0] == d["niq"] - 1
+    ob = [(fi, V, Cx) for (fi, V, Cx) in links if fi["role"] == 0][-1]
+    assert np.array_equal(ob[1], [[front(0, 2), back(2, 2)]])
+    # link parameters: after the last phase
+    ocp2 = ZOO["ocp_multispacecraft_LGL5_block_constant"]()
+    nlp2 = ocp2.transcribe()
+    d2 = nlp2.dims()
+    assert np.array_equal(ocp2.LinkParamLocs, d2["nvars"] - 7 + np.arange(7))
+    assert ocp2.makeSolverInput().shape == (d2["nvars"],)
+    fi, V, Cx = [(nlp2.function_info(f),) + tuple(nlp2.function_indices(f)) for f in range(d2["nfuncs"])
+                 if nlp2.function_info(f)["role"] == 1][-1]
+    assert np.array_equal(V, [ocp2.LinkParamLocs[:6]]) and Cx[0, 0] == d2["neq"] - 1

@@ -14,6 +14,7 @@ from . import _lib
 from ._lib import lib
 
 EVAL_KKT, EVAL_KKTNO, EVAL_SOE, EVAL_AUG, EVAL_RHS, EVAL_OGC, EVAL_OCC, EVAL_OBJ = range(8)
+OUT_ARRAYS = ("KKT", "PGX", "AGX", "FXE", "FXI", "val")  # order of the gather lists / cut sets in the C ABI
 
 
 class NonLinearProgram:
@@ -155,17 +156,122 @@ class NonLinearProgram:
         return buf.value.decode()
 
     # ------------------------------------------------------------------ device
-    def to_device(self, device=0):
+    def to_device(self, device=0, rank=0, world=1, group=None):
+        """Build the device plan.  ``world > 1``: this process evaluates rank's share of every function (contiguous
+        application ranges); the cut set is summed over ``group`` (a torch.distributed process
+        group, NCCL) after every evaluation and every output ends up non-zero on exactly one rank."""
         if self.plan:
             lib.ab_plan_destroy(self.plan)
             self.plan = None
         if self._dims is None or not self.dims()["kktdim"]:
             self.analyze()
         p = C.c_void_p()
-        _lib.check0(lib.ab_plan_create(self.h, device, C.byref(p)))
+        if world > 1:
+            _lib.check0(lib.ab_plan_create_sharded(self.h, device, rank, world, C.byref(p)))
+        else:
+            _lib.check0(lib.ab_plan_create(self.h, device, C.byref(p)))
         self.plan = p
         self.device = device
+        self.rank, self.world, self.group = rank, world, group
+        self._cut = None
         return self
+
+    def partition(self, rank, world):
+        """Host-side description of one rank's share (no GPU needed): application ranges per function, the gather
+        lists restricted to the rank's own sources and the cut set {array: (target, owner, mine)}."""
+        q = lib.ab_partition_create(self.h, rank, world)
+        if not q:
+            raise ValueError(_lib.last_error())
+        try:
+            nf = self.dims()["nfuncs"]
+            rng = np.zeros((nf, 2), dtype=np.int32)
+            for f in range(nf):
+                _lib.check(lib.ab_partition_app_range(q, f, rng[f].ctypes.data_as(_lib._ip)))
+            gathers, cuts = {}, {}
+            for a, name in enumerate(OUT_ARRAYS):
+                lists = []
+                for lvl in range(2):
+                    sz = (C.c_longlong * 2)()
+                    _lib.check(lib.ab_partition_gather_sizes(q, a, lvl, sz))
+                    ptr = np.zeros(sz[0] + 1, dtype=np.int64)
+                    src = np.zeros(max(sz[1], 1), dtype=np.int32)
+                    tgt = np.zeros(max(sz[0], 1), dtype=np.int32)
+                    _lib.check(lib.ab_partition_gather(q, a, lvl, ptr.ctypes.data_as(_lib._llp), src.ctypes.data_as(_lib._ip),
+                                                       tgt.ctypes.data_as(_lib._ip)))
+                    lists.append((ptr, src[:sz[1]], tgt[:sz[0]]))
+                gathers[name] = lists
+                n = int(lib.ab_partition_cut_size(q, a))
+                t, o, m = (np.zeros(max(n, 1), dtype=np.int32) for _ in range(3))
+                _lib.check(lib.ab_partition_cut(q, a, t.ctypes.data_as(_lib._ip), o.ctypes.data_as(_lib._ip),
+                                                m.ctypes.data_as(_lib._ip)))
+                cuts[name] = (t[:n], o[:n], m[:n])
+            return {"app_ranges": rng, "gathers": gathers, "cuts": cuts}
+        finally:
+            lib.ab_partition_destroy(q)
+
+    def gather_lists(self):
+        """The unpartitioned fixed-order gather lists {array: [(ptr, src, target)] * 2} and the staging buffer size."""
+        out, stage = {}, 0
+        for a, name in enumerate(OUT_ARRAYS):
+            lists = []
+            for lvl in range(2):
+                sz = (C.c_longlong * 3)()
+                _lib.check(lib.ab_problem_gather_sizes(self.h, a, lvl, sz))
+                stage = int(sz[2])
+                ptr = np.zeros(sz[0] + 1, dtype=np.int64)
+                src = np.zeros(max(sz[1], 1), dtype=np.int32)
+                tgt = np.zeros(max(sz[0], 1), dtype=np.int32)
+                _lib.check(lib.ab_problem_gather(self.h, a, lvl, ptr.ctypes.data_as(_lib._llp), src.ctypes.data_as(_lib._ip),
+                                                 tgt.ctypes.data_as(_lib._ip)))
+                lists.append((ptr, src[:sz[1]], tgt[:sz[0]]))
+            out[name] = lists
+        return out, stage
+
+    def reduce_cut(self):
+        """Sum the cut set over the ranks (asynchronous on the plan's stream): pack, NCCL all-reduce, unpack."""
+        if getattr(self, "world", 1) <= 1:
+            return
+        n = int(lib.ab_plan_cut_count(self.plan))
+        if n == 0:
+            return
+        import torch
+        import torch.distributed as dist
+        cut = self.cut_tensor()
+        _lib.check0(lib.ab_plan_cut_pack(self.plan))
+        with torch.cuda.stream(self._tstream):
+            dist.all_reduce(cut, op=dist.ReduceOp.SUM, group=self.group)
+        _lib.check0(lib.ab_plan_cut_unpack(self.plan))
+
+    def cut_tensor(self):
+        """The packed cut buffer as a torch tensor aliasing the plan's device memory (no copy)."""
+        import torch
+        if self._cut is None:
+            n = int(lib.ab_plan_cut_count(self.plan))
+
+            class _Raw:
+                pass
+            raw = _Raw()
+            raw.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (int(lib.ab_plan_cut_buffer(self.plan)), False),
+                                            "version": 3, "strides": None}
+            self._cut = torch.as_tensor(raw, device=torch.device("cuda", self.device))
+            self._tstream = torch.cuda.ExternalStream(self.stream(), device=self.device)
+        return self._cut
+
+    def output_ranges(self):
+        """{array: [(lo, hi), ...]} of what this (sharded) plan writes and reads back."""
+        res = {}
+        for a, nm in enumerate(OUT_ARRAYS):
+            n = _lib.check(lib.ab_plan_output_ranges(self.plan, a, None, 0))
+            out = (C.c_longlong * max(2 * n, 2))()
+            _lib.check(lib.ab_plan_output_ranges(self.plan, a, out, n))
+            res[nm] = [(int(out[2 * k]), int(out[2 * k + 1])) for k in range(n)]
+        return res
+
+    def cut_pack(self):
+        _lib.check0(lib.ab_plan_cut_pack(self.plan))
+
+    def cut_unpack(self):
+        _lib.check0(lib.ab_plan_cut_unpack(self.plan))
 
     def _need_plan(self):
         if not self.plan:
@@ -198,8 +304,13 @@ class NonLinearProgram:
         if "KKT" in want:
             out["KKT"] = np.zeros(d["nnz"])
         g = lambda k: _lib.dptr(out[k]) if k in out else None  # noqa: E731
-        _lib.check0(lib.ab_plan_eval_host(self.plan, mode, float(ObjScale), _lib.dptr(X), _lib.dptr(LE), _lib.dptr(LI),
-                                          g("val"), g("PGX"), g("AGX"), g("FXE"), g("FXI"), g("KKT")))
+        if getattr(self, "world", 1) > 1:  # sharded: the cut set is reduced between the evaluation and the read-back
+            self.set_inputs(X, LE, LI)
+            self.eval_device(mode, ObjScale)
+            _lib.check0(lib.ab_plan_get_outputs(self.plan, g("val"), g("PGX"), g("AGX"), g("FXE"), g("FXI"), g("KKT")))
+        else:
+            _lib.check0(lib.ab_plan_eval_host(self.plan, mode, float(ObjScale), _lib.dptr(X), _lib.dptr(LE), _lib.dptr(LI),
+                                              g("val"), g("PGX"), g("AGX"), g("FXE"), g("FXI"), g("KKT")))
         if "val" in out:
             out["val"] = float(out["val"][0])
         return out
@@ -237,6 +348,19 @@ class NonLinearProgram:
     def eval_device(self, mode, ObjScale):
         """Launch one evaluation on the device-resident inputs (asynchronous); outputs stay on the device."""
         _lib.check0(lib.ab_plan_eval(self.plan, mode, float(ObjScale)))
+        if getattr(self, "world", 1) > 1:
+            self.reduce_cut()
+
+    def get_outputs(self, want=("val", "PGX", "AGX", "FXE", "FXI", "KKT")):
+        """Device -> host copy of the last evaluation's outputs (synchronises the plan's stream)."""
+        d = self.dims()
+        size = {"val": 1, "PGX": d["nvars"], "AGX": d["nvars"], "FXE": d["neq"], "FXI": d["niq"], "KKT": d["nnz"]}
+        out = {k: np.zeros(size[k]) for k in want}
+        g = lambda k: _lib.dptr(out[k]) if k in out else None  # noqa: E731
+        _lib.check0(lib.ab_plan_get_outputs(self.plan, g("val"), g("PGX"), g("AGX"), g("FXE"), g("FXI"), g("KKT")))
+        if "val" in out:
+            out["val"] = float(out["val"][0])
+        return out
 
     def sync(self):
         _lib.check0(lib.ab_plan_sync(self.plan))
@@ -249,6 +373,17 @@ class NonLinearProgram:
         g = _lib.dptr
         _lib.check0(lib.ab_plan_eval_host(self.plan, mode, float(ObjScale), g(X), g(LE), g(LI), g(val), g(PGX), g(AGX),
                                           g(FXE), g(FXI), g(KKT)))
+
+    def eval_host_sharded(self, mode, ObjScale, X, LE, LI, val, PGX, AGX, FXE, FXI, KKT, compact=False):
+        """eval_host for a sharded plan: H2D of the (replicated) iterate, evaluation, cut-set all-reduce, D2H of this
+        rank's output ranges only."""
+        g = _lib.dptr
+        _lib.check0(lib.ab_plan_set_inputs(self.plan, g(X), g(LE), g(LI)))
+        self.eval_device(mode, ObjScale)
+        if compact:  # the arrays hold this rank's output ranges back to back (see output_ranges)
+            _lib.check0(lib.ab_plan_get_outputs_packed(self.plan, g(KKT), g(PGX), g(AGX), g(FXE), g(FXI), g(val)))
+        else:
+            _lib.check0(lib.ab_plan_get_outputs(self.plan, g(val), g(PGX), g(AGX), g(FXE), g(FXI), g(KKT)))
 
     def profile(self, enable=True):
         self._need_plan()

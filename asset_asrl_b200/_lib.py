@@ -75,6 +75,22 @@ SIGNATURES = {
     "ab_phase_make_input": (_i, [_vp, _dp, _dp, _dp]),
     "ab_plan_create": (_i, [_vp, _i, C.POINTER(_vp)]),
     "ab_plan_destroy": (None, [_vp]),
+    "ab_plan_create_sharded": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
+    "ab_plan_cut_count": (_ll, [_vp]),
+    "ab_plan_output_ranges": (_i, [_vp, _i, _llp, _i]),
+    "ab_plan_get_outputs_packed": (_i, [_vp, _dp, _dp, _dp, _dp, _dp, _dp]),
+    "ab_plan_cut_buffer": (_vp, [_vp]),
+    "ab_plan_cut_pack": (_i, [_vp]),
+    "ab_plan_cut_unpack": (_i, [_vp]),
+    "ab_partition_create": (_vp, [_vp, _i, _i]),
+    "ab_partition_destroy": (None, [_vp]),
+    "ab_partition_app_range": (_i, [_vp, _i, _ip]),
+    "ab_partition_gather_sizes": (_i, [_vp, _i, _i, _llp]),
+    "ab_partition_gather": (_i, [_vp, _i, _i, _llp, _ip, _ip]),
+    "ab_partition_cut_size": (_ll, [_vp, _i]),
+    "ab_partition_cut": (_i, [_vp, _i, _ip, _ip, _ip]),
+    "ab_problem_gather_sizes": (_i, [_vp, _i, _i, _llp]),
+    "ab_problem_gather": (_i, [_vp, _i, _i, _llp, _ip, _ip]),
     "ab_plan_set_inputs": (_i, [_vp, _dp, _dp, _dp]),
     "ab_plan_set_solver_coeffs": (_i, [_vp, _dp]),
     "ab_plan_eval": (_i, [_vp, _i, _d]),

@@ -339,6 +339,7 @@ long long ab_problem_kernel_ptx(const ab_problem* p, int fidx, int mode, int ind
     sp.g_stage = p->p.g_stage.at(fidx);
     sp.v_stage = p->p.v_stage.at(fidx);
     sp.nthreads = 64;
+    jit_env_knobs(sp);
     const std::string s = emit_ptx(P, sp, am);
     if (buf && cap > 0) {
       const size_t n = std::min<size_t>(s.size(), (size_t) cap - 1);
@@ -522,6 +523,12 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* sp, doub
 }
 
 // ------------------------------------------------------------------ plan
+#define PLAN_CUDA(call)                                                              \
+  do {                                                                               \
+    cudaError_t e__ = (call);                                                        \
+    if (e__ != cudaSuccess) return fail((int) e__, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+  } while (0)
+
 int ab_plan_create(const ab_problem* p, int device, ab_plan** out) {
   AB_TRY
   if (!out) return fail(AB_ERR_INVALID, "null out pointer");
@@ -536,13 +543,144 @@ int ab_plan_create(const ab_problem* p, int device, ab_plan** out) {
   return AB_OK;
   AB_CATCH
 }
+int ab_plan_create_sharded(const ab_problem* p, int device, int rank, int world, ab_plan** out) {
+  AB_TRY
+  if (!out) return fail(AB_ERR_INVALID, "null out pointer");
+  *out = nullptr;
+  if (world < 1 || rank < 0 || rank >= world) return fail(AB_ERR_INVALID, "ab_plan_create_sharded: bad rank / world");
+  if (ab_device_count() <= 0)
+    return fail(AB_ERR_NO_DEVICE, "no CUDA device: the KKT evaluation path has no CPU fallback");
+  std::unique_ptr<ab_plan> pl(new ab_plan());
+  pl->plan.prob = p->p;
+  int rc = pl->plan.build(device, rank, world);
+  if (rc != 0) return fail(rc, pl->plan.last_error);
+  *out = pl.release();
+  return AB_OK;
+  AB_CATCH
+}
 void ab_plan_destroy(ab_plan* plan) { delete plan; }
+long long ab_plan_cut_count(const ab_plan* plan) { return plan->plan.cut_count; }
+int ab_plan_output_ranges(const ab_plan* plan, int array, long long* out, int cap) {
+  if (array < 0 || array >= OA_COUNT) return fail(AB_ERR_INVALID, "bad array");
+  const auto& R = plan->plan.out_ranges[array];
+  for (size_t k = 0; k < R.size() && (int) k < cap; k++) {
+    out[2 * k] = R[k][0];
+    out[2 * k + 1] = R[k][1];
+  }
+  return (int) R.size();
+}
+int ab_plan_get_outputs_packed(ab_plan* plan, double* kkt, double* pgx, double* agx, double* fxe, double* fxi, double* val) {
+  Plan& P = plan->plan;
+  if (P.world <= 1) return fail(AB_ERR_INVALID, "ab_plan_get_outputs_packed: not a sharded plan");
+  PLAN_CUDA(cudaSetDevice(P.device));
+  double* dst[OA_COUNT] = {kkt, pgx, agx, fxe, fxi, val};
+  const double* src[OA_COUNT] = {P.d_kkt, P.d_pgx, P.d_agx, P.d_fxe, P.d_fxi, P.d_val};
+  for (int a = 0; a < OA_COUNT; a++) {
+    if (!dst[a]) continue;
+    size_t off = 0;
+    for (const auto& r: P.out_ranges[a]) {
+      const size_t n = (size_t) (r[1] - r[0]);
+      PLAN_CUDA(cudaMemcpyAsync(dst[a] + off, src[a] + r[0], n * sizeof(double), cudaMemcpyDeviceToHost, P.stream));
+      off += n;
+    }
+  }
+  PLAN_CUDA(cudaStreamSynchronize(P.stream));
+  return AB_OK;
+}
+void* ab_plan_cut_buffer(ab_plan* plan) { return plan->plan.d_cutbuf; }
+int ab_plan_cut_pack(ab_plan* plan) {
+  AB_TRY
+  int rc = plan->plan.cut_pack();
+  if (rc != 0) return fail(rc, plan->plan.last_error);
+  return AB_OK;
+  AB_CATCH
+}
+int ab_plan_cut_unpack(ab_plan* plan) {
+  AB_TRY
+  int rc = plan->plan.cut_unpack();
+  if (rc != 0) return fail(rc, plan->plan.last_error);
+  return AB_OK;
+  AB_CATCH
+}
 
-#define PLAN_CUDA(call)                                                              \
-  do {                                                                               \
-    cudaError_t e__ = (call);                                                        \
-    if (e__ != cudaSuccess) return fail((int) e__, std::string(#call) + ": " + cudaGetErrorString(e__)); \
-  } while (0)
+// ------------------------------------------------------------------ partition (host only; also used by the CPU tests)
+struct ab_partition {
+  RankPartition part;
+};
+ab_partition* ab_partition_create(const ab_problem* p, int rank, int world) {
+  try {
+    std::unique_ptr<ab_partition> q(new ab_partition());
+    q->part = make_partition(p->p, rank, world);
+    return q.release();
+  } catch (const std::exception& e) {
+    fail(AB_ERR_INVALID, e.what());
+    return nullptr;
+  }
+}
+void ab_partition_destroy(ab_partition* q) { delete q; }
+int ab_partition_app_range(const ab_partition* q, int f, int out[2]) {
+  AB_TRY
+  out[0] = q->part.app_begin.at(f);
+  out[1] = q->part.app_end.at(f);
+  return AB_OK;
+  AB_CATCH
+}
+int ab_partition_gather_sizes(const ab_partition* q, int array, int level, long long out[2]) {
+  AB_TRY
+  if (array < 0 || array >= OA_COUNT || level < 0 || level > 1) return fail(AB_ERR_INVALID, "bad array / level");
+  out[0] = q->part.g[array][level].ntargets();
+  out[1] = (long long) q->part.g[array][level].src.size();
+  return AB_OK;
+  AB_CATCH
+}
+int ab_partition_gather(const ab_partition* q, int array, int level, long long* ptr, int* src, int* target) {
+  AB_TRY
+  if (array < 0 || array >= OA_COUNT || level < 0 || level > 1) return fail(AB_ERR_INVALID, "bad array / level");
+  const GatherList& g = q->part.g[array][level];
+  std::memcpy(ptr, g.ptr.data(), g.ptr.size() * sizeof(long long));
+  if (!g.src.empty()) std::memcpy(src, g.src.data(), g.src.size() * sizeof(int));
+  if (!g.target.empty()) std::memcpy(target, g.target.data(), g.target.size() * sizeof(int));
+  return AB_OK;
+  AB_CATCH
+}
+long long ab_partition_cut_size(const ab_partition* q, int array) {
+  if (array < 0 || array >= OA_COUNT) return -1;
+  return (long long) q->part.cut_target[array].size();
+}
+int ab_partition_cut(const ab_partition* q, int array, int* target, int* owner, int* mine) {
+  AB_TRY
+  if (array < 0 || array >= OA_COUNT) return fail(AB_ERR_INVALID, "bad array");
+  const size_t n = q->part.cut_target[array].size();
+  for (size_t k = 0; k < n; k++) {
+    target[k] = q->part.cut_target[array][k];
+    owner[k] = q->part.cut_owner[array][k];
+    mine[k] = q->part.cut_mine[array][k];
+  }
+  return AB_OK;
+  AB_CATCH
+}
+/* the problem's own (unpartitioned) gather lists and staging layout, for the tests' emulation of a sharded evaluation */
+int ab_problem_gather_sizes(const ab_problem* p, int array, int level, long long out[3]) {
+  AB_TRY
+  if (array < 0 || array >= OA_COUNT || level < 0 || level > 1) return fail(AB_ERR_INVALID, "bad array / level");
+  const GatherList* gl[OA_COUNT] = {p->p.g_kkt, p->p.g_pgx, p->p.g_agx, p->p.g_fxe, p->p.g_fxi, p->p.g_val};
+  out[0] = gl[array][level].ntargets();
+  out[1] = (long long) gl[array][level].src.size();
+  out[2] = p->p.stage_size;
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_gather(const ab_problem* p, int array, int level, long long* ptr, int* src, int* target) {
+  AB_TRY
+  if (array < 0 || array >= OA_COUNT || level < 0 || level > 1) return fail(AB_ERR_INVALID, "bad array / level");
+  const GatherList* gl[OA_COUNT] = {p->p.g_kkt, p->p.g_pgx, p->p.g_agx, p->p.g_fxe, p->p.g_fxi, p->p.g_val};
+  const GatherList& g = gl[array][level];
+  std::memcpy(ptr, g.ptr.data(), g.ptr.size() * sizeof(long long));
+  if (!g.src.empty()) std::memcpy(src, g.src.data(), g.src.size() * sizeof(int));
+  if (!g.target.empty()) std::memcpy(target, g.target.data(), g.target.size() * sizeof(int));
+  return AB_OK;
+  AB_CATCH
+}
 
 int ab_plan_set_inputs(ab_plan* plan, const double* X, const double* LE, const double* LI) {
   Plan& P = plan->plan;
@@ -572,6 +710,17 @@ int ab_plan_get_outputs(ab_plan* plan, double* val, double* pgx, double* agx, do
     if (!dst || n == 0) return cudaSuccess;
     return cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToHost, P.stream);
   };
+  if (P.world > 1) {
+    // sharded plan: only the ranges this rank can write travel (everything else is zero here by construction and is
+    // left untouched in the caller's arrays)
+    double* dst[OA_COUNT] = {kkt, pgx, agx, fxe, fxi, val};
+    const double* src[OA_COUNT] = {P.d_kkt, P.d_pgx, P.d_agx, P.d_fxe, P.d_fxi, P.d_val};
+    for (int a = 0; a < OA_COUNT; a++)
+      if (dst[a])
+        for (const auto& r: P.out_ranges[a]) PLAN_CUDA(D2H(dst[a] + r[0], src[a] + r[0], (size_t) (r[1] - r[0])));
+    PLAN_CUDA(cudaStreamSynchronize(P.stream));
+    return AB_OK;
+  }
   PLAN_CUDA(D2H(val, P.d_val, 1));
   PLAN_CUDA(D2H(pgx, P.d_pgx, P.prob.nvars));
   PLAN_CUDA(D2H(agx, P.d_agx, P.prob.nvars));

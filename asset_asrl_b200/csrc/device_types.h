@@ -63,9 +63,13 @@ struct EvalIO {
 // Fixed-order segmented gather-sum: out[target[t]] = sum_{s in [ptr[t], ptr[t+1])} stage[src[s]]
 struct GatherDev {
   int ntargets;
+  int maxparts;  // high fan-in lists: ceil(largest fan-in / GATHER_PART) (two-stage fixed-order sum)
   const long long* ptr;
   const int* src;
   const int* target;
 };
+
+// sources summed by one block of the first stage of a high fan-in gather
+constexpr int GATHER_PART = 2048;
 
 }  // namespace ab

@@ -33,9 +33,12 @@ struct JitSpec {
   long long g_stage = 0;  // gradient contributions go to stage[g_stage + app*ir + i]
   long long v_stage = 0;  // objective value contributions go to stage[v_stage + app]
   int nthreads = 128;     // block size (.maxntid)
-  int reg_budget = 96;    // affine variant: values kept in registers; the rest are parked in shared memory
+  int reg_budget = 112;   // affine variant: values kept in registers; the rest are parked in shared memory
   bool lockstep = false;        // bar.sync at every output flush: the warps of a block share instruction-cache fills
   bool prefetch_table = true;   // output-table entries of the next flush are loaded one flush ahead
+  bool unroll_flush = false;    // 32 unrolled load/store pairs per output chunk instead of a loop: measured SLOWER (more straight-line code, r1j)
+  bool flush_unroll4 = true;    // output walk in trips of four segments with rotating data / address registers
+  int debug = 0;                // measurement only (wrong results): 1 no global stores, 2 no output walk at all
   bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)
 };
 
@@ -70,6 +73,9 @@ struct JitOut {
   int arr;
   long long base, stride;
 };
+
+// Development knobs (ASSET_B200_JIT_REGS / _THREADS / _LOCKSTEP / _PREFETCH / _UNROLL / _HOIST) applied over the defaults.
+void jit_env_knobs(JitSpec& sp);
 
 // PTX text of the kernel; throws std::runtime_error when the function cannot be specialised (mixed direct/staged
 // destinations inside the affine range, offsets out of range).

@@ -221,26 +221,49 @@ __global__ void __launch_bounds__(256) k_gather_small(const GatherDev g, const d
   out[g.target[t]] = s;
 }
 
-// High fan-in targets (objective value, parameter rows): one block per target, fixed partition and
-// fixed tree so the result does not depend on scheduling.
-__global__ void __launch_bounds__(256) k_gather_large(const GatherDev g, const double* __restrict__ stage,
-                                                      double* __restrict__ out) {
-  __shared__ double part[256];
-  const int t = blockIdx.x;
-  const long long b = g.ptr[t], e = g.ptr[t + 1];
-  const long long n = e - b;
-  const long long chunk = (n + 255) / 256;
-  const long long lo = b + chunk * threadIdx.x;
-  const long long hi = (lo + chunk < e) ? (lo + chunk) : e;
-  double s = 0.0;
-  for (long long k = lo; k < hi; k++) s += stage[g.src[k]];
+// High fan-in targets (objective value, parameter rows, accumulated constraints): two stages, both with a fixed
+// partition and a fixed summation tree, so the result does not depend on scheduling.  Stage 1: block (part, target)
+// sums sources [part*GATHER_PART, (part+1)*GATHER_PART) of its target; stage 2: one block per target sums the partials.
+__device__ __forceinline__ double block_tree_sum(double s, double* part) {
   part[threadIdx.x] = s;
   __syncthreads();
   for (int w = 128; w > 0; w >>= 1) {
     if (threadIdx.x < w) part[threadIdx.x] += part[threadIdx.x + w];
     __syncthreads();
   }
-  if (threadIdx.x == 0) out[g.target[t]] = part[0];
+  return part[0];
+}
+__global__ void __launch_bounds__(256) k_gather_large_parts(const GatherDev g, const double* __restrict__ stage,
+                                                            double* __restrict__ partials) {
+  __shared__ double part[256];
+  const int t = blockIdx.y;
+  const long long b = g.ptr[t], e = g.ptr[t + 1];
+  const long long lo0 = b + (long long) blockIdx.x * GATHER_PART;
+  if (lo0 >= e) return;
+  const long long hi0 = (lo0 + GATHER_PART < e) ? lo0 + GATHER_PART : e;
+  constexpr int PER = GATHER_PART / 256;
+  const long long lo = lo0 + (long long) threadIdx.x * PER;
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < PER; k++)
+    if (lo + k < hi0) s += stage[g.src[lo + k]];
+  s = block_tree_sum(s, part);
+  if (threadIdx.x == 0) partials[(size_t) t * g.maxparts + blockIdx.x] = s;
+}
+__global__ void __launch_bounds__(256) k_gather_large_final(const GatherDev g, const double* __restrict__ partials,
+                                                            double* __restrict__ out) {
+  __shared__ double part[256];
+  const int t = blockIdx.x;
+  const long long n = g.ptr[t + 1] - g.ptr[t];
+  const int np = (int) ((n + GATHER_PART - 1) / GATHER_PART);
+  const int chunk = (np + 255) / 256;
+  double s = 0.0;
+  for (int k = 0; k < chunk; k++) {
+    const int q = threadIdx.x * chunk + k;
+    if (q < np) s += partials[(size_t) t * g.maxparts + q];
+  }
+  s = block_tree_sum(s, part);
+  if (threadIdx.x == 0) out[g.target[t]] = s;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -276,13 +299,40 @@ cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io) {
   return cudaGetLastError();
 }
 
+__global__ void __launch_bounds__(256) k_cut_pack(const double* __restrict__ arr, const int* __restrict__ target,
+                                                  const unsigned char* __restrict__ flag, long long n, int active,
+                                                  double* __restrict__ buf) {
+  const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) buf[i] = (active && (flag[i] & 1)) ? arr[target[i]] : 0.0;
+}
+__global__ void __launch_bounds__(256) k_cut_unpack(double* __restrict__ arr, const int* __restrict__ target,
+                                                    const unsigned char* __restrict__ flag, long long n,
+                                                    const double* __restrict__ buf) {
+  const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (flag[i] & 2)
+    arr[target[i]] = buf[i];
+  else if (flag[i] & 1)
+    arr[target[i]] = 0.0;
+}
+cudaError_t launch_cut(bool pack, bool active, double* arr, const int* target, const unsigned char* flag, long long n,
+                       double* buf, cudaStream_t st) {
+  const unsigned blocks = (unsigned) ((n + 255) / 256);
+  if (pack)
+    k_cut_pack<<<blocks, 256, 0, st>>>(arr, target, flag, n, active ? 1 : 0, buf);
+  else
+    k_cut_unpack<<<blocks, 256, 0, st>>>(arr, target, flag, n, buf);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_gather(const GatherDev& small, const GatherDev& large, const double* stage, double* out,
-                          cudaStream_t st) {
+                          double* scratch, cudaStream_t st) {
   if (small.ntargets > 0) {
     k_gather_small<<<(small.ntargets + 255) / 256, 256, 0, st>>>(small, stage, out);
   }
   if (large.ntargets > 0) {
-    k_gather_large<<<large.ntargets, 256, 0, st>>>(large, stage, out);
+    k_gather_large_parts<<<dim3((unsigned) large.maxparts, (unsigned) large.ntargets), 256, 0, st>>>(large, stage, scratch);
+    k_gather_large_final<<<large.ntargets, 256, 0, st>>>(large, scratch, out);
   }
   return cudaGetLastError();
 }

@@ -280,4 +280,97 @@ void Problem::analyze() {
   analyzed = true;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Multi-GPU partition (see RankPartition in nlp.hpp)
+// ---------------------------------------------------------------------------------------------------------------
+RankPartition make_partition(const Problem& prob, int rank, int world) {
+  if (!prob.analyzed) throw std::invalid_argument("make_partition: analyze() first");
+  if (world < 1 || world > 64 || rank < 0 || rank >= world) throw std::invalid_argument("make_partition: bad rank / world");
+  RankPartition P;
+  P.rank = rank;
+  P.world = world;
+  const size_t nf = prob.funcs.size();
+  P.app_begin.resize(nf);
+  P.app_end.resize(nf);
+  auto cut = [&](int nappl, int r) { return (int) ((long long) nappl * r / world); };
+  for (size_t f = 0; f < nf; f++) {
+    P.app_begin[f] = cut(prob.funcs[f].nappl, rank);
+    P.app_end[f] = cut(prob.funcs[f].nappl, rank + 1);
+  }
+  // rank evaluating application `a` of a function with `n` applications: the r with cut(n, r) <= a < cut(n, r + 1)
+  auto rank_of = [&](int n, int a) {
+    int r = (int) (((long long) a * world + world - 1) / std::max(n, 1));
+    r = std::min(std::max(r, 0), world - 1);
+    while (r > 0 && cut(n, r) > a) r--;
+    while (r + 1 < world && cut(n, r + 1) <= a) r++;
+    return (unsigned char) r;
+  };
+  // which rank writes each staging slot (255: solver-owned coefficient, follows the owner of its target)
+  std::vector<unsigned char> slot_rank((size_t) prob.stage_size, 255);
+  for (int fi: prob.order) {
+    const FuncRec& fn = prob.funcs[fi];
+    const int E = fn.triplets_per_app();
+    const long long tb = prob.trip_base[fi];
+    for (int a = 0; a < fn.nappl; a++) {
+      const unsigned char r = rank_of(fn.nappl, a);
+      for (int e = 0; e < E; e++) {
+        const int d = prob.kkt_dest[(size_t) (tb + (long long) a * E + e)];
+        if (d < 0) slot_rank[(size_t) ~d] = r;
+      }
+      if (prob.g_stage[fi] >= 0)
+        for (int i = 0; i < fn.ir; i++) slot_rank[(size_t) (prob.g_stage[fi] + (long long) a * fn.ir + i)] = r;
+      if (prob.v_stage[fi] >= 0) slot_rank[(size_t) (prob.v_stage[fi] + a)] = r;
+      if (fn.role != 0)
+        for (int o = 0; o < fn.orows; o++) {
+          const int d = prob.f_dest[(size_t) (prob.fdest_base[fi] + (long long) a * fn.orows + o)];
+          if (d < 0) slot_rank[(size_t) ~d] = r;
+        }
+    }
+  }
+  const GatherList* src_lists[OA_COUNT] = {prob.g_kkt, prob.g_pgx, prob.g_agx, prob.g_fxe, prob.g_fxi, prob.g_val};
+  for (int a = 0; a < OA_COUNT; a++) {
+    for (int w = 0; w < 2; w++) {
+      P.g[a][w].ptr.assign(1, 0);
+      P.g[a][w].src.clear();
+      P.g[a][w].target.clear();
+    }
+    for (int w = 0; w < 2; w++) {
+      const GatherList& gl = src_lists[a][w];
+      const int nt = gl.ntargets();
+      for (int t = 0; t < nt; t++) {
+        const long long b = gl.ptr[t], e = gl.ptr[(size_t) t + 1];
+        unsigned long long mask = 0;
+        for (long long k = b; k < e; k++) {
+          const unsigned char r = slot_rank[(size_t) gl.src[(size_t) k]];
+          if (r != 255) mask |= 1ull << r;
+        }
+        int owner;
+        if (mask == 0)
+          owner = (int) ((long long) t * world / std::max(nt, 1));  // solver-only or empty target: spread by position
+        else
+          owner = __builtin_ctzll(mask);
+        const bool multi = (mask & (mask - 1)) != 0;
+        const bool mine = multi ? ((mask >> rank) & 1ull) != 0 : owner == rank;
+        if (multi) {
+          P.cut_target[a].push_back(gl.target[t]);
+          P.cut_owner[a].push_back((unsigned char) owner);
+          P.cut_mine[a].push_back(mine ? 1 : 0);
+        }
+        if (!mine) continue;
+        // own sources (and the solver coefficient if this rank owns the target), in the original fixed order; the list
+        // keeps its fan-in class so the same kernels serve it
+        GatherList& out = P.g[a][w];
+        for (long long k = b; k < e; k++) {
+          const int sidx = gl.src[(size_t) k];
+          const unsigned char r = slot_rank[(size_t) sidx];
+          if (r == rank || (r == 255 && owner == rank)) out.src.push_back(sidx);
+        }
+        out.ptr.push_back((long long) out.src.size());
+        out.target.push_back(gl.target[t]);
+      }
+    }
+  }
+  return P;
+}
+
 }  // namespace ab

@@ -73,4 +73,30 @@ struct Problem {
 
 constexpr int LARGE_FANIN = 96;
 
+// ---------------------------------------------------------------------------------------------------------------
+// One rank's share of the evaluation when a problem is split over several GPUs.  Every function's
+// applications are cut into `world` contiguous ranges (the mirror of SolverIndexingData::thread_split,
+// /root/reference/src/VectorFunctions/IndexingData.h:117-146); a rank evaluates its range, which fills the direct
+// outputs of those applications and their staging slots.  An output with several sources is summed by the rank(s)
+// holding its sources; outputs whose sources sit on more than one rank (the shared node at a cut, the control spline
+// straddling it, parameter blocks, accumulated constraints, the objective value) form the *cut set*: each contributing
+// rank sums its own sources, the partial sums are added across ranks (one all-reduce over the packed cut buffer) and the
+// owner -- the lowest contributing rank -- keeps the result, so that every output ends up non-zero on exactly one rank.
+// ---------------------------------------------------------------------------------------------------------------
+enum OutArray : int { OA_KKT = 0, OA_PGX, OA_AGX, OA_FXE, OA_FXI, OA_VAL, OA_COUNT };
+struct RankPartition {
+  int rank = 0, world = 1;
+  std::vector<int> app_begin, app_end;  // per function, indexed like Problem::funcs
+  GatherList g[OA_COUNT][2];            // the problem's gather lists restricted to this rank's sources
+  std::vector<int> cut_target[OA_COUNT];            // output index, ascending; identical on every rank
+  std::vector<unsigned char> cut_owner[OA_COUNT];   // rank that keeps the summed value
+  std::vector<unsigned char> cut_mine[OA_COUNT];    // 1 if this rank holds sources of the target
+  long long cut_total() const {
+    long long n = 0;
+    for (int a = 0; a < OA_COUNT; a++) n += (long long) cut_target[a].size();
+    return n;
+  }
+};
+RankPartition make_partition(const Problem& prob, int rank, int world);
+
 }  // namespace ab

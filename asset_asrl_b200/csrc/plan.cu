@@ -1,5 +1,6 @@
 #include "plan.hpp"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -99,6 +100,9 @@ AffineMaps function_affine(const Problem& prob, int fi) {
 static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
   for (int w = 0; w < 2; w++) {
     dg.dev[w].ntargets = gl[w].ntargets();
+    long long maxfan = 0;
+    for (int t = 0; t < gl[w].ntargets(); t++) maxfan = std::max(maxfan, gl[w].ptr[(size_t) t + 1] - gl[w].ptr[t]);
+    dg.dev[w].maxparts = (int) std::max<long long>(1, (maxfan + GATHER_PART - 1) / GATHER_PART);
     long long* ptr = P.dupload(gl[w].ptr);
     int* src = P.dupload(gl[w].src);
     int* tgt = P.dupload(gl[w].target);
@@ -110,9 +114,19 @@ static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
   return true;
 }
 
-int Plan::build(int dev) {
+int Plan::build(int dev, int rank_, int world_) {
   if (!prob.analyzed) prob.analyze();
   device = dev;
+  rank = rank_;
+  world = world_;
+  if (world > 1) {
+    try {
+      part = make_partition(prob, rank, world);
+    } catch (const std::exception& e) {
+      last_error = e.what();
+      return (int) cudaErrorInvalidValue;
+    }
+  }
   AB_CUDA(cudaSetDevice(dev));
   AB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   int* d_kkt_dest = dupload(prob.kkt_dest);
@@ -193,8 +207,8 @@ int Plan::build(int dev) {
     f.nappconst = fr.nappconst;
     f.role = fr.role;
     f.linear = fr.linear ? 1 : 0;
-    f.app_begin = 0;
-    f.app_end = fr.nappl;
+    f.app_begin = world > 1 ? part.app_begin[fi] : 0;
+    f.app_end = world > 1 ? part.app_end[fi] : fr.nappl;
     f.E = fr.triplets_per_app();
     f.vindex = dupload(fr.vindex);
     f.cindex = dupload(fr.cindex);
@@ -225,10 +239,82 @@ int Plan::build(int dev) {
   }
   AB_CUDA(cudaMemset(d_stage, 0, sizeof(double) * (size_t) std::max<long long>(prob.stage_size, 1)));
   AB_CUDA(cudaMemset(d_kkt, 0, sizeof(double) * (size_t) std::max<long long>(prob.nnz(), 1)));
-  if (!up_gather(*this, prob.g_kkt, gk) || !up_gather(*this, prob.g_pgx, gp) || !up_gather(*this, prob.g_agx, ga)
-      || !up_gather(*this, prob.g_fxe, ge) || !up_gather(*this, prob.g_fxi, gi) || !up_gather(*this, prob.g_val, gv)) {
+  // outputs another rank produces read as zero here, so that the sum over ranks is the full result
+  AB_CUDA(cudaMemset(d_fxe, 0, sizeof(double) * (size_t) std::max(prob.neq, 1)));
+  AB_CUDA(cudaMemset(d_fxi, 0, sizeof(double) * (size_t) std::max(prob.niq, 1)));
+  AB_CUDA(cudaMemset(d_pgx, 0, sizeof(double) * (size_t) std::max(prob.nvars, 1)));
+  AB_CUDA(cudaMemset(d_agx, 0, sizeof(double) * (size_t) std::max(prob.nvars, 1)));
+  AB_CUDA(cudaMemset(d_val, 0, sizeof(double)));
+  const GatherList* gsrc[OA_COUNT] = {prob.g_kkt, prob.g_pgx, prob.g_agx, prob.g_fxe, prob.g_fxi, prob.g_val};
+  if (world > 1) {
+    for (int a = 0; a < OA_COUNT; a++) gsrc[a] = part.g[a];
+    cut_count = part.cut_total();
+    {
+      const long long sizes[OA_COUNT] = {prob.nnz(), prob.nvars, prob.nvars, prob.neq, prob.niq, 1};
+      std::vector<char> blocks[OA_COUNT];
+      for (int a = 0; a < OA_COUNT; a++) blocks[a].assign((size_t) ((sizes[a] + OUT_BLOCK - 1) / OUT_BLOCK) + 1, 0);
+      auto touch = [&](int a, long long i) { blocks[a][(size_t) (i / OUT_BLOCK)] = 1; };
+      for (int fi: prob.order) {
+        const FuncRec& fr = prob.funcs[fi];
+        const int E = fr.triplets_per_app();
+        for (int ap = part.app_begin[fi]; ap < part.app_end[fi]; ap++) {
+          for (int e = 0; e < E; e++) {
+            const int d = prob.kkt_dest[(size_t) (prob.trip_base[fi] + (long long) ap * E + e)];
+            if (d >= 0) touch(OA_KKT, d);
+          }
+          if (fr.role != 0)
+            for (int o = 0; o < fr.orows; o++) {
+              const int d = prob.f_dest[(size_t) (prob.fdest_base[fi] + (long long) ap * fr.orows + o)];
+              if (d >= 0) touch(fr.role == 1 ? OA_FXE : OA_FXI, d);
+            }
+        }
+      }
+      for (int a = 0; a < OA_COUNT; a++) {
+        for (int w = 0; w < 2; w++)
+          for (int t: part.g[a][w].target) touch(a, t);
+        out_ranges[a].clear();
+        const long long nb = (long long) blocks[a].size();
+        for (long long q = 0; q < nb;) {
+          if (!blocks[a][(size_t) q]) {
+            q++;
+            continue;
+          }
+          long long e = q;
+          while (e < nb && blocks[a][(size_t) e]) e++;
+          out_ranges[a].push_back({q * OUT_BLOCK, std::min(e * OUT_BLOCK, sizes[a])});
+          q = e;
+        }
+      }
+    }
+    d_cutbuf = dalloc<double>((size_t) std::max<long long>(cut_count, 1));
+    bool ok = d_cutbuf != nullptr;
+    for (int a = 0; a < OA_COUNT && ok; a++) {
+      std::vector<unsigned char> flag(part.cut_target[a].size());
+      for (size_t q = 0; q < flag.size(); q++)
+        flag[q] = (unsigned char) ((part.cut_mine[a][q] ? 1 : 0) | (part.cut_owner[a][q] == rank ? 2 : 0));
+      d_cut_target[a] = dupload(part.cut_target[a]);
+      d_cut_flag[a] = dupload(flag);
+      ok = d_cut_target[a] && d_cut_flag[a];
+    }
+    if (!ok) {
+      last_error = "out of device memory for the cut set";
+      return (int) cudaErrorMemoryAllocation;
+    }
+  }
+  if (!up_gather(*this, gsrc[OA_KKT], gk) || !up_gather(*this, gsrc[OA_PGX], gp) || !up_gather(*this, gsrc[OA_AGX], ga)
+      || !up_gather(*this, gsrc[OA_FXE], ge) || !up_gather(*this, gsrc[OA_FXI], gi) || !up_gather(*this, gsrc[OA_VAL], gv)) {
     last_error = "out of device memory for the gather lists";
     return (int) cudaErrorMemoryAllocation;
+  }
+  {
+    size_t need = 1;
+    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv})
+      need = std::max(need, (size_t) g->dev[1].ntargets * (size_t) g->dev[1].maxparts);
+    d_gscratch = dalloc<double>(need);
+    if (!d_gscratch) {
+      last_error = "out of device memory for the gather scratch";
+      return (int) cudaErrorMemoryAllocation;
+    }
   }
   AB_CUDA(cudaDeviceSynchronize());
   return 0;
@@ -300,11 +386,7 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
   std::string ptx;
   std::vector<JitOut> outs;
   JitStats js;
-  if (const char* e = getenv("ASSET_B200_JIT_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
-  if (const char* e = getenv("ASSET_B200_JIT_THREADS")) sp.nthreads = std::max(32, std::atoi(e) / 32 * 32);
-  if (const char* e = getenv("ASSET_B200_JIT_LOCKSTEP")) sp.lockstep = std::atoi(e) != 0;
-  if (const char* e = getenv("ASSET_B200_JIT_PREFETCH")) sp.prefetch_table = std::atoi(e) != 0;
-  if (const char* e = getenv("ASSET_B200_JIT_HOIST")) sp.hoist_loads = std::atoi(e) != 0;
+  jit_env_knobs(sp);
   try {
     ptx = emit_ptx(host_progs[k][fm], sp, am, &outs, &js);
   } catch (const std::exception& e) {
@@ -384,6 +466,7 @@ int Plan::eval(int mode, double obj_scale) {
   }
   launches = 0;
   jit_launches = 0;
+  last_mode = mode;
   if (profiling != 2) prof_labels.clear();
   if (out_kkt && mode != EM_KKT) {
     // partial matrix modes: entries this mode does not compute must read as zero
@@ -487,8 +570,8 @@ int Plan::eval(int mode, double obj_scale) {
     const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);
     if (n == 0) return 0;
     if (int rc = prof_begin(label)) return rc;
-    AB_CUDA(launch_gather(g.dev[0], g.dev[1], d_stage, out, stream));
-    launches += n;
+    AB_CUDA(launch_gather(g.dev[0], g.dev[1], d_stage, out, d_gscratch, stream));
+    launches += n + (g.dev[1].ntargets > 0);
     return prof_end();
   };
   int rc = 0;
@@ -497,6 +580,56 @@ int Plan::eval(int mode, double obj_scale) {
   if (out_agx && (rc = G(ga, d_agx, "gather:AGX"))) return rc;
   if (out_fx && ((rc = G(ge, d_fxe, "gather:FXE")) || (rc = G(gi, d_fxi, "gather:FXI")))) return rc;
   if (out_val && (rc = G(gv, d_val, "gather:val"))) return rc;
+  return 0;
+}
+
+// which output arrays an eval mode produces: {KKT, PGX, AGX, FXE, FXI, val}
+static void mode_outputs(int mode, bool out[OA_COUNT]) {
+  const bool kkt = mode == EM_KKT || mode == EM_KKTNO || mode == EM_SOE || mode == EM_AUG;
+  const bool pgx = mode == EM_KKT || mode == EM_AUG || mode == EM_RHS || mode == EM_OGC;
+  const bool agx = mode == EM_KKT || mode == EM_KKTNO || mode == EM_AUG || mode == EM_RHS;
+  const bool fx = mode != EM_OBJ;
+  const bool val = mode != EM_KKTNO && mode != EM_SOE;
+  out[OA_KKT] = kkt;
+  out[OA_PGX] = pgx;
+  out[OA_AGX] = agx;
+  out[OA_FXE] = out[OA_FXI] = fx;
+  out[OA_VAL] = val;
+}
+
+int Plan::cut_pack() {
+  if (world <= 1 || cut_count == 0) return 0;
+  AB_CUDA(cudaSetDevice(device));
+  bool on[OA_COUNT];
+  mode_outputs(last_mode, on);
+  double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
+  long long off = 0;
+  for (int a = 0; a < OA_COUNT; a++) {
+    const long long n = (long long) part.cut_target[a].size();
+    if (n > 0) {
+      AB_CUDA(launch_cut(true, on[a], arrs[a], d_cut_target[a], d_cut_flag[a], n, d_cutbuf + off, stream));
+      launches++;
+    }
+    off += n;
+  }
+  return 0;
+}
+
+int Plan::cut_unpack() {
+  if (world <= 1 || cut_count == 0) return 0;
+  AB_CUDA(cudaSetDevice(device));
+  bool on[OA_COUNT];
+  mode_outputs(last_mode, on);
+  double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
+  long long off = 0;
+  for (int a = 0; a < OA_COUNT; a++) {
+    const long long n = (long long) part.cut_target[a].size();
+    if (n > 0 && on[a]) {
+      AB_CUDA(launch_cut(false, true, arrs[a], d_cut_target[a], d_cut_flag[a], n, d_cutbuf + off, stream));
+      launches++;
+    }
+    off += n;
+  }
   return 0;
 }
 

@@ -56,6 +56,7 @@ struct Plan {
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;
   double *d_kkt = nullptr, *d_fxe = nullptr, *d_fxi = nullptr, *d_pgx = nullptr, *d_agx = nullptr, *d_val = nullptr;
   double* d_stage = nullptr;
+  double* d_gscratch = nullptr;  // partial sums of the high fan-in gathers (one gather runs at a time)
   DevGather gk, gp, ga, ge, gi, gv;
   long long launches = 0;  // kernels launched by the last eval
   // optional per-launch device timing (cudaEvent pairs on `stream`), used by bench.py for the roofline of the
@@ -68,7 +69,23 @@ struct Plan {
   int profile_read(float* ms, int cap);  // synchronises the stream; returns the number of launches
 
   ~Plan();
-  int build(int device);  // upload everything; returns 0 or a cudaError
+  // upload everything; returns 0 or a cudaError.  world > 1: this plan evaluates rank's share of every function
+  // (RankPartition in nlp.hpp) and the cut set has to be reduced across ranks after each eval (cut_pack / all-reduce of
+  // cut_buffer() by the caller / cut_unpack).
+  int build(int device, int rank = 0, int world = 1);
+  int rank = 0, world = 1;
+  RankPartition part;
+  int* d_cut_target[OA_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  unsigned char* d_cut_flag[OA_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // bit0 mine, bit1 owner
+  double* d_cutbuf = nullptr;
+  long long cut_count = 0;
+  // index ranges [lo, hi) of each output array this rank can write (direct outputs of its applications + its gather
+  // targets, at a granularity of OUT_BLOCK elements); the read-back of a sharded plan copies only these ranges
+  static constexpr long long OUT_BLOCK = 1 << 16;
+  std::vector<std::array<long long, 2>> out_ranges[OA_COUNT];
+  int last_mode = 0;
+  int cut_pack();    // after eval(): partial sums of the cut set -> cut buffer (zeros where this rank has no sources)
+  int cut_unpack();  // after the all-reduce: the owner keeps the sum, other contributors clear their partial
   int eval(int mode, double obj_scale);
   int set_solver_coeffs(const double* host_coeffs);
 
@@ -81,7 +98,10 @@ struct Plan {
 // Largest application range of function `fi` over which every index map is affine in the application number.
 AffineMaps function_affine(const Problem& prob, int fi);
 cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io);
+// pack: buf[i] = (active && mine) ? arr[target[i]] : 0;  unpack: owner: arr[target[i]] = buf[i], other contributors: 0
+cudaError_t launch_cut(bool pack, bool active, double* arr, const int* target, const unsigned char* flag, long long n,
+                       double* buf, cudaStream_t st);
 cudaError_t launch_gather(const GatherDev& small, const GatherDev& large, const double* stage, double* out,
-                          cudaStream_t st);
+                          double* scratch /* large.ntargets * large.maxparts partial sums */, cudaStream_t st);
 
 }  // namespace ab

@@ -40,6 +40,12 @@ def parse_args():
     ap.add_argument("--no-extras", action="store_true", help="defect constraints only (no bounds / integral objective)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--shard", default="one-phase", choices=["one-phase", "phases"],
+                    help="N > 1: one phase of N x segments split across the ranks with the NCCL cut-set reduce (default), "
+                         "or one independent phase per rank (no collective)")
+    ap.add_argument("--max-total-segments", type=int, default=800000,
+                    help="one-phase sharding: every rank analyses the whole problem on the host (about 45 KB and 0.1 ms "
+                         "per segment), so the total is capped and segments per GPU shrink beyond the cap")
     return ap.parse_args()
 
 
@@ -136,6 +142,11 @@ def run_reference(a):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
+def _lib_cut_count(nlp):
+    from asset_asrl_b200._lib import lib
+    return lib.ab_plan_cut_count(nlp.plan)
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -153,12 +164,29 @@ def run_b200(a):
     from asset_asrl_b200.Solvers import EVAL_KKT
 
     t_setup = time.time()
-    ph = W.make_phase(a.ode, a.mode, a.segments, extras=not a.no_extras, seed=12345 + rank)
-    nlp = ph.transcribe()
-    d = nlp.dims()
-    X = ph.makeSolverInput()
-    LE, LI = W.multipliers(nlp, seed=67890 + rank)
-    nlp.to_device(local)
+    sharded = world > 1 and a.shard == "one-phase"
+    if sharded:
+        # one phase of world x segments; every rank builds the same problem and evaluates its share of every function
+        cap = a.max_total_segments
+        try:  # every rank holds the whole analysed problem on the host: stay well inside the box's memory
+            import psutil
+            cap = min(cap, int(0.5 * psutil.virtual_memory().available / (45e3 * world)))
+        except ImportError:
+            pass
+        a.segments = max(1000, min(a.segments, cap // world))
+        ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345)
+        nlp = ph.transcribe()
+        d = nlp.dims()
+        X = ph.makeSolverInput()
+        LE, LI = W.multipliers(nlp, seed=67890)
+        nlp.to_device(local, rank=rank, world=world)
+    else:
+        ph = W.make_phase(a.ode, a.mode, a.segments, extras=not a.no_extras, seed=12345 + rank)
+        nlp = ph.transcribe()
+        d = nlp.dims()
+        X = ph.makeSolverInput()
+        LE, LI = W.multipliers(nlp, seed=67890 + rank)
+        nlp.to_device(local)
     nlp.set_solver_coeffs(np.ones(d["n_solver"]))
     t_setup = time.time() - t_setup
     stream = torch.cuda.ExternalStream(nlp.stream(), device=local)
@@ -225,7 +253,7 @@ def run_b200(a):
     except OSError:
         pass
     peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    b_alg_eval = W.algorithmic_bytes(nlp)
+    b_alg_eval = W.algorithmic_bytes(nlp) // (world if sharded else 1)  # per GPU
     if dom == "defect":
         bytes_launch = b_seg_defect * a.segments
     else:  # another kernel dominates: charge it the whole evaluation's algorithmic bytes (upper bound on its share)
@@ -251,23 +279,34 @@ def run_b200(a):
             return torch.empty(max(nel, 1), dtype=torch.float64).pin_memory().numpy()[:nel]
         hX, hLE, hLI = pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"])
         hX[:], hLE[:], hLI[:] = X, LE, LI
-        out = [pinned(1), pinned(d["nvars"]), pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"]), pinned(d["nnz"])]
+        if sharded:  # compact pinned buffers holding this rank's output ranges only
+            rg = nlp.output_ranges()
+            out = [pinned(max(sum(hi - lo for (lo, hi) in rg[k]), 1)) for k in ("val", "PGX", "AGX", "FXE", "FXI", "KKT")]
+            host_call = lambda *args: nlp.eval_host_sharded(*args, compact=True)  # noqa: E731
+        else:
+            out = [pinned(1), pinned(d["nvars"]), pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"]), pinned(d["nnz"])]
+            host_call = nlp.eval_host
         ksteps = max(1, min(a.steps, 5))
         for _ in range(2):
-            nlp.eval_host(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
+            host_call(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
         barrier()
         t0 = time.perf_counter()
         for _ in range(ksteps):
-            nlp.eval_host(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
+            host_call(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
         barrier()
         dt = (time.perf_counter() - t0) / ksteps
         if world > 1:
             t = torch.tensor([dt], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
+        d2h = 8 * (1 + 2 * d["nvars"] + d["neq"] + d["niq"] + d["nnz"])
+        note = "ab_plan_eval_host: pinned host X/LE/LI in, val/PGX/AGX/FXE/FXI/KKT values out"
+        if sharded:
+            d2h = 8 * sum(hi - lo for rr in nlp.output_ranges().values() for (lo, hi) in rr)
+            note = ("per rank: pinned host X/LE/LI in (replicated), evaluation of the rank's share, NCCL cut-set reduce, "
+                    "the rank's output ranges out; bytes are rank 0's")
         e2e = {"value": world * a.segments / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * (d["nvars"] + d["neq"] + d["niq"]),
-               "d2h_bytes_per_step": 8 * (1 + 2 * d["nvars"] + d["neq"] + d["niq"] + d["nnz"]), "ms_per_step": dt * 1e3,
-               "steps": ksteps, "note": "ab_plan_eval_host: pinned host X/LE/LI in, val/PGX/AGX/FXE/FXI/KKT values out"}
+               "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3, "steps": ksteps, "note": note}
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
@@ -281,6 +320,9 @@ def run_b200(a):
                 "config": {"workload": workload_name(a), "segments_per_gpu": a.segments, "segments_total": world * a.segments,
                            "eval": "evalKKT", "nvars": d["nvars"], "neq": d["neq"], "niq": d["niq"], "nnz": d["nnz"],
                            "kkt_evals_per_sec": 1e3 / ms_step,
+                           "sharding": ("one phase split into contiguous application ranges, NCCL all-reduce of the cut set ("
+                                        + str(int(_lib_cut_count(nlp))) + " doubles)") if sharded else
+                                       ("one independent phase per rank, no collective" if world > 1 else "single GPU"),
                            "l2": f"no flush: per-eval working set {b_alg_eval / 1e6:.0f} MB of values (+ index maps) > 126 MB L2",
                            "setup_s": round(t_setup, 2)},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "specialised_launches": specialised, "clocks": clk,

@@ -121,7 +121,35 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_p
 
 /* ---------------- device plan ---------------- */
 int ab_plan_create(const ab_problem* p, int device, ab_plan** out);
+/* One rank's share of a problem split over `world` GPUs (the thread split of
+ * SolverIndexingData::thread_split, src/VectorFunctions/IndexingData.h:117-146, across devices).  After ab_plan_eval:
+ * ab_plan_cut_pack, then the caller sums ab_plan_cut_buffer() (ab_plan_cut_count() doubles, device memory) over all
+ * ranks on the plan's stream (NCCL all-reduce), then ab_plan_cut_unpack.  Every output is then non-zero on exactly one
+ * rank: the per-rank value arrays are disjoint slices whose sum is the reference's result. */
+int ab_plan_create_sharded(const ab_problem* p, int device, int rank, int world, ab_plan** out);
+long long ab_plan_cut_count(const ab_plan* plan);
+/* Index ranges [lo, hi) of output array `array` (0 KKT values, 1 PGX, 2 AGX, 3 FXE, 4 FXI, 5 val) that a sharded plan
+ * can write; returns their number and fills up to `cap` pairs.  ab_plan_get_outputs copies only these ranges into the
+ * caller's full-size arrays; ab_plan_get_outputs_packed copies them back to back into compact arrays. */
+int ab_plan_output_ranges(const ab_plan* plan, int array, long long* out, int cap);
+int ab_plan_get_outputs_packed(ab_plan* plan, double* kkt, double* pgx, double* agx, double* fxe, double* fxi, double* val);
+void* ab_plan_cut_buffer(ab_plan* plan);
+int ab_plan_cut_pack(ab_plan* plan);
+int ab_plan_cut_unpack(ab_plan* plan);
 void ab_plan_destroy(ab_plan* plan);
+
+/* Host-side view of a rank's partition (application ranges, restricted gather lists, cut set); no GPU needed.
+ * array: 0 KKT values, 1 PGX, 2 AGX, 3 FXE, 4 FXI, 5 val; level: 0 low fan-in list, 1 high fan-in list. */
+typedef struct ab_partition ab_partition;
+ab_partition* ab_partition_create(const ab_problem* p, int rank, int world);
+void ab_partition_destroy(ab_partition* q);
+int ab_partition_app_range(const ab_partition* q, int f, int out[2]);
+int ab_partition_gather_sizes(const ab_partition* q, int array, int level, long long out[2] /* targets, sources */);
+int ab_partition_gather(const ab_partition* q, int array, int level, long long* ptr, int* src, int* target);
+long long ab_partition_cut_size(const ab_partition* q, int array);
+int ab_partition_cut(const ab_partition* q, int array, int* target, int* owner, int* mine);
+int ab_problem_gather_sizes(const ab_problem* p, int array, int level, long long out[3] /* targets, sources, stage size */);
+int ab_problem_gather(const ab_problem* p, int array, int level, long long* ptr, int* src, int* target);
 int ab_plan_set_inputs(ab_plan* plan, const double* X, const double* LE, const double* LI); /* host -> device */
 int ab_plan_set_solver_coeffs(ab_plan* plan, const double* coeffs /* n_solver_entries */);
 int ab_plan_eval(ab_plan* plan, int mode, double obj_scale); /* asynchronous on the plan's stream */

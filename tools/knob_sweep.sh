@@ -14,15 +14,9 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run base            ASSET_B200_JIT_PREFETCH=0 ASSET_B200_JIT_HOIST=0
-run prefetch        ASSET_B200_JIT_PREFETCH=1 ASSET_B200_JIT_HOIST=0
-run hoist           ASSET_B200_JIT_PREFETCH=0 ASSET_B200_JIT_HOIST=1
-run both            ASSET_B200_JIT_PREFETCH=1 ASSET_B200_JIT_HOIST=1
-run both_t128       ASSET_B200_JIT_THREADS=128
-run both_t128_lock  ASSET_B200_JIT_THREADS=128 ASSET_B200_JIT_LOCKSTEP=1
-run both_t64_lock   ASSET_B200_JIT_THREADS=64 ASSET_B200_JIT_LOCKSTEP=1
-run regs64          ASSET_B200_JIT_REGS=64
-run regs80          ASSET_B200_JIT_REGS=80
-run regs112         ASSET_B200_JIT_REGS=112
-run t32             ASSET_B200_JIT_THREADS=32
-run t32_regs80      ASSET_B200_JIT_THREADS=32 ASSET_B200_JIT_REGS=80
+run default         ASSET_B200_X=0
+run no_unroll       ASSET_B200_JIT_UNROLL=0
+run regs96          ASSET_B200_JIT_REGS=96
+run regs104         ASSET_B200_JIT_REGS=104
+run t128            ASSET_B200_JIT_THREADS=128 ASSET_B200_JIT_REGS=96
+timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3

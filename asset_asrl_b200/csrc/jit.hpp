@@ -38,6 +38,7 @@ struct JitSpec {
   bool prefetch_table = true;   // output-table entries of the next flush are loaded one flush ahead
   bool unroll_flush = false;    // 32 unrolled load/store pairs per output chunk instead of a loop: measured SLOWER (more straight-line code, r1j)
   bool flush_unroll4 = true;    // output walk in trips of four segments with rotating data / address registers
+  bool skip_zero_outputs = true;  // structural zeros of the dense blocks are written once (plan build), not per eval
   int debug = 0;                // measurement only (wrong results): 1 no global stores, 2 no output walk at all
   bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)
 };

@@ -42,6 +42,8 @@ Plan::~Plan() {
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
   if (side) cudaStreamDestroy(side);
+  if (bulk2) cudaStreamDestroy(bulk2);
+  if (ev_join2) cudaEventDestroy(ev_join2);
   for (cudaEvent_t e: prof_events) cudaEventDestroy(e);
   for (void* p: owned) cudaFree(p);
   if (stream) cudaStreamDestroy(stream);
@@ -97,6 +99,35 @@ AffineMaps function_affine(const Problem& prob, int fi) {
                      fr.triplets_per_app(), fr.nappl);
 }
 
+// Outputs of a program that are the constant zero: (output kind, index) pairs.
+static std::vector<std::pair<uint32_t, uint32_t>> const_zero_outputs(const Program& P) {
+  std::vector<std::pair<uint32_t, uint32_t>> z;
+  const size_t nb = P.code.size() / 4;
+  for (size_t bi = 0; bi < nb; bi++) {
+    const PInstr* ins = &P.code[4 * bi];
+    const uint32_t kind = ins[0].d >> 28, cnt = (ins[0].d >> 24) & 15u;
+    if (kind == PK_END) break;
+    if (kind != PK_OUT) continue;
+    for (uint32_t q = 0; q < cnt; q++)
+      if (!(ins[q].a & P_SLOT) && P.consts.at(ins[q].a >> 3) == 0.0) z.emplace_back(ins[q].b, ins[q].c);
+  }
+  return z;
+}
+
+// Drops the sources flagged in `dead` (staging slots that only ever hold a structural zero) from a gather list.
+static GatherList prune_gather(const GatherList& g, const std::vector<unsigned char>& dead) {
+  GatherList o;
+  o.ptr.assign(1, 0);
+  o.target = g.target;
+  o.src.reserve(g.src.size());
+  for (int t = 0; t < g.ntargets(); t++) {
+    for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++)
+      if (!dead[(size_t) g.src[(size_t) k]]) o.src.push_back(g.src[(size_t) k]);
+    o.ptr.push_back((long long) o.src.size());
+  }
+  return o;
+}
+
 static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
   for (int w = 0; w < 2; w++) {
     dg.dev[w].ntargets = gl[w].ntargets();
@@ -146,6 +177,8 @@ int Plan::build(int dev, int rank_, int world_) {
   AB_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
   AB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   AB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  AB_CUDA(cudaStreamCreateWithFlags(&bulk2, cudaStreamNonBlocking));
+  AB_CUDA(cudaEventCreateWithFlags(&ev_join2, cudaEventDisableTiming));
   if (const char* e = getenv("ASSET_B200_JIT")) use_jit = std::atoi(e) != 0;
   if (const char* e = getenv("ASSET_B200_JIT_MIN")) jit_min_apps = std::max(1, std::atoi(e));
   for (int fi: prob.order) {
@@ -223,6 +256,19 @@ int Plan::build(int dev, int rank_, int world_) {
     f.v_stage = prob.v_stage[fi];
     fns.push_back(f);
   }
+  {
+    long long best = -1;
+    heavy_fn = -1;
+    for (size_t k = 0; k < fns.size(); k++) {
+      const long long w = (long long) (fns[k].app_end - fns[k].app_begin) * (fns[k].E + fns[k].ir + fns[k].orows);
+      if (w > best) {
+        best = w;
+        heavy_fn = (int) k;
+      }
+    }
+    if (const char* e = getenv("ASSET_B200_OVERLAP"))
+      if (std::atoi(e) == 0) heavy_fn = -1;
+  }
   d_X = dalloc<double>(prob.nvars);
   d_LE = dalloc<double>(prob.neq);
   d_LI = dalloc<double>(prob.niq);
@@ -299,6 +345,38 @@ int Plan::build(int dev, int rank_, int world_) {
     if (!ok) {
       last_error = "out of device memory for the cut set";
       return (int) cudaErrorMemoryAllocation;
+    }
+  }
+  // Staging slots that only ever receive a structural zero (the specialised kernels do not store those, jit.cpp) are
+  // removed from the gather lists: the staging buffer is zero-filled above and the sums lose nothing.
+  GatherList pruned[OA_COUNT][2];
+  if (use_jit && !getenv("ASSET_B200_NO_PRUNE")) {
+    std::vector<unsigned char> dead((size_t) std::max<long long>(prob.stage_size, 1), 0);
+    for (size_t k = 0; k < fns.size(); k++) {
+      const int fi = prob.order[k];
+      const FuncRec& fr = prob.funcs[fi];
+      const int E = fr.triplets_per_app();
+      for (const auto& z: const_zero_outputs(host_progs[k][FM_ALL])) {
+        for (int ap = 0; ap < fr.nappl; ap++) {
+          long long slot = -1;
+          if (z.first == PO_H || z.first == PO_J) {
+            const int d = prob.kkt_dest[(size_t) (prob.trip_base[fi] + (long long) ap * E + z.second)];
+            if (d < 0) slot = ~d;
+          } else if (z.first == PO_G) {
+            slot = prob.g_stage[fi] + (long long) ap * fr.ir + z.second;
+          } else if (z.first == PO_F && fr.role != ROLE_OBJ) {
+            const int d = prob.f_dest[(size_t) (prob.fdest_base[fi] + (long long) ap * fr.orows + z.second)];
+            if (d < 0) slot = ~d;
+          } else if (z.first == PO_F) {
+            slot = prob.v_stage[fi] + ap;
+          }
+          if (slot >= 0) dead[(size_t) slot] = 1;
+        }
+      }
+    }
+    for (int a = 0; a < OA_COUNT; a++) {
+      for (int w = 0; w < 2; w++) pruned[a][w] = prune_gather(gsrc[a][w], dead);
+      gsrc[a] = pruned[a];
     }
   }
   if (!up_gather(*this, gsrc[OA_KKT], gk) || !up_gather(*this, gsrc[OA_PGX], gp) || !up_gather(*this, gsrc[OA_AGX], ga)
@@ -487,6 +565,16 @@ int Plan::eval(int mode, double obj_scale) {
     }
     return side;
   };
+  bool forked2 = false;
+  auto bulk_stream = [&](size_t k) -> cudaStream_t {
+    if (!overlap || heavy_fn < 0 || (int) k == heavy_fn) return stream;
+    if (!forked2) {
+      if (!forked) cudaEventRecord(ev_fork, stream);
+      cudaStreamWaitEvent(bulk2, ev_fork, 0);
+      forked2 = true;
+    }
+    return bulk2;
+  };
   for (const FnDev& f: fns) {
     int fm = (f.role == ROLE_OBJ) ? obj_mode : con_mode;
     if (fm < 0) continue;
@@ -552,7 +640,7 @@ int Plan::eval(int mode, double obj_scale) {
       a.end = je - a0;
       a.out_base = jits[0][k][fm].out_base;
       a.out_stride = jits[0][k][fm].out_stride;
-      AB_CUDA(launch_jit(jits[0][k][fm], a, stream));
+      AB_CUDA(launch_jit(jits[0][k][fm], a, bulk_stream(k)));
       launches++;
       jit_launches++;
       if (int rc = prof_end()) return rc;
@@ -565,6 +653,10 @@ int Plan::eval(int mode, double obj_scale) {
   if (forked) {
     AB_CUDA(cudaEventRecord(ev_join, side));
     AB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+  }
+  if (forked2) {
+    AB_CUDA(cudaEventRecord(ev_join2, bulk2));
+    AB_CUDA(cudaStreamWaitEvent(stream, ev_join2, 0));
   }
   auto G = [&](DevGather& g, double* out, const char* label) -> int {
     const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);

@@ -51,6 +51,11 @@ struct Plan {
   int ensure_jit(size_t k, int fm, int variant);  // returns 1 ready, 0 use the interpreter, < 0 CUDA error (negated)
   cudaStream_t side = nullptr;  // the small launches (mesh ends, single applications) overlap the bulk kernels here
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // The bulk kernel of the heaviest function (the defect) is latency-bound at 4 warps per SM and leaves most of the
+  // register file and the memory system idle; the bulk kernels of the other functions run beside it on this stream.
+  cudaStream_t bulk2 = nullptr;
+  cudaEvent_t ev_join2 = nullptr;
+  int heavy_fn = -1;  // index into fns
   long long jit_launches = 0;                          // specialised-kernel launches of the last eval
 
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;

@@ -15,8 +15,9 @@ except Exception as e:
 PY
 }
 run default         ASSET_B200_X=0
-run no_unroll       ASSET_B200_JIT_UNROLL=0
-run regs96          ASSET_B200_JIT_REGS=96
-run regs104         ASSET_B200_JIT_REGS=104
+run no_overlap      ASSET_B200_OVERLAP=0
+run no_skipzero     ASSET_B200_JIT_SKIPZERO=0 ASSET_B200_NO_PRUNE=1
+run no_prune        ASSET_B200_NO_PRUNE=1
 run t128            ASSET_B200_JIT_THREADS=128 ASSET_B200_JIT_REGS=96
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+run regs96          ASSET_B200_JIT_REGS=96
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3

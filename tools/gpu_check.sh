@@ -13,3 +13,4 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:$KRE -c 8 -o $O/top_kernel -f \
     python bench.py --steps 2 --warmup 1 --no-cpu --no-e2e > $O/ncu_full.log 2>&1; echo "ncu full rc=$?"
 tail -3 $O/pytest.log $O/smoke.log
+timeout 600 python bench.py --impl reference > $O/bench_reference.json 2> $O/bench_reference.err; echo "reference arm rc=$?"; cat $O/bench_reference.json

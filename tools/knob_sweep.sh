@@ -14,10 +14,10 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run default         ASSET_B200_X=0
-run no_overlap      ASSET_B200_OVERLAP=0
-run no_skipzero     ASSET_B200_JIT_SKIPZERO=0 ASSET_B200_NO_PRUNE=1
-run no_prune        ASSET_B200_NO_PRUNE=1
-run t128            ASSET_B200_JIT_THREADS=128 ASSET_B200_JIT_REGS=96
-run regs96          ASSET_B200_JIT_REGS=96
+run zrun4_default   ASSET_B200_X=0
+run zrun1           ASSET_B200_JIT_ZRUN=1
+run zrun2           ASSET_B200_JIT_ZRUN=2
+run zrun8           ASSET_B200_JIT_ZRUN=8
+run zrun16          ASSET_B200_JIT_ZRUN=16
+run zrun1000        ASSET_B200_JIT_ZRUN=1000
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3

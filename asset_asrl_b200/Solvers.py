@@ -131,6 +131,25 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_program_code(self.h, f, mode, code.ctypes.data_as(C.c_void_p), _lib.dptr(consts)))
         return st, code, consts
 
+    def fused_info(self, min_threads=32):
+        """Host-side description of the owner-writes fused interior (no GPU needed)."""
+        out = (C.c_longlong * 12)()
+        why = C.create_string_buffer(512)
+        _lib.check(lib.ab_problem_fused_info(self.h, min_threads, out, why, 512))
+        keys = ["ok", "anchor", "t_lo", "t_hi", "vars_per_segment", "slots_per_segment", "families", "home_families", "loads",
+                "outputs", "fma", "pieces"]
+        d = dict(zip(keys, [int(v) for v in out]))
+        d["why"] = why.value.decode()
+        return d
+
+    def fused_ptx(self, piece=0, min_threads=32):
+        n = _lib.check(lib.ab_problem_fused_ptx(self.h, min_threads, piece, None, 0))
+        if n == 0:
+            return None
+        buf = C.create_string_buffer(n + 1)
+        _lib.check(lib.ab_problem_fused_ptx(self.h, min_threads, piece, buf, n + 1))
+        return buf.value.decode()
+
     def kernel_ptx(self, f, mode=4, indexed=False):
         """PTX of the specialised kernel for function ``f``: the affine variant (None if the function has no affine
         application range) or the indexed variant that reads explicit index maps."""
@@ -404,6 +423,10 @@ class NonLinearProgram:
 
     def launches(self):
         return int(lib.ab_plan_launches(self.plan)) if self.plan else 0
+
+    def fused_segments(self):
+        """Segments evaluated by the fused owner-writes kernel in the last eval (0: per-function path only)."""
+        return int(lib.ab_plan_fused_segments(self.plan)) if self.plan else 0
 
     def specialised_launches(self):
         """How many launches of the last eval were specialised (run-time assembled) kernels."""

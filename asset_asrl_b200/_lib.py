@@ -73,10 +73,13 @@ SIGNATURES = {
     "ab_phase_transcribe": (_i, [_vp, _vp, _i, _i, _i, _ip]),
     "ab_phase_region_vindex": (_i, [_vp, _i, _ip, _i, _ip, _i, _ip, _i, _ip, _i, _ip]),
     "ab_phase_make_input": (_i, [_vp, _dp, _dp, _dp]),
+    "ab_problem_fused_info": (_ll, [_vp, _i, _llp, _cp, _ll]),
+    "ab_problem_fused_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
     "ab_plan_create": (_i, [_vp, _i, C.POINTER(_vp)]),
     "ab_plan_destroy": (None, [_vp]),
     "ab_plan_create_sharded": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
     "ab_plan_cut_count": (_ll, [_vp]),
+    "ab_plan_fused_segments": (_i, [_vp]),
     "ab_plan_output_ranges": (_i, [_vp, _i, _llp, _i]),
     "ab_plan_get_outputs_packed": (_i, [_vp, _dp, _dp, _dp, _dp, _dp, _dp]),
     "ab_plan_cut_buffer": (_vp, [_vp]),

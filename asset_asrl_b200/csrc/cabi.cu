@@ -10,6 +10,7 @@
 
 #include "../../include/asset_b200.h"
 #include "phase.hpp"
+#include "fused.hpp"
 #include "plan.hpp"
 
 using namespace ab;
@@ -522,6 +523,53 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* sp, doub
   AB_CATCH
 }
 
+// ------------------------------------------------------------------ fused interior (host side; no GPU needed)
+long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long out[12], char* why, long long cap) {
+  try {
+    FusedPlan fp = build_fused(p->p, min_threads);
+    out[0] = fp.ok ? 1 : 0;
+    out[1] = fp.anchor;
+    out[2] = fp.t_lo;
+    out[3] = fp.t_hi;
+    out[4] = fp.vs;
+    out[5] = fp.ks;
+    out[6] = (long long) fp.insts.size();
+    out[7] = fp.n_inst_home;
+    out[8] = (long long) fp.fin.size();
+    out[9] = 0;
+    out[10] = 0;
+    for (const auto& pc: fp.pieces) {
+      out[9] += (long long) pc.fout.size();
+      out[10] += pc.prog.n_fma;
+    }
+    out[11] = (long long) fp.pieces.size();
+    if (why && cap > 0) {
+      const size_t n = std::min<size_t>(fp.why.size(), (size_t) cap - 1);
+      std::memcpy(why, fp.why.data(), n);
+      why[n] = 0;
+    }
+    return AB_OK;
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
+
+long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap) {
+  try {
+    FusedPlan fp = build_fused(p->p, min_threads);
+    if (!fp.ok || piece < 0 || piece >= (int) fp.pieces.size()) return 0;
+    const std::string s = fused_ptx(fp, piece, nullptr, nullptr);
+    if (buf && cap > 0) {
+      const size_t n = std::min<size_t>(s.size(), (size_t) cap - 1);
+      std::memcpy(buf, s.data(), n);
+      buf[n] = 0;
+    }
+    return (long long) s.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
+
 // ------------------------------------------------------------------ plan
 #define PLAN_CUDA(call)                                                              \
   do {                                                                               \
@@ -560,6 +608,9 @@ int ab_plan_create_sharded(const ab_problem* p, int device, int rank, int world,
 }
 void ab_plan_destroy(ab_plan* plan) { delete plan; }
 long long ab_plan_cut_count(const ab_plan* plan) { return plan->plan.cut_count; }
+int ab_plan_fused_segments(const ab_plan* plan) {
+  return plan->plan.last_fused ? plan->plan.fused.t_hi - plan->plan.fused.t_lo : 0;
+}
 int ab_plan_output_ranges(const ab_plan* plan, int array, long long* out, int cap) {
   if (array < 0 || array >= OA_COUNT) return fail(AB_ERR_INVALID, "bad array");
   const auto& R = plan->plan.out_ranges[array];

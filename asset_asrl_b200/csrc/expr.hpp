@@ -160,7 +160,7 @@ struct Tape {
 // bundles of four mutually independent operations of one kind (instruction-level parallelism for the interpreter).
 // ---------------------------------------------------------------------------------------------
 enum PKind : uint32_t { PK_FMA = 0, PK_LOAD = 1, PK_OUT = 2, PK_SPECIAL = 3, PK_END = 4 };
-enum POut : uint32_t { PO_F = 0, PO_J = 1, PO_G = 2, PO_H = 3 };
+enum POut : uint32_t { PO_F = 0, PO_J = 1, PO_G = 2, PO_H = 3, PO_TABLE = 4 /* index into a destination table */ };
 enum PLoad : uint32_t { PL_X = 0, PL_LAMBDA = 1, PL_APPCONST = 2 };
 // Operand word: bit0 = 1 lane-private slot / 0 shared constant, bit1 = negate, bits[31:3] = index (unlinked) or
 // byte offset (linked for a block size).  The destination word of the first instruction of a bundle carries the
@@ -193,6 +193,13 @@ struct ProgramSpec {
 int triplet_offset_h(int i, int j, int ir, int orows, bool lay_h, bool lay_j);
 int triplet_offset_j(int i, int k, int ir, int orows, bool lay_h, bool lay_j);
 Program emit_program(ScalarFn& f, const ProgramSpec& spec);
+// The same scheduler over an explicit output list (in the order given); used for fused programs whose inputs and
+// outputs are entries of address tables rather than one function's argument / triplet numbers.
+struct ProgOut {
+  int node;
+  uint32_t kind, index;
+};
+Program emit_program_outs(ScalarFn& f, const std::vector<ProgOut>& outs);
 struct LinkedProgram {
   std::vector<PInstr> code;
   int nthreads = 0, nslots = 0;

@@ -20,6 +20,7 @@
 
 namespace ab {
 
+struct JitOut;
 struct JitSpec {
   std::string name;       // kernel entry name ([A-Za-z0-9_])
   int role = 1;           // FnRole
@@ -34,6 +35,11 @@ struct JitSpec {
   long long v_stage = 0;  // objective value contributions go to stage[v_stage + app]
   int nthreads = 128;     // block size (.maxntid)
   int reg_budget = 112;   // affine variant: values kept in registers; the rest are parked in shared memory
+  // fused programs (fused.hpp): loads are entries of *fin, outputs (PO_TABLE) entries of *fout, both (array, element base
+  // for rel = 0, stride per rel); array codes are FusedArr.  The multiplier array of inequalities travels in the
+  // vindex parameter slot.
+  const std::vector<JitOut>* fin = nullptr;
+  const std::vector<JitOut>* fout = nullptr;
   bool lockstep = false;        // bar.sync at every output flush: the warps of a block share instruction-cache fills
   bool prefetch_table = true;   // output-table entries of the next flush are loaded one flush ahead
   bool unroll_flush = false;    // 32 unrolled load/store pairs per output chunk instead of a loop: measured SLOWER (more straight-line code, r1j)

@@ -39,6 +39,7 @@ Plan::~Plan() {
   for (auto& v: jits)
     for (auto& a: v)
       for (JitKernel& k: a) unload_jit(k);
+  for (JitKernel& k: fused_jits) unload_jit(k);
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
   if (side) cudaStreamDestroy(side);
@@ -379,6 +380,42 @@ int Plan::build(int dev, int rank_, int world_) {
       gsrc[a] = pruned[a];
     }
   }
+  if (const char* e = getenv("ASSET_B200_FUSED")) use_fused = std::atoi(e) != 0;
+  if (use_fused && use_jit && world == 1) {
+    int npieces = 0;
+    if (const char* e = getenv("ASSET_B200_FUSED_PIECES")) npieces = std::max(0, std::atoi(e));
+    fused = build_fused(prob, jit_min_apps, npieces);
+    if (fused.ok) {
+      // targets inside the fused rows leave the gather lists of the fused evaluation
+      const long long R = fused.t_hi - fused.t_lo;
+      auto without = [&](const GatherList& g, long long lo, long long hi) {
+        GatherList o;
+        o.ptr.assign(1, 0);
+        for (int t = 0; t < g.ntargets(); t++) {
+          if (g.target[t] >= lo && g.target[t] < hi) continue;
+          o.src.insert(o.src.end(), g.src.begin() + g.ptr[t], g.src.begin() + g.ptr[(size_t) t + 1]);
+          o.ptr.push_back((long long) o.src.size());
+          o.target.push_back(g.target[t]);
+        }
+        return o;
+      };
+      GatherList fk[2], fp[2], fa[2];
+      for (int w = 0; w < 2; w++) {
+        fk[w] = without(gsrc[OA_KKT][w], fused.kb, fused.kb + R * fused.ks);
+        fp[w] = without(gsrc[OA_PGX][w], fused.vb, fused.vb + R * fused.vs);
+        fa[w] = without(gsrc[OA_AGX][w], fused.vb, fused.vb + R * fused.vs);
+      }
+      std::vector<double> appc;
+      for (const FuncRec& fr: prob.funcs) appc.insert(appc.end(), fr.appconst.begin(), fr.appconst.end());
+      d_appc_all = dupload(appc);
+      if (!up_gather(*this, fk, gkF) || !up_gather(*this, fp, gpF) || !up_gather(*this, fa, gaF) || !d_appc_all) {
+        last_error = "out of device memory for the fused evaluation's gather lists";
+        return (int) cudaErrorMemoryAllocation;
+      }
+    } else {
+      jit_log = "no fused interior: " + fused.why;
+    }
+  }
   if (!up_gather(*this, gsrc[OA_KKT], gk) || !up_gather(*this, gsrc[OA_PGX], gp) || !up_gather(*this, gsrc[OA_AGX], ga)
       || !up_gather(*this, gsrc[OA_FXE], ge) || !up_gather(*this, gsrc[OA_FXI], gi) || !up_gather(*this, gsrc[OA_VAL], gv)) {
     last_error = "out of device memory for the gather lists";
@@ -386,7 +423,7 @@ int Plan::build(int dev, int rank_, int world_) {
   }
   {
     size_t need = 1;
-    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv})
+    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF})
       need = std::max(need, (size_t) g->dev[1].ntargets * (size_t) g->dev[1].maxparts);
     d_gscratch = dalloc<double>(need);
     if (!d_gscratch) {
@@ -441,6 +478,91 @@ struct CubinEntry {
 std::mutex g_cubin_mu;
 std::unordered_map<std::string, CubinEntry> g_cubins;
 }  // namespace
+
+int Plan::ensure_fused() {
+  if (fused_state != 0) return fused_state > 0 ? 1 : 0;
+  fused_state = -1;
+  if (!fused.ok) return 0;
+  int dev_smem = 0;
+  cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  fused_jits.assign(fused.pieces.size(), JitKernel());
+  for (size_t pc = 0; pc < fused.pieces.size(); pc++) {
+    std::string ptx;
+    std::vector<JitOut> outs;
+    JitStats js;
+    try {
+      ptx = fused_ptx(fused, (int) pc, &outs, &js);
+    } catch (const std::exception& e) {
+      jit_log = std::string("fused kernel: ") + e.what();
+      return 0;
+    }
+    if ((int) js.smem_bytes > dev_smem) {
+      jit_log = "fused kernel needs " + std::to_string(js.smem_bytes) + " B of shared memory per block";
+      return 0;  // the per-function path evaluates everything
+    }
+    CubinEntry ce;
+    bool have = false;
+    {
+      std::lock_guard<std::mutex> lk(g_cubin_mu);
+      auto it = g_cubins.find(ptx);
+      if (it != g_cubins.end()) {
+        ce = it->second;
+        have = true;
+      }
+    }
+    if (!have) {
+      std::string log;
+      if (!assemble_ptx(ptx, ce.cubin, log, &ce.nregs, &ce.spill)) {
+        last_error = "fused kernel: " + log;
+        return -(int) cudaErrorInvalidPtx;
+      }
+      std::lock_guard<std::mutex> lk(g_cubin_mu);
+      g_cubins.emplace(ptx, ce);
+    }
+    JitKernel& jk = fused_jits[pc];
+    jk.smem_bytes = js.smem_bytes;
+    cudaError_t e = load_jit(ce.cubin, "ab_fused_kkt" + std::to_string(pc), jk);
+    if (e != cudaSuccess) {
+      last_error = std::string("loading the fused kernel: ") + cudaGetErrorString(e);
+      return -(int) e;
+    }
+    const size_t n = (outs.size() + 31) / 32 * 32;
+    std::vector<long long> tb(n, 0);
+    std::vector<int> ts(n, 0);
+    for (size_t q = 0; q < outs.size(); q++) {
+      const JitOut& w = outs[q];
+      double* arr = nullptr;
+      switch (w.arr) {
+        case FA_KKT: arr = d_kkt; break;
+        case FA_FXE: arr = d_fxe; break;
+        case FA_FXI: arr = d_fxi; break;
+        case FA_STAGE: arr = d_stage; break;
+        case FA_PGX: arr = d_pgx; break;
+        case FA_AGX: arr = d_agx; break;
+        default: last_error = "fused kernel: unknown output array"; return -(int) cudaErrorInvalidValue;
+      }
+      tb[q] = (long long) (uintptr_t) arr + w.base * 8;
+      ts[q] = (int) (w.stride * 8);
+    }
+    jk.out_base = dupload(tb);
+    jk.out_stride = dupload(ts);
+    if (!jk.out_base || !jk.out_stride) {
+      last_error = "out of device memory for the output table of the fused kernel";
+      return -(int) cudaErrorMemoryAllocation;
+    }
+    jk.nthreads = 64;
+    if (const char* env = getenv("ASSET_B200_JIT_THREADS")) jk.nthreads = std::max(32, std::atoi(env) / 32 * 32);
+    jk.nregs = ce.nregs;
+    jk.spill_bytes = ce.spill;
+    if (getenv("ASSET_B200_JIT_VERBOSE"))
+      fprintf(stderr, "[asset_b200] ab_fused_kkt%zu of %zu: segments [%d, %d), %zu application families, %zu loads, %zu stored "
+                      "outputs, %d FMA, %d regs, %d B assembler spill, %u B smem/block, %d parked slots, cubin %zu B\n",
+              pc, fused.pieces.size(), fused.t_lo, fused.t_hi, fused.insts.size(), fused.fin.size(), outs.size(),
+              fused.pieces[pc].prog.n_fma, ce.nregs, ce.spill, js.smem_bytes, js.parked_slots, ce.cubin.size());
+  }
+  fused_state = 1;
+  return 1;
+}
 
 int Plan::ensure_jit(size_t k, int fm, int variant) {
   if (!use_jit) return 0;
@@ -575,6 +697,13 @@ int Plan::eval(int mode, double obj_scale) {
     }
     return bulk2;
   };
+  bool fused_eval = false;
+  if (mode == EM_KKT && fused.ok && world == 1) {
+    const int fr = ensure_fused();
+    if (fr < 0) return -fr;
+    fused_eval = fr > 0;
+  }
+  last_fused = fused_eval;
   for (const FnDev& f: fns) {
     int fm = (f.role == ROLE_OBJ) ? obj_mode : con_mode;
     if (fm < 0) continue;
@@ -629,6 +758,15 @@ int Plan::eval(int mode, double obj_scale) {
       launches++;
       return prof_end();
     };
+    if (fused_eval) {
+      const int fi = prob.order[k];
+      const int xl = fused.ex_lo[fi], xh = fused.ex_hi[fi];
+      if (xh > xl) {  // the fused kernel evaluates [xl, xh): only the applications at the ends are left
+        if (int rc = rest(f.app_begin, std::min(xl, f.app_end), ":ends")) return rc;
+        if (int rc = rest(std::max(xh, f.app_begin), f.app_end, ":ends")) return rc;
+        continue;
+      }
+    }
     const int jr = ensure_jit(k, fm, 0);
     if (jr < 0) return -jr;
     const int a0 = affs[k].a0, a1 = affs[k].a1;
@@ -658,6 +796,31 @@ int Plan::eval(int mode, double obj_scale) {
     AB_CUDA(cudaEventRecord(ev_join2, bulk2));
     AB_CUDA(cudaStreamWaitEvent(stream, ev_join2, 0));
   }
+  if (fused_eval) {
+    if (int rc = prof_begin("fused")) return rc;
+    JitArgs a;
+    a.X = d_X;
+    a.L = d_LE;
+    a.kkt = d_kkt;
+    a.fx = d_fxe;
+    a.stage = d_stage;
+    a.appconst = d_appc_all;
+    a.vindex = (const int*) d_LI;  // multipliers of the inequalities (see JitSpec::fin)
+    a.cindex = nullptr;
+    a.kkt_dest = nullptr;
+    a.f_dest = nullptr;
+    a.obj_scale = obj_scale;
+    a.begin = 0;
+    a.end = fused.t_hi - fused.t_lo;
+    for (const JitKernel& jk: fused_jits) {
+      a.out_base = jk.out_base;
+      a.out_stride = jk.out_stride;
+      AB_CUDA(launch_jit(jk, a, stream));
+      launches++;
+      jit_launches++;
+    }
+    if (int rc = prof_end()) return rc;
+  }
   auto G = [&](DevGather& g, double* out, const char* label) -> int {
     const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);
     if (n == 0) return 0;
@@ -667,9 +830,9 @@ int Plan::eval(int mode, double obj_scale) {
     return prof_end();
   };
   int rc = 0;
-  if (out_kkt && (rc = G(gk, d_kkt, "gather:KKT"))) return rc;
-  if (out_pgx && (rc = G(gp, d_pgx, "gather:PGX"))) return rc;
-  if (out_agx && (rc = G(ga, d_agx, "gather:AGX"))) return rc;
+  if (out_kkt && (rc = G(fused_eval ? gkF : gk, d_kkt, "gather:KKT"))) return rc;
+  if (out_pgx && (rc = G(fused_eval ? gpF : gp, d_pgx, "gather:PGX"))) return rc;
+  if (out_agx && (rc = G(fused_eval ? gaF : ga, d_agx, "gather:AGX"))) return rc;
   if (out_fx && ((rc = G(ge, d_fxe, "gather:FXE")) || (rc = G(gi, d_fxi, "gather:FXI")))) return rc;
   if (out_val && (rc = G(gv, d_val, "gather:val"))) return rc;
   return 0;

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "device_types.h"
+#include "fused.hpp"
 #include "jit.hpp"
 #include "nlp.hpp"
 
@@ -25,7 +26,7 @@ enum EvalMode : int {
 };
 
 struct DevGather {
-  GatherDev dev[2];
+  GatherDev dev[2] = {};
   void* bufs[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -57,6 +58,19 @@ struct Plan {
   cudaEvent_t ev_join2 = nullptr;
   int heavy_fn = -1;  // index into fns
   long long jit_launches = 0;                          // specialised-kernel launches of the last eval
+
+  // Owner-writes fused interior (fused.hpp), used by evalKKT on a single device: the per-function path then covers only
+  // the applications at the mesh ends and functions outside the periodic interior, and runs first; the fused kernel
+  // runs last on the stream, so where both write a value (entries the end applications share with the first / last
+  // fused segments) the fused result stands.
+  bool use_fused = true;  // ASSET_B200_FUSED=0 switches it off
+  FusedPlan fused;
+  std::vector<JitKernel> fused_jits;  // one kernel per piece (row block)
+  signed char fused_state = 0;  // 0 not tried, 1 ready, -1 unavailable
+  DevGather gkF, gpF, gaF;      // gather lists without the targets the fused kernel writes
+  double* d_appc_all = nullptr; // per-application constants of all functions, concatenated (fused.appc_offset)
+  int ensure_fused();           // 1 ready, 0 unavailable, < 0 CUDA error (negated)
+  bool last_fused = false;      // the last eval ran the fused kernel
 
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;
   double *d_kkt = nullptr, *d_fxe = nullptr, *d_fxi = nullptr, *d_pgx = nullptr, *d_agx = nullptr, *d_val = nullptr;

@@ -175,17 +175,11 @@ struct Builder {
 Program emit_program(ScalarFn& f, const ProgramSpec& spec) {
   if ((spec.want_g || spec.want_h) && (int) f.grads.size() != f.nin) f.make_gradient();
   if ((spec.want_j || spec.want_h) && f.jac.empty()) f.make_second_order();
-  Builder B(f);
-  SDag& dag = f.dag;
   const int ir = f.nin, orr = f.nout;
   const bool lay_h = !spec.linear, lay_j = !spec.is_objective;
 
   // ---- outputs in the triplet order of DenseFunctionBase::getKKTSpace: F, then per column i: H rows j >= i, J rows, G_i
-  struct OutRec {
-    int node;
-    uint32_t kind, index;
-  };
-  std::vector<OutRec> outs;
+  std::vector<ProgOut> outs;
   if (spec.want_f)
     for (int k = 0; k < orr; k++) outs.push_back({f.outs[k], PO_F, (uint32_t) k});
   for (int i = 0; i < ir; i++) {
@@ -197,6 +191,13 @@ Program emit_program(ScalarFn& f, const ProgramSpec& spec) {
         outs.push_back({f.jac[(size_t) k * ir + i], PO_J, (uint32_t) triplet_offset_j(i, k, ir, orr, lay_h, lay_j)});
     if (spec.want_g) outs.push_back({f.grads[i], PO_G, (uint32_t) i});
   }
+  return emit_program_outs(f, outs);
+}
+
+Program emit_program_outs(ScalarFn& f, const std::vector<ProgOut>& outs) {
+  Builder B(f);
+  SDag& dag = f.dag;
+  const int ir = f.nin, orr = f.nout;
   {
     std::vector<int> roots;
     for (auto& o: outs) roots.push_back(o.node);

@@ -120,6 +120,13 @@ int ab_phase_region_vindex(ab_phase* ph, int region, const int* xtuv, int nxtuv,
 int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_params, double* X);
 
 /* ---------------- device plan ---------------- */
+/* Owner-writes fused interior of an analysed problem, host side only: out = {fusable, anchor
+ * function, first fused segment, one past the last, variables per segment, CSR slots per segment, application families
+ * per thread, of which home, distinct loads, outputs, FMAs over all pieces, number of pieces (kernels)}; `why` receives the
+ * reason when the problem has no fused interior. */
+long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long out[12], char* why, long long cap);
+/* PTX text of one piece of the fused evaluation (0 if there is none); buf == NULL only sizes. */
+long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap);
 int ab_plan_create(const ab_problem* p, int device, ab_plan** out);
 /* One rank's share of a problem split over `world` GPUs (the thread split of
  * SolverIndexingData::thread_split, src/VectorFunctions/IndexingData.h:117-146, across devices).  After ab_plan_eval:
@@ -127,6 +134,8 @@ int ab_plan_create(const ab_problem* p, int device, ab_plan** out);
  * ranks on the plan's stream (NCCL all-reduce), then ab_plan_cut_unpack.  Every output is then non-zero on exactly one
  * rank: the per-rank value arrays are disjoint slices whose sum is the reference's result. */
 int ab_plan_create_sharded(const ab_problem* p, int device, int rank, int world, ab_plan** out);
+/* Segments the fused owner-writes kernel evaluated in the last ab_plan_eval (0: the per-function path did everything). */
+int ab_plan_fused_segments(const ab_plan* plan);
 long long ab_plan_cut_count(const ab_plan* plan);
 /* Index ranges [lo, hi) of output array `array` (0 KKT values, 1 PGX, 2 AGX, 3 FXE, 4 FXI, 5 val) that a sharded plan
  * can write; returns their number and fills up to `cap` pairs.  ab_plan_get_outputs copies only these ranges into the

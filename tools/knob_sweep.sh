@@ -9,15 +9,17 @@ import json, sys
 try:
     j = json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])
     k = j["kernels_ms"]
-    print(f"{sys.argv[1]:28s} step {j['ms_per_step']:.3f} ms  defect {k.get('defect',0):.3f}  spline {k.get('control_spline',0):.3f}  gatherKKT {k.get('gather:KKT',0):.3f}")
+    print(f"{sys.argv[1]:28s} step {j['ms_per_step']:.3f} ms  fused {k.get('fused',0):.3f}  defect {k.get('defect',0):.3f}  spline {k.get('control_spline',0):.3f}  gatherKKT {k.get('gather:KKT',0):.3f}")
 except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run zrun4_default   ASSET_B200_X=0
-run zrun1           ASSET_B200_JIT_ZRUN=1
-run zrun2           ASSET_B200_JIT_ZRUN=2
-run zrun8           ASSET_B200_JIT_ZRUN=8
-run zrun16          ASSET_B200_JIT_ZRUN=16
-run zrun1000        ASSET_B200_JIT_ZRUN=1000
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+run fused_auto       ASSET_B200_X=0
+run fused_p1         ASSET_B200_FUSED_PIECES=1
+run fused_p2         ASSET_B200_FUSED_PIECES=2
+run fused_p3         ASSET_B200_FUSED_PIECES=3
+run fused_p5         ASSET_B200_FUSED_PIECES=5
+run fused_p2_t32     ASSET_B200_FUSED_PIECES=2 ASSET_B200_JIT_THREADS=32
+run fused_p4_regs96  ASSET_B200_FUSED_PIECES=4 ASSET_B200_JIT_REGS=96
+run nofused          ASSET_B200_FUSED=0
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5

@@ -264,8 +264,8 @@ class NonLinearProgram:
     def cut_tensor(self):
         """The packed cut buffer as a torch tensor aliasing the plan's device memory (no copy)."""
         import torch
-        if self._cut is None:
-            n = int(lib.ab_plan_cut_count(self.plan))
+        n = int(lib.ab_plan_cut_count(self.plan))  # depends on which evaluation ran last (fused / per-function)
+        if self._cut is None or self._cut.numel() != n:
 
             class _Raw:
                 pass

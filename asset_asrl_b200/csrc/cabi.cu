@@ -607,7 +607,7 @@ int ab_plan_create_sharded(const ab_problem* p, int device, int rank, int world,
   AB_CATCH
 }
 void ab_plan_destroy(ab_plan* plan) { delete plan; }
-long long ab_plan_cut_count(const ab_plan* plan) { return plan->plan.cut_count; }
+long long ab_plan_cut_count(const ab_plan* plan) { return plan->plan.active_cut_count(); }
 int ab_plan_fused_segments(const ab_plan* plan) {
   return plan->plan.last_fused ? plan->plan.fused.t_hi - plan->plan.fused.t_lo : 0;
 }

@@ -465,13 +465,11 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
     if (npieces > 0) {
       build_pieces(npieces);
     } else {
-      // as few pieces as keep every program under ~3500 FMAs (about 110 KB of code, ~200 live values)
-      for (int np = 1; np <= 8; np++) {
-        build_pieces(np);
-        int worst = 0;
-        for (const auto& pc: FP.pieces) worst = std::max(worst, pc.prog.n_fma);
-        if (worst <= 3500 || np >= (int) s) break;
-      }
+      // one piece per ~2600 FMAs of the whole program (sweep r1u: two pieces for the 5090-FMA LGL5 low-thrust segment;
+      // one piece leaves a single block per SM, four recompute more than they save)
+      build_pieces(1);
+      const int np = std::min<long long>(std::min<long long>(8, s), std::max(1, (FP.pieces[0].prog.n_fma + 1300) / 2600));
+      if (np > 1) build_pieces(np);
     }
   } catch (const std::exception& ex) {
     FP.why = std::string("fused program: ") + ex.what();

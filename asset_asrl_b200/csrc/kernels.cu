@@ -315,6 +315,15 @@ __global__ void __launch_bounds__(256) k_cut_unpack(double* __restrict__ arr, co
   else if (flag[i] & 1)
     arr[target[i]] = 0.0;
 }
+__global__ void __launch_bounds__(256) k_clear(double* __restrict__ arr, const int* __restrict__ idx, long long n) {
+  const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) arr[idx[i]] = 0.0;
+}
+cudaError_t launch_clear(double* arr, const int* idx, long long n, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  k_clear<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(arr, idx, n);
+  return cudaGetLastError();
+}
 cudaError_t launch_cut(bool pack, bool active, double* arr, const int* target, const unsigned char* flag, long long n,
                        double* buf, cudaStream_t st) {
   const unsigned blocks = (unsigned) ((n + 255) / 256);

@@ -175,7 +175,13 @@ int Plan::build(int dev, int rank_, int world_) {
     jits[v].clear();
     jit_state[v].clear();
   }
-  AB_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+  {
+    // the side stream carries latency-bound single-block launches (mesh ends, edge segments): highest priority, so their
+    // blocks are placed as soon as a slot frees up beside the bulk kernels
+    int prio_lo = 0, prio_hi = 0;
+    AB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    AB_CUDA(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, getenv("ASSET_B200_NO_PRIORITY") ? prio_lo : prio_hi));
+  }
   AB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   AB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   AB_CUDA(cudaStreamCreateWithFlags(&bulk2, cudaStreamNonBlocking));
@@ -298,9 +304,8 @@ int Plan::build(int dev, int rank_, int world_) {
     cut_count = part.cut_total();
     {
       const long long sizes[OA_COUNT] = {prob.nnz(), prob.nvars, prob.nvars, prob.neq, prob.niq, 1};
-      std::vector<char> blocks[OA_COUNT];
-      for (int a = 0; a < OA_COUNT; a++) blocks[a].assign((size_t) ((sizes[a] + OUT_BLOCK - 1) / OUT_BLOCK) + 1, 0);
-      auto touch = [&](int a, long long i) { blocks[a][(size_t) (i / OUT_BLOCK)] = 1; };
+      for (int a = 0; a < OA_COUNT; a++) out_blocks[a].assign((size_t) ((sizes[a] + OUT_BLOCK - 1) / OUT_BLOCK) + 1, 0);
+      auto touch = [&](int a, long long i) { out_blocks[a][(size_t) (i / OUT_BLOCK)] = 1; };
       for (int fi: prob.order) {
         const FuncRec& fr = prob.funcs[fi];
         const int E = fr.triplets_per_app();
@@ -316,25 +321,11 @@ int Plan::build(int dev, int rank_, int world_) {
             }
         }
       }
-      for (int a = 0; a < OA_COUNT; a++) {
+      for (int a = 0; a < OA_COUNT; a++)
         for (int w = 0; w < 2; w++)
           for (int t: part.g[a][w].target) touch(a, t);
-        out_ranges[a].clear();
-        const long long nb = (long long) blocks[a].size();
-        for (long long q = 0; q < nb;) {
-          if (!blocks[a][(size_t) q]) {
-            q++;
-            continue;
-          }
-          long long e = q;
-          while (e < nb && blocks[a][(size_t) e]) e++;
-          out_ranges[a].push_back({q * OUT_BLOCK, std::min(e * OUT_BLOCK, sizes[a])});
-          q = e;
-        }
-      }
     }
-    d_cutbuf = dalloc<double>((size_t) std::max<long long>(cut_count, 1));
-    bool ok = d_cutbuf != nullptr;
+    bool ok = true;
     for (int a = 0; a < OA_COUNT && ok; a++) {
       std::vector<unsigned char> flag(part.cut_target[a].size());
       for (size_t q = 0; q < flag.size(); q++)
@@ -350,7 +341,7 @@ int Plan::build(int dev, int rank_, int world_) {
   }
   // Staging slots that only ever receive a structural zero (the specialised kernels do not store those, jit.cpp) are
   // removed from the gather lists: the staging buffer is zero-filled above and the sums lose nothing.
-  GatherList pruned[OA_COUNT][2];
+  GatherList pruned[OA_COUNT][2], pruned_full[OA_COUNT][2];
   if (use_jit && !getenv("ASSET_B200_NO_PRUNE")) {
     std::vector<unsigned char> dead((size_t) std::max<long long>(prob.stage_size, 1), 0);
     for (size_t k = 0; k < fns.size(); k++) {
@@ -379,42 +370,148 @@ int Plan::build(int dev, int rank_, int world_) {
       for (int w = 0; w < 2; w++) pruned[a][w] = prune_gather(gsrc[a][w], dead);
       gsrc[a] = pruned[a];
     }
+    if (world > 1) {  // the fused evaluation of a sharded plan starts from the unpartitioned lists
+      const GatherList* full[OA_COUNT] = {prob.g_kkt, prob.g_pgx, prob.g_agx, prob.g_fxe, prob.g_fxi, prob.g_val};
+      for (int a = 0; a < OA_COUNT; a++)
+        for (int w = 0; w < 2; w++) pruned_full[a][w] = prune_gather(full[a][w], dead);
+    }
   }
   if (const char* e = getenv("ASSET_B200_FUSED")) use_fused = std::atoi(e) != 0;
-  if (use_fused && use_jit && world == 1) {
+  if (use_fused && use_jit && (world == 1 || !getenv("ASSET_B200_NO_PRUNE"))) {
     int npieces = 0;
     if (const char* e = getenv("ASSET_B200_FUSED_PIECES")) npieces = std::max(0, std::atoi(e));
     fused = build_fused(prob, jit_min_apps, npieces);
     if (fused.ok) {
-      // targets inside the fused rows leave the gather lists of the fused evaluation
       const long long R = fused.t_hi - fused.t_lo;
-      auto without = [&](const GatherList& g, long long lo, long long hi) {
-        GatherList o;
-        o.ptr.assign(1, 0);
-        for (int t = 0; t < g.ntargets(); t++) {
-          if (g.target[t] >= lo && g.target[t] < hi) continue;
-          o.src.insert(o.src.end(), g.src.begin() + g.ptr[t], g.src.begin() + g.ptr[(size_t) t + 1]);
-          o.ptr.push_back((long long) o.src.size());
-          o.target.push_back(g.target[t]);
+      // staging slots the fused kernels write (objective value per segment, entries of rows no segment owns)
+      std::vector<unsigned char> fslot;
+      if (world > 1) {
+        fslot.assign((size_t) std::max<long long>(prob.stage_size, 1), 0);
+        for (const auto& pc: fused.pieces)
+          for (const JitOut& w: pc.fout)
+            if (w.arr == FA_STAGE)  // 2: written by this rank's segments, 1: by another rank's
+              for (long long r = 0; r < R; r++)
+                fslot[(size_t) (w.base + r * w.stride)] = (r >= R * rank / world && r < R * (rank + 1) / world) ? 2 : 1;
+      }
+      // Gather lists of the fused evaluation: targets inside the fused rows are gone.  Sharded plans: rank 0 runs the
+      // per-function path of the mesh ends and owns every remaining target; the other ranks keep only the targets fed
+      // by their fused kernels' staged outputs (without the solver coefficients, which rank 0 adds) and all ranks add
+      // those up through the cut buffer.
+      const GatherList* base[OA_COUNT];
+      for (int a = 0; a < OA_COUNT; a++) base[a] = world > 1 ? pruned_full[a] : gsrc[a];
+      const long long own_lo[OA_COUNT] = {fused.kb, fused.vb, fused.vb, 0, 0, 0};
+      const long long own_hi[OA_COUNT] = {fused.kb + R * fused.ks, fused.vb + R * fused.vs, fused.vb + R * fused.vs, 0, 0, 0};
+      GatherList fl[OA_COUNT][2];
+      std::vector<int> cut_t[OA_COUNT];
+      for (int a = 0; a < OA_COUNT; a++) {
+        for (int w = 0; w < 2; w++) {
+          const GatherList& g = base[a][w];
+          GatherList& o = fl[a][w];
+          o.ptr.assign(1, 0);
+          for (int t = 0; t < g.ntargets(); t++) {
+            if (g.target[t] >= own_lo[a] && g.target[t] < own_hi[a]) continue;
+            bool fed = false;
+            if (world > 1)
+              for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) fed = fed || fslot[(size_t) g.src[(size_t) k]] != 0;
+            if (world > 1 && rank != 0 && !fed) continue;
+            for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) {
+              const int sidx = g.src[(size_t) k];
+              if (world > 1) {
+                // a rank sums what it wrote in this evaluation: its own segments' staged outputs, and on rank 0 the mesh
+                // ends' and the solver coefficients (slots of other modes' evaluations may hold stale values)
+                const unsigned char fs = fslot[(size_t) sidx];
+                if (fs == 1 || (rank != 0 && fs != 2)) continue;
+              }
+              o.src.push_back(sidx);
+            }
+            o.ptr.push_back((long long) o.src.size());
+            o.target.push_back(g.target[t]);
+            if (fed) cut_t[a].push_back(g.target[t]);
+          }
         }
-        return o;
-      };
-      GatherList fk[2], fp[2], fa[2];
-      for (int w = 0; w < 2; w++) {
-        fk[w] = without(gsrc[OA_KKT][w], fused.kb, fused.kb + R * fused.ks);
-        fp[w] = without(gsrc[OA_PGX][w], fused.vb, fused.vb + R * fused.vs);
-        fa[w] = without(gsrc[OA_AGX][w], fused.vb, fused.vb + R * fused.vs);
       }
       std::vector<double> appc;
       for (const FuncRec& fr: prob.funcs) appc.insert(appc.end(), fr.appconst.begin(), fr.appconst.end());
       d_appc_all = dupload(appc);
-      if (!up_gather(*this, fk, gkF) || !up_gather(*this, fp, gpF) || !up_gather(*this, fa, gaF) || !d_appc_all) {
+      bool ok = d_appc_all && up_gather(*this, fl[OA_KKT], gkF) && up_gather(*this, fl[OA_PGX], gpF) && up_gather(*this, fl[OA_AGX], gaF);
+      if (ok && world > 1) {
+        ok = up_gather(*this, fl[OA_FXE], geF) && up_gather(*this, fl[OA_FXI], giF) && up_gather(*this, fl[OA_VAL], gvF);
+        cutF_count = 0;
+        for (int a = 0; a < OA_COUNT && ok; a++) {
+          cutF_n[a] = (long long) cut_t[a].size();
+          cutF_count += cutF_n[a];
+          std::vector<unsigned char> flag(cut_t[a].size(), (unsigned char) (rank == 0 ? 3 : 1));
+          d_cutF_target[a] = dupload(cut_t[a]);
+          d_cutF_flag[a] = dupload(flag);
+          ok = d_cutF_target[a] && d_cutF_flag[a];
+        }
+        // what this rank writes in the fused evaluation: its segments' rows, their constraint rows and far entries;
+        // rank 0 also everything the mesh ends and the remaining gather targets touch
+        const long long r0 = R * rank / world, r1 = R * (rank + 1) / world;
+        auto touch = [&](int a, long long i) { out_blocks[a][(size_t) (i / OUT_BLOCK)] = 1; };
+        auto arr_of = [](int fa) {
+          return fa == FA_KKT ? (int) OA_KKT : fa == FA_FXE ? (int) OA_FXE : fa == FA_FXI ? (int) OA_FXI
+                 : fa == FA_PGX ? (int) OA_PGX : fa == FA_AGX ? (int) OA_AGX : -1;
+        };
+        for (const auto& pc: fused.pieces)
+          for (const JitOut& w: pc.fout) {
+            const int a = arr_of(w.arr);
+            if (a < 0 || r1 <= r0) continue;
+            const long long i0 = w.base + r0 * w.stride, i1 = w.base + (r1 - 1) * w.stride;
+            for (long long i = std::min(i0, i1) / OUT_BLOCK; i <= std::max(i0, i1) / OUT_BLOCK; i++) out_blocks[a][(size_t) i] = 1;
+          }
+        if (rank == 0) {
+          std::vector<int> clr[OA_COUNT];
+          for (const auto& pc: fused.pieces)
+            for (const JitOut& w: pc.fout) {
+              const int a = arr_of(w.arr);
+              if (a < 0) continue;
+              for (long long r = std::max(r1, R - 4); r < R; r++) clr[a].push_back((int) (w.base + r * w.stride));
+            }
+          for (int a = 0; a < OA_COUNT && ok; a++) {
+            clear_n[a] = (long long) clr[a].size();
+            d_clear[a] = dupload(clr[a]);
+            ok = d_clear[a] != nullptr;
+          }
+          for (int a = 0; a < OA_COUNT; a++)
+            for (int w = 0; w < 2; w++)
+              for (int t: fl[a][w].target) touch(a, t);
+          for (int fi: prob.order) {
+            const FuncRec& fr = prob.funcs[fi];
+            const int E = fr.triplets_per_app();
+            for (int ap = 0; ap < fr.nappl; ap++) {
+              if (ap >= fused.ex_lo[fi] && ap < fused.ex_hi[fi]) {
+                ap = fused.ex_hi[fi] - 1;
+                continue;
+              }
+              for (int e = 0; e < E; e++) {
+                const int d = prob.kkt_dest[(size_t) (prob.trip_base[fi] + (long long) ap * E + e)];
+                if (d >= 0) touch(OA_KKT, d);
+              }
+              if (fr.role != 0)
+                for (int o = 0; o < fr.orows; o++) {
+                  const int d = prob.f_dest[(size_t) (prob.fdest_base[fi] + (long long) ap * fr.orows + o)];
+                  if (d >= 0) touch(fr.role == 1 ? OA_FXE : OA_FXI, d);
+                }
+            }
+          }
+        }
+      }
+      if (!ok) {
         last_error = "out of device memory for the fused evaluation's gather lists";
         return (int) cudaErrorMemoryAllocation;
       }
     } else {
       jit_log = "no fused interior: " + fused.why;
     }
+  }
+  if (world > 1) {
+    d_cutbuf = dalloc<double>((size_t) std::max<long long>(std::max(cut_count, cutF_count), 1));
+    if (!d_cutbuf) {
+      last_error = "out of device memory for the cut buffer";
+      return (int) cudaErrorMemoryAllocation;
+    }
+    finalize_out_ranges();
   }
   if (!up_gather(*this, gsrc[OA_KKT], gk) || !up_gather(*this, gsrc[OA_PGX], gp) || !up_gather(*this, gsrc[OA_AGX], ga)
       || !up_gather(*this, gsrc[OA_FXE], ge) || !up_gather(*this, gsrc[OA_FXI], gi) || !up_gather(*this, gsrc[OA_VAL], gv)) {
@@ -423,7 +520,7 @@ int Plan::build(int dev, int rank_, int world_) {
   }
   {
     size_t need = 1;
-    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF})
+    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF, &geF, &giF, &gvF})
       need = std::max(need, (size_t) g->dev[1].ntargets * (size_t) g->dev[1].maxparts);
     d_gscratch = dalloc<double>(need);
     if (!d_gscratch) {
@@ -497,8 +594,17 @@ int Plan::ensure_fused() {
       return 0;
     }
     if ((int) js.smem_bytes > dev_smem) {
-      jit_log = "fused kernel needs " + std::to_string(js.smem_bytes) + " B of shared memory per block";
-      return 0;  // the per-function path evaluates everything
+      // too many values alive for one block: cut the rows into more pieces and start over
+      const int np = (int) fused.pieces.size() + 1;
+      if (np > 8 || np > fused.vs) {
+        jit_log = "fused kernel needs " + std::to_string(js.smem_bytes) + " B of shared memory per block";
+        return 0;  // the per-function path evaluates everything
+      }
+      for (JitKernel& k: fused_jits) unload_jit(k);
+      fused = build_fused(prob, jit_min_apps, np);
+      if (!fused.ok) return 0;
+      fused_state = 0;
+      return ensure_fused();
     }
     CubinEntry ce;
     bool have = false;
@@ -698,16 +804,35 @@ int Plan::eval(int mode, double obj_scale) {
     return bulk2;
   };
   bool fused_eval = false;
-  if (mode == EM_KKT && fused.ok && world == 1) {
+  if (mode == EM_KKT && fused.ok) {
     const int fr = ensure_fused();
     if (fr < 0) return -fr;
     fused_eval = fr > 0;
+  }
+  if (world > 1 && fused_eval != last_fused) {
+    // The fused evaluation and the per-function evaluation split the outputs between the ranks along slightly different
+    // lines; entries this rank wrote under the other split must read as zero again ("every output is non-zero on
+    // exactly one rank").
+    AB_CUDA(cudaMemsetAsync(d_kkt, 0, sizeof(double) * (size_t) prob.nnz(), stream));
+    AB_CUDA(cudaMemsetAsync(d_fxe, 0, sizeof(double) * (size_t) std::max(prob.neq, 1), stream));
+    AB_CUDA(cudaMemsetAsync(d_fxi, 0, sizeof(double) * (size_t) std::max(prob.niq, 1), stream));
+    AB_CUDA(cudaMemsetAsync(d_pgx, 0, sizeof(double) * (size_t) std::max(prob.nvars, 1), stream));
+    AB_CUDA(cudaMemsetAsync(d_agx, 0, sizeof(double) * (size_t) std::max(prob.nvars, 1), stream));
+    AB_CUDA(cudaMemsetAsync(d_val, 0, sizeof(double), stream));
   }
   last_fused = fused_eval;
   for (const FnDev& f: fns) {
     int fm = (f.role == ROLE_OBJ) ? obj_mode : con_mode;
     if (fm < 0) continue;
     const size_t k = (size_t) (&f - fns.data());
+    // applications this plan evaluates through the per-function kernels: its share of the function, except in the fused
+    // evaluation of a sharded plan, where rank 0 alone runs what the fused kernels leave (the mesh ends)
+    int fb = f.app_begin, fe = f.app_end;
+    if (fused_eval && world > 1) {
+      if (rank != 0) continue;
+      fb = 0;
+      fe = prob.funcs[prob.order[k]].nappl;
+    }
     const std::string& name = prob.funcs[prob.order[k]].name;
     EvalIO io;
     io.X = d_X;
@@ -762,15 +887,15 @@ int Plan::eval(int mode, double obj_scale) {
       const int fi = prob.order[k];
       const int xl = fused.ex_lo[fi], xh = fused.ex_hi[fi];
       if (xh > xl) {  // the fused kernel evaluates [xl, xh): only the applications at the ends are left
-        if (int rc = rest(f.app_begin, std::min(xl, f.app_end), ":ends")) return rc;
-        if (int rc = rest(std::max(xh, f.app_begin), f.app_end, ":ends")) return rc;
+        if (int rc = rest(fb, std::min(xl, fe), ":ends")) return rc;
+        if (int rc = rest(std::max(xh, fb), fe, ":ends")) return rc;
         continue;
       }
     }
     const int jr = ensure_jit(k, fm, 0);
     if (jr < 0) return -jr;
     const int a0 = affs[k].a0, a1 = affs[k].a1;
-    const int jb = std::max(a0, f.app_begin), je = std::min(a1, f.app_end);
+    const int jb = std::max(a0, fb), je = std::min(a1, fe);
     if (jr > 0 && je > jb) {
       if (int rc = prof_begin(name)) return rc;
       JitArgs a = ja;
@@ -782,11 +907,53 @@ int Plan::eval(int mode, double obj_scale) {
       launches++;
       jit_launches++;
       if (int rc = prof_end()) return rc;
-      if (int rc = rest(f.app_begin, jb, ":ends")) return rc;
-      if (int rc = rest(je, f.app_end, ":ends")) return rc;
+      if (int rc = rest(fb, jb, ":ends")) return rc;
+      if (int rc = rest(je, fe, ":ends")) return rc;
     } else {
-      if (int rc = rest(f.app_begin, f.app_end, "")) return rc;
+      if (int rc = rest(fb, fe, "")) return rc;
     }
+  }
+  // Fused kernels.  Only the first and last 64 fused segments share entries with the applications at the mesh ends
+  // (evaluated above on the side stream); they are launched after that stream has been joined, so that where both
+  // write a value the fused result stands.  Everything between runs concurrently with the mesh ends.
+  JitArgs fa;
+  long long f_b = 0, f_e = 0, f_blo = 0, f_bhi = 0;
+  auto fused_launch = [&](long long lo, long long hi, cudaStream_t st) -> int {
+    if (hi <= lo) return 0;
+    fa.begin = (int) lo;
+    fa.end = (int) hi;
+    for (const JitKernel& jk: fused_jits) {
+      fa.out_base = jk.out_base;
+      fa.out_stride = jk.out_stride;
+      AB_CUDA(launch_jit(jk, fa, st));
+      launches++;
+      jit_launches++;
+    }
+    return 0;
+  };
+  if (fused_eval) {
+    if (int rc = prof_begin("fused")) return rc;
+    fa.X = d_X;
+    fa.L = d_LE;
+    fa.kkt = d_kkt;
+    fa.fx = d_fxe;
+    fa.stage = d_stage;
+    fa.appconst = d_appc_all;
+    fa.vindex = (const int*) d_LI;  // multipliers of the inequalities (see JitSpec::fin)
+    fa.cindex = nullptr;
+    fa.kkt_dest = nullptr;
+    fa.f_dest = nullptr;
+    fa.obj_scale = obj_scale;
+    const long long R = fused.t_hi - fused.t_lo, EDGE = getenv("ASSET_B200_NO_EDGE_SPLIT") ? 0 : 64;
+    f_b = R * rank / world;
+    f_e = R * (rank + 1) / world;
+    f_blo = f_b < EDGE ? std::min(f_e, EDGE) : f_b;
+    f_bhi = f_e > R - EDGE ? std::max(f_blo, R - EDGE) : f_e;
+    if (int rc = fused_launch(f_blo, f_bhi, stream)) return rc;
+    // the edge segments follow the mesh ends on the side stream, beside the bulk
+    cudaStream_t es = small_stream();
+    if (int rc = fused_launch(f_b, f_blo, es)) return rc;
+    if (int rc = fused_launch(f_bhi, f_e, es)) return rc;
   }
   if (forked) {
     AB_CUDA(cudaEventRecord(ev_join, side));
@@ -797,27 +964,13 @@ int Plan::eval(int mode, double obj_scale) {
     AB_CUDA(cudaStreamWaitEvent(stream, ev_join2, 0));
   }
   if (fused_eval) {
-    if (int rc = prof_begin("fused")) return rc;
-    JitArgs a;
-    a.X = d_X;
-    a.L = d_LE;
-    a.kkt = d_kkt;
-    a.fx = d_fxe;
-    a.stage = d_stage;
-    a.appconst = d_appc_all;
-    a.vindex = (const int*) d_LI;  // multipliers of the inequalities (see JitSpec::fin)
-    a.cindex = nullptr;
-    a.kkt_dest = nullptr;
-    a.f_dest = nullptr;
-    a.obj_scale = obj_scale;
-    a.begin = 0;
-    a.end = fused.t_hi - fused.t_lo;
-    for (const JitKernel& jk: fused_jits) {
-      a.out_base = jk.out_base;
-      a.out_stride = jk.out_stride;
-      AB_CUDA(launch_jit(jk, a, stream));
-      launches++;
-      jit_launches++;
+    if (world > 1 && rank == 0) {
+      double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
+      for (int a = 0; a < OA_COUNT; a++)
+        if (clear_n[a] > 0) {
+          AB_CUDA(launch_clear(arrs[a], d_clear[a], clear_n[a], stream));
+          launches++;
+        }
     }
     if (int rc = prof_end()) return rc;
   }
@@ -833,8 +986,9 @@ int Plan::eval(int mode, double obj_scale) {
   if (out_kkt && (rc = G(fused_eval ? gkF : gk, d_kkt, "gather:KKT"))) return rc;
   if (out_pgx && (rc = G(fused_eval ? gpF : gp, d_pgx, "gather:PGX"))) return rc;
   if (out_agx && (rc = G(fused_eval ? gaF : ga, d_agx, "gather:AGX"))) return rc;
-  if (out_fx && ((rc = G(ge, d_fxe, "gather:FXE")) || (rc = G(gi, d_fxi, "gather:FXI")))) return rc;
-  if (out_val && (rc = G(gv, d_val, "gather:val"))) return rc;
+  const bool fsh = fused_eval && world > 1;
+  if (out_fx && ((rc = G(fsh ? geF : ge, d_fxe, "gather:FXE")) || (rc = G(fsh ? giF : gi, d_fxi, "gather:FXI")))) return rc;
+  if (out_val && (rc = G(fsh ? gvF : gv, d_val, "gather:val"))) return rc;
   return 0;
 }
 
@@ -852,17 +1006,37 @@ static void mode_outputs(int mode, bool out[OA_COUNT]) {
   out[OA_VAL] = val;
 }
 
+void Plan::finalize_out_ranges() {
+  const long long sizes[OA_COUNT] = {prob.nnz(), prob.nvars, prob.nvars, prob.neq, prob.niq, 1};
+  for (int a = 0; a < OA_COUNT; a++) {
+    out_ranges[a].clear();
+    const long long nb = (long long) out_blocks[a].size();
+    for (long long q = 0; q < nb;) {
+      if (!out_blocks[a][(size_t) q]) {
+        q++;
+        continue;
+      }
+      long long e = q;
+      while (e < nb && out_blocks[a][(size_t) e]) e++;
+      out_ranges[a].push_back({q * OUT_BLOCK, std::min(e * OUT_BLOCK, sizes[a])});
+      q = e;
+    }
+    std::vector<char>().swap(out_blocks[a]);
+  }
+}
+
 int Plan::cut_pack() {
-  if (world <= 1 || cut_count == 0) return 0;
+  if (world <= 1 || active_cut_count() == 0) return 0;
   AB_CUDA(cudaSetDevice(device));
   bool on[OA_COUNT];
   mode_outputs(last_mode, on);
   double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
   long long off = 0;
   for (int a = 0; a < OA_COUNT; a++) {
-    const long long n = (long long) part.cut_target[a].size();
+    const long long n = last_fused ? cutF_n[a] : (long long) part.cut_target[a].size();
     if (n > 0) {
-      AB_CUDA(launch_cut(true, on[a], arrs[a], d_cut_target[a], d_cut_flag[a], n, d_cutbuf + off, stream));
+      AB_CUDA(launch_cut(true, on[a], arrs[a], last_fused ? d_cutF_target[a] : d_cut_target[a],
+                         last_fused ? d_cutF_flag[a] : d_cut_flag[a], n, d_cutbuf + off, stream));
       launches++;
     }
     off += n;
@@ -871,16 +1045,17 @@ int Plan::cut_pack() {
 }
 
 int Plan::cut_unpack() {
-  if (world <= 1 || cut_count == 0) return 0;
+  if (world <= 1 || active_cut_count() == 0) return 0;
   AB_CUDA(cudaSetDevice(device));
   bool on[OA_COUNT];
   mode_outputs(last_mode, on);
   double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
   long long off = 0;
   for (int a = 0; a < OA_COUNT; a++) {
-    const long long n = (long long) part.cut_target[a].size();
+    const long long n = last_fused ? cutF_n[a] : (long long) part.cut_target[a].size();
     if (n > 0 && on[a]) {
-      AB_CUDA(launch_cut(false, true, arrs[a], d_cut_target[a], d_cut_flag[a], n, d_cutbuf + off, stream));
+      AB_CUDA(launch_cut(false, true, arrs[a], last_fused ? d_cutF_target[a] : d_cut_target[a],
+                         last_fused ? d_cutF_flag[a] : d_cut_flag[a], n, d_cutbuf + off, stream));
       launches++;
     }
     off += n;

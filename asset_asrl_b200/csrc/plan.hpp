@@ -68,6 +68,18 @@ struct Plan {
   std::vector<JitKernel> fused_jits;  // one kernel per piece (row block)
   signed char fused_state = 0;  // 0 not tried, 1 ready, -1 unavailable
   DevGather gkF, gpF, gaF;      // gather lists without the targets the fused kernel writes
+  DevGather geF, giF, gvF;      // sharded plans: this rank's share of the constraint-row / objective-value lists
+  // cut set of the fused evaluation on a sharded plan: every gather target fed by the fused kernels' staged outputs
+  // (objective value, entries of rows no segment owns); rank 0 owns them all
+  int* d_cutF_target[OA_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  unsigned char* d_cutF_flag[OA_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  long long cutF_n[OA_COUNT] = {0, 0, 0, 0, 0, 0};
+  long long cutF_count = 0;
+  // rank 0 of a sharded plan evaluates the applications at the far mesh end as well; what they write into entries that
+  // the last rank's fused kernels own is cleared again on rank 0 (indices per output array)
+  int* d_clear[OA_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  long long clear_n[OA_COUNT] = {0, 0, 0, 0, 0, 0};
+  long long active_cut_count() const { return last_fused ? cutF_count : cut_count; }
   double* d_appc_all = nullptr; // per-application constants of all functions, concatenated (fused.appc_offset)
   int ensure_fused();           // 1 ready, 0 unavailable, < 0 CUDA error (negated)
   bool last_fused = false;      // the last eval ran the fused kernel
@@ -102,6 +114,8 @@ struct Plan {
   // targets, at a granularity of OUT_BLOCK elements); the read-back of a sharded plan copies only these ranges
   static constexpr long long OUT_BLOCK = 1 << 16;
   std::vector<std::array<long long, 2>> out_ranges[OA_COUNT];
+  std::vector<char> out_blocks[OA_COUNT];  // touched blocks, collected while the plan is built
+  void finalize_out_ranges();
   int last_mode = 0;
   int cut_pack();    // after eval(): partial sums of the cut set -> cut buffer (zeros where this rank has no sources)
   int cut_unpack();  // after the all-reduce: the owner keeps the sum, other contributors clear their partial
@@ -120,6 +134,7 @@ cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io);
 // pack: buf[i] = (active && mine) ? arr[target[i]] : 0;  unpack: owner: arr[target[i]] = buf[i], other contributors: 0
 cudaError_t launch_cut(bool pack, bool active, double* arr, const int* target, const unsigned char* flag, long long n,
                        double* buf, cudaStream_t st);
+cudaError_t launch_clear(double* arr, const int* idx, long long n, cudaStream_t st);  // arr[idx[i]] = 0
 cudaError_t launch_gather(const GatherDev& small, const GatherDev& large, const double* stage, double* out,
                           double* scratch /* large.ntargets * large.maxparts partial sums */, cudaStream_t st);
 

@@ -14,12 +14,7 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run fused_auto       ASSET_B200_X=0
-run fused_p1         ASSET_B200_FUSED_PIECES=1
-run fused_p2         ASSET_B200_FUSED_PIECES=2
-run fused_p3         ASSET_B200_FUSED_PIECES=3
-run fused_p5         ASSET_B200_FUSED_PIECES=5
-run fused_p2_t32     ASSET_B200_FUSED_PIECES=2 ASSET_B200_JIT_THREADS=32
-run fused_p4_regs96  ASSET_B200_FUSED_PIECES=4 ASSET_B200_JIT_REGS=96
-run nofused          ASSET_B200_FUSED=0
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+run prio_edge        ASSET_B200_X=0
+run noprio_edge      ASSET_B200_NO_PRIORITY=1
+run prio_noedge      ASSET_B200_NO_EDGE_SPLIT=1
+run noprio_noedge    ASSET_B200_NO_PRIORITY=1 ASSET_B200_NO_EDGE_SPLIT=1

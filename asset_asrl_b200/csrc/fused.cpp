@@ -3,6 +3,7 @@
 #include "fused.hpp"
 
 #include <algorithm>
+#include <cstdlib>
 #include <map>
 #include <stdexcept>
 #include <tuple>
@@ -488,6 +489,10 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   sp.fin = &fp.fin;
   sp.fout = &fp.pieces.at((size_t) piece).fout;
   jit_env_knobs(sp);
+  // knobs of the fused kernels alone (sweeps)
+  if (const char* e = getenv("ASSET_B200_FUSED_ZRUN")) sp.zero_run_min = std::max(1, std::atoi(e));
+  if (const char* e = getenv("ASSET_B200_FUSED_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
+  if (const char* e = getenv("ASSET_B200_FUSED_THREADS")) sp.nthreads = std::max(32, std::atoi(e) / 32 * 32);
   AffineMaps am;
   am.a0 = 0;
   am.a1 = fp.t_hi - fp.t_lo;

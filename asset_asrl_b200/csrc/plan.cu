@@ -408,15 +408,36 @@ int Plan::build(int dev, int rank_, int world_) {
           const GatherList& g = base[a][w];
           GatherList& o = fl[a][w];
           o.ptr.assign(1, 0);
+          // solver-only targets of this list (outside the fused rows), for an even spread over the ranks
+          long long total_solver_only = 0, n_solver_only = 0;
+          if (world > 1)
+            for (int t = 0; t < g.ntargets(); t++) {
+              if (g.target[t] >= own_lo[a] && g.target[t] < own_hi[a]) continue;
+              bool so = g.ptr[(size_t) t + 1] > g.ptr[t];
+              for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1] && so; k++) {
+                const int sidx = g.src[(size_t) k];
+                if (sidx < prob.stage_solver || sidx >= prob.stage_solver + prob.n_solver) so = false;
+              }
+              if (so) total_solver_only++;
+            }
           for (int t = 0; t < g.ntargets(); t++) {
             if (g.target[t] >= own_lo[a] && g.target[t] < own_hi[a]) continue;
             bool fed = false;
             if (world > 1)
               for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) fed = fed || fslot[(size_t) g.src[(size_t) k]] != 0;
-            if (world > 1 && rank != 0 && !fed) continue;
+            // targets fed only by solver coefficients (pivot and slack rows: most of what is left) are spread over the
+            // ranks by position; everything else that no fused kernel feeds belongs to rank 0, which runs the mesh ends
+            bool solver_only = world > 1 && !fed && g.ptr[(size_t) t + 1] > g.ptr[t];
+            if (solver_only)
+              for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) {
+                const int sidx = g.src[(size_t) k];
+                if (sidx < prob.stage_solver || sidx >= prob.stage_solver + prob.n_solver) solver_only = false;
+              }
+            const int towner = solver_only ? (int) (n_solver_only++ * world / std::max<long long>(total_solver_only, 1)) : 0;
+            if (world > 1 && !fed && rank != towner) continue;
             for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) {
               const int sidx = g.src[(size_t) k];
-              if (world > 1) {
+              if (world > 1 && !solver_only) {
                 // a rank sums what it wrote in this evaluation: its own segments' staged outputs, and on rank 0 the mesh
                 // ends' and the solver coefficients (slots of other modes' evaluations may hold stale values)
                 const unsigned char fs = fslot[(size_t) sidx];
@@ -460,6 +481,9 @@ int Plan::build(int dev, int rank_, int world_) {
             const long long i0 = w.base + r0 * w.stride, i1 = w.base + (r1 - 1) * w.stride;
             for (long long i = std::min(i0, i1) / OUT_BLOCK; i <= std::max(i0, i1) / OUT_BLOCK; i++) out_blocks[a][(size_t) i] = 1;
           }
+        for (int a = 0; a < OA_COUNT; a++)
+          for (int w = 0; w < 2; w++)
+            for (int t: fl[a][w].target) touch(a, t);
         if (rank == 0) {
           std::vector<int> clr[OA_COUNT];
           for (const auto& pc: fused.pieces)
@@ -473,9 +497,6 @@ int Plan::build(int dev, int rank_, int world_) {
             d_clear[a] = dupload(clr[a]);
             ok = d_clear[a] != nullptr;
           }
-          for (int a = 0; a < OA_COUNT; a++)
-            for (int w = 0; w < 2; w++)
-              for (int t: fl[a][w].target) touch(a, t);
           for (int fi: prob.order) {
             const FuncRec& fr = prob.funcs[fi];
             const int E = fr.triplets_per_app();
@@ -658,6 +679,7 @@ int Plan::ensure_fused() {
     }
     jk.nthreads = 64;
     if (const char* env = getenv("ASSET_B200_JIT_THREADS")) jk.nthreads = std::max(32, std::atoi(env) / 32 * 32);
+    if (const char* env = getenv("ASSET_B200_FUSED_THREADS")) jk.nthreads = std::max(32, std::atoi(env) / 32 * 32);
     jk.nregs = ce.nregs;
     jk.spill_bytes = ce.spill;
     if (getenv("ASSET_B200_JIT_VERBOSE"))

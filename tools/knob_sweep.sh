@@ -14,7 +14,11 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run prio_edge        ASSET_B200_X=0
-run noprio_edge      ASSET_B200_NO_PRIORITY=1
-run prio_noedge      ASSET_B200_NO_EDGE_SPLIT=1
-run noprio_noedge    ASSET_B200_NO_PRIORITY=1 ASSET_B200_NO_EDGE_SPLIT=1
+run fz_default       ASSET_B200_JIT_VERBOSE=1
+run fz_zrun1000      ASSET_B200_FUSED_ZRUN=1000
+run fz_zrun4         ASSET_B200_FUSED_ZRUN=4
+run fz_t32           ASSET_B200_FUSED_THREADS=32 ASSET_B200_JIT_VERBOSE=1
+run fz_regs96        ASSET_B200_FUSED_REGS=96
+run fz_regs120       ASSET_B200_FUSED_REGS=120
+run fz_t32_zrun1000  ASSET_B200_FUSED_THREADS=32 ASSET_B200_FUSED_ZRUN=1000
+grep -h "ab_fused" $O/fz_default.err $O/fz_t32.err | cut -c1-260

@@ -940,14 +940,27 @@ int Plan::eval(int mode, double obj_scale) {
   // write a value the fused result stands.  Everything between runs concurrently with the mesh ends.
   JitArgs fa;
   long long f_b = 0, f_e = 0, f_blo = 0, f_bhi = 0;
-  auto fused_launch = [&](long long lo, long long hi, cudaStream_t st) -> int {
+  // `spread`: the pieces write disjoint rows, so odd pieces go to the second bulk stream and run beside the even ones
+  // (the piece holding the shared node leaves room for another block per SM)
+  const bool spread_pieces = overlap && !getenv("ASSET_B200_NO_PIECE_OVERLAP");
+  auto fused_launch = [&](long long lo, long long hi, cudaStream_t st, bool spread = false) -> int {
     if (hi <= lo) return 0;
     fa.begin = (int) lo;
     fa.end = (int) hi;
-    for (const JitKernel& jk: fused_jits) {
+    for (size_t pc = 0; pc < fused_jits.size(); pc++) {
+      const JitKernel& jk = fused_jits[pc];
       fa.out_base = jk.out_base;
       fa.out_stride = jk.out_stride;
-      AB_CUDA(launch_jit(jk, fa, st));
+      cudaStream_t use = st;
+      if (spread && spread_pieces && (pc & 1)) {
+        if (!forked2) {
+          if (!forked) cudaEventRecord(ev_fork, stream);
+          cudaStreamWaitEvent(bulk2, ev_fork, 0);
+          forked2 = true;
+        }
+        use = bulk2;
+      }
+      AB_CUDA(launch_jit(jk, fa, use));
       launches++;
       jit_launches++;
     }
@@ -971,7 +984,16 @@ int Plan::eval(int mode, double obj_scale) {
     f_e = R * (rank + 1) / world;
     f_blo = f_b < EDGE ? std::min(f_e, EDGE) : f_b;
     f_bhi = f_e > R - EDGE ? std::max(f_blo, R - EDGE) : f_e;
-    if (int rc = fused_launch(f_blo, f_bhi, stream)) return rc;
+    if (overlap && !forked) {  // fork the side streams before the bulk is queued, or they would wait for it
+      cudaEventRecord(ev_fork, stream);
+      cudaStreamWaitEvent(side, ev_fork, 0);
+      forked = true;
+    }
+    if (spread_pieces && fused_jits.size() > 1 && !forked2) {
+      cudaStreamWaitEvent(bulk2, ev_fork, 0);
+      forked2 = true;
+    }
+    if (int rc = fused_launch(f_blo, f_bhi, stream, true)) return rc;
     // the edge segments follow the mesh ends on the side stream, beside the bulk
     cudaStream_t es = small_stream();
     if (int rc = fused_launch(f_b, f_blo, es)) return rc;

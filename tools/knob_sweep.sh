@@ -14,11 +14,7 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run fz_default       ASSET_B200_JIT_VERBOSE=1
-run fz_zrun1000      ASSET_B200_FUSED_ZRUN=1000
-run fz_zrun4         ASSET_B200_FUSED_ZRUN=4
-run fz_t32           ASSET_B200_FUSED_THREADS=32 ASSET_B200_JIT_VERBOSE=1
-run fz_regs96        ASSET_B200_FUSED_REGS=96
-run fz_regs120       ASSET_B200_FUSED_REGS=120
-run fz_t32_zrun1000  ASSET_B200_FUSED_THREADS=32 ASSET_B200_FUSED_ZRUN=1000
-grep -h "ab_fused" $O/fz_default.err $O/fz_t32.err | cut -c1-260
+run piece_overlap    ASSET_B200_X=0
+run piece_serial     ASSET_B200_NO_PIECE_OVERLAP=1
+run piece_overlap_z  ASSET_B200_FUSED_ZRUN=1000
+timeout 900 python -m pytest tests/test_gpu_fused.py tests/test_gpu_multi.py -m gpu -x -q 2>&1 | tail -3

@@ -466,10 +466,11 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
     if (npieces > 0) {
       build_pieces(npieces);
     } else {
-      // one piece per ~2600 FMAs of the whole program (sweep r1u: two pieces for the 5090-FMA LGL5 low-thrust segment;
-      // one piece leaves a single block per SM, four recompute more than they save)
+      // one piece per ~1300 FMAs of the whole program (sweep r2g, 32-thread blocks with zero runs written out: four
+      // pieces for the 5090-FMA LGL5 low-thrust segment run the step in 0.81 ms, two in 0.88, one leaves a single
+      // block per SM)
       build_pieces(1);
-      const int np = std::min<long long>(std::min<long long>(8, s), std::max(1, (FP.pieces[0].prog.n_fma + 1300) / 2600));
+      const int np = std::min<long long>(std::min<long long>(8, s), std::max(1, (FP.pieces[0].prog.n_fma + 650) / 1300));
       if (np > 1) build_pieces(np);
     }
   } catch (const std::exception& ex) {
@@ -485,7 +486,12 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   sp.name = "ab_fused_kkt" + std::to_string(piece);
   sp.role = 1;  // multipliers and the objective scale are table entries, not the role's implicit operand
   sp.indexed = false;
-  sp.nthreads = 64;
+  // One warp per block and every zero between stored values written (ncu, capture r2f): with the structural zeros left
+  // out the region has holes, and partly written sectors cost 1.03 GB of DRAM fill reads per 200 k segments; written
+  // out, the region is one contiguous stream (reads drop to 0.25 GB) and the kernels become latency-bound, where the
+  // smaller block's third resident warp per SM helps.
+  sp.nthreads = 32;
+  sp.zero_run_min = 1000;
   sp.fin = &fp.fin;
   sp.fout = &fp.pieces.at((size_t) piece).fout;
   jit_env_knobs(sp);

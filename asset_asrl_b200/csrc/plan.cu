@@ -677,7 +677,7 @@ int Plan::ensure_fused() {
       last_error = "out of device memory for the output table of the fused kernel";
       return -(int) cudaErrorMemoryAllocation;
     }
-    jk.nthreads = 64;
+    jk.nthreads = 32;
     if (const char* env = getenv("ASSET_B200_JIT_THREADS")) jk.nthreads = std::max(32, std::atoi(env) / 32 * 32);
     if (const char* env = getenv("ASSET_B200_FUSED_THREADS")) jk.nthreads = std::max(32, std::atoi(env) / 32 * 32);
     jk.nregs = ce.nregs;

@@ -452,26 +452,74 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
   for (const Extra& x: far_out) recs.push_back({x.where, x.node, -1});
   fused.nin = (int) FP.fin.size();
   fused.nout = (int) recs.size();
-  auto build_pieces = [&](int np) {
+  // pieces are blocks of whole owned rows; bnd holds the np+1 row boundaries
+  auto build_pieces = [&](const std::vector<long long>& bnd) {
+    const int np = (int) bnd.size() - 1;
     FP.pieces.assign((size_t) np, FusedPlan::Piece());
     std::vector<std::vector<ProgOut>> outs((size_t) np);
     for (const Rec& r: recs) {
-      const int pc = r.row < 0 ? np - 1 : (int) std::min<long long>(np - 1, r.row * np / s);
+      const int pc = r.row < 0 ? np - 1 : (int) (std::upper_bound(bnd.begin() + 1, bnd.end() - 1, r.row) - bnd.begin()) - 1;
       FP.pieces[(size_t) pc].fout.push_back(r.where);
       outs[(size_t) pc].push_back({r.node, PO_TABLE, (uint32_t) FP.pieces[(size_t) pc].fout.size() - 1});
     }
     for (int pc = 0; pc < np; pc++) FP.pieces[(size_t) pc].prog = emit_program_outs(fused, outs[(size_t) pc]);
   };
+  auto even = [&](int np) {
+    std::vector<long long> bnd((size_t) np + 1);
+    for (int i = 0; i <= np; i++) bnd[(size_t) i] = (s * i + np - 1) / np;
+    return bnd;
+  };
+  auto cost = [&](int pc) { return (double) FP.pieces[(size_t) pc].prog.n_fma + 2.0 * (double) FP.pieces[(size_t) pc].fout.size(); };
+  // Experimental (ASSET_B200_FUSED_BALANCE=1): the rows are far from equally expensive (the first node's rows of an
+  // LGL5 segment carry twice the arithmetic of the second's); move the boundaries towards equal-cost quantiles, taking
+  // the cost of a piece as spread evenly over its rows, and keep the split whose largest piece is smallest.  Off by
+  // default: the pieces run back to back at full width (sweep r2h: two-stream overlap gains 2%), so their sum counts,
+  // not the largest, and the even split has the smaller sum.
+  auto balance = [&](int np) {
+    std::vector<long long> bnd = even(np), best = bnd;
+    double best_max = 1e300;
+    for (int it = 0; it < 4; it++) {
+      build_pieces(bnd);
+      double total = 0, mx = 0;
+      for (int pc = 0; pc < np; pc++) total += cost(pc), mx = std::max(mx, cost(pc));
+      if (mx < best_max) best_max = mx, best = bnd;
+      std::vector<double> cum((size_t) s + 1, 0.0);  // cumulative cost at each row boundary
+      for (int pc = 0; pc < np; pc++) {
+        const long long lo = bnd[(size_t) pc], hi = bnd[(size_t) pc + 1];
+        for (long long r = lo; r < hi; r++) cum[(size_t) r + 1] = cum[(size_t) r] + cost(pc) / (double) (hi - lo);
+      }
+      std::vector<long long> nb((size_t) np + 1, 0);
+      nb[(size_t) np] = s;
+      for (int i = 1; i < np; i++) {
+        const double want = total * i / np;
+        long long r = std::lower_bound(cum.begin(), cum.end(), want) - cum.begin();
+        if (r > 0 && want - cum[(size_t) r - 1] < cum[(size_t) r] - want) r--;
+        nb[(size_t) i] = std::min<long long>(s - (np - i), std::max<long long>(nb[(size_t) i - 1] + 1, r));
+      }
+      if (nb == bnd) break;
+      bnd = nb;
+    }
+    if (best != bnd || FP.pieces.size() != (size_t) np) build_pieces(best);
+    else {
+      double mx = 0;
+      for (int pc = 0; pc < np; pc++) mx = std::max(mx, cost(pc));
+      if (mx > best_max) build_pieces(best);
+    }
+  };
   try {
     if (npieces > 0) {
-      build_pieces(npieces);
+      if (getenv("ASSET_B200_FUSED_BALANCE")) balance((int) std::min<long long>(npieces, s));
+      else build_pieces(even((int) std::min<long long>(npieces, s)));
     } else {
       // one piece per ~1300 FMAs of the whole program (sweep r2g, 32-thread blocks with zero runs written out: four
       // pieces for the 5090-FMA LGL5 low-thrust segment run the step in 0.81 ms, two in 0.88, one leaves a single
       // block per SM)
-      build_pieces(1);
+      build_pieces(even(1));
       const int np = std::min<long long>(std::min<long long>(8, s), std::max(1, (FP.pieces[0].prog.n_fma + 650) / 1300));
-      if (np > 1) build_pieces(np);
+      if (np > 1) {
+        if (getenv("ASSET_B200_FUSED_BALANCE")) balance(np);
+        else build_pieces(even(np));
+      }
     }
   } catch (const std::exception& ex) {
     FP.why = std::string("fused program: ") + ex.what();
@@ -492,10 +540,12 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   // smaller block's third resident warp per SM helps.
   sp.nthreads = 32;
   sp.zero_run_min = 1000;
+  sp.ring_stores = true;  // the thread's CSR region leads the outputs: store it on 128-byte line boundaries (jit.cpp ring_flush)
   sp.fin = &fp.fin;
   sp.fout = &fp.pieces.at((size_t) piece).fout;
   jit_env_knobs(sp);
   // knobs of the fused kernels alone (sweeps)
+  if (const char* e = getenv("ASSET_B200_FUSED_RING")) sp.ring_stores = std::atoi(e) != 0;
   if (const char* e = getenv("ASSET_B200_FUSED_ZRUN")) sp.zero_run_min = std::max(1, std::atoi(e));
   if (const char* e = getenv("ASSET_B200_FUSED_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
   if (const char* e = getenv("ASSET_B200_FUSED_THREADS")) sp.nthreads = std::max(32, std::atoi(e) / 32 * 32);

@@ -45,6 +45,7 @@ struct JitSpec {
   bool unroll_flush = false;    // 32 unrolled load/store pairs per output chunk instead of a loop: measured SLOWER (more straight-line code, r1j)
   bool flush_unroll4 = true;    // output walk in trips of four segments with rotating data / address registers
   bool skip_zero_outputs = true;  // structural zeros of the dense blocks are written once (plan build), not per eval
+  bool ring_stores = false;        // a leading contiguous run of outputs is stored on 128-byte line boundaries (fused kernels)
   int zero_run_min = 1;           // minimum length of a zero run enclosed by stored values to be skipped (sweep r1r: 1 is fastest)
   int debug = 0;                // measurement only (wrong results): 1 no global stores, 2 no output walk at all
   bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)

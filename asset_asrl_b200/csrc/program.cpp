@@ -246,7 +246,11 @@ Program emit_program_outs(ScalarFn& f, const std::vector<ProgOut>& outs) {
         const int p = prod.at(on[q]);
         if (!done[p] || bundle_of[p] == nbund) ready = false;
       }
-      if (!ready) continue;
+      if (!ready) {
+        // outputs leave in the order they were asked for (the specialiser stores runs of consecutive outputs)
+        if (kind == PK_OUT) break;
+        continue;
+      }
       cur.push_back(k);
     }
     if (cur.empty()) throw std::logic_error("emit_program: scheduler stalled");

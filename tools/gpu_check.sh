@@ -10,7 +10,7 @@ timeout 600 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?"
 tail -c 3000 $O/bench.json
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file $O/launches.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu --no-e2e > $O/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:$KRE -c 8 -o $O/top_kernel -f \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:$KRE -c 16 -o $O/top_kernel -f \
     python bench.py --steps 2 --warmup 1 --no-cpu --no-e2e > $O/ncu_full.log 2>&1; echo "ncu full rc=$?"
-tail -3 $O/pytest.log $O/smoke.log
+tail -q -n 3 $O/pytest.log $O/smoke.log
 timeout 600 python bench.py --impl reference > $O/bench_reference.json 2> $O/bench_reference.err; echo "reference arm rc=$?"; cat $O/bench_reference.json

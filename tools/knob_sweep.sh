@@ -14,13 +14,11 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run p4_default       ASSET_B200_JIT_VERBOSE=1
-run p5               ASSET_B200_FUSED_PIECES=5
-run p6               ASSET_B200_FUSED_PIECES=6
-run p8               ASSET_B200_FUSED_PIECES=8
-run p4_regs96        ASSET_B200_FUSED_REGS=96
-run p4_regs128       ASSET_B200_FUSED_REGS=128
-run p4_t64           ASSET_B200_FUSED_THREADS=64
-run p4_serial        ASSET_B200_NO_PIECE_OVERLAP=1
-grep -h "ab_fused" $O/p4_default.err | cut -c1-260
+run ring0            ASSET_B200_FUSED_RING=0
+run ring1            ASSET_B200_JIT_VERBOSE=1
+run ring1_p3         ASSET_B200_FUSED_PIECES=3
+run ring1_p2         ASSET_B200_FUSED_PIECES=2
+run ring1_p5         ASSET_B200_FUSED_PIECES=5
+run ring1_t64        ASSET_B200_FUSED_THREADS=64
+grep -h "ab_fused" $O/ring1.err | cut -c1-260
 timeout 900 python -m pytest tests/test_gpu_fused.py tests/test_gpu_multi.py -m gpu -x -q 2>&1 | tail -3

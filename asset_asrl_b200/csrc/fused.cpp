@@ -540,7 +540,7 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   // smaller block's third resident warp per SM helps.
   sp.nthreads = 32;
   sp.zero_run_min = 1000;
-  sp.ring_stores = true;  // the thread's CSR region leads the outputs: store it on 128-byte line boundaries (jit.cpp ring_flush)
+  sp.ring_stores = false;  // line-aligned stores of the CSR run (jit.cpp ring_flush): measured no gain (sweeps r2k, r2l), off
   sp.fin = &fp.fin;
   sp.fout = &fp.pieces.at((size_t) piece).fout;
   jit_env_knobs(sp);

@@ -16,9 +16,7 @@ PY
 }
 run ring0            ASSET_B200_FUSED_RING=0
 run ring1            ASSET_B200_JIT_VERBOSE=1
+run ring1_noalign    ASSET_B200_JIT_RING_NOALIGN=1
 run ring1_p3         ASSET_B200_FUSED_PIECES=3
-run ring1_p2         ASSET_B200_FUSED_PIECES=2
-run ring1_p5         ASSET_B200_FUSED_PIECES=5
-run ring1_t64        ASSET_B200_FUSED_THREADS=64
 grep -h "ab_fused" $O/ring1.err | cut -c1-260
 timeout 900 python -m pytest tests/test_gpu_fused.py tests/test_gpu_multi.py -m gpu -x -q 2>&1 | tail -3

@@ -202,7 +202,7 @@ int main(int argc, char** argv) {
     snprintf(name, sizeof(name), "F<32>  one-warp blocks, %2d warps/SM    ", warps);
     timeit(name, [&] { kF<32><<<nseg / 32, 32, dyn>>>(out, nseg, dps); });
     snprintf(name, sizeof(name), "F<64>  one-warp blocks, %2d warps/SM    ", warps);
-    timeit(name, [&] { kF<64><<<nseg / 32, 32, dyn>>>(out, nseg, dps); });
+    if (dyn >= 32 * 65 * 8) timeit(name, [&] { kF<64><<<nseg / 32, 32, dyn>>>(out, nseg, dps); });
     if (dyn >= 32 * 129 * 8) {
       snprintf(name, sizeof(name), "F<128> one-warp blocks, %2d warps/SM    ", warps);
       timeit(name, [&] { kF<128><<<nseg / 32, 32, dyn>>>(out, nseg, dps); });

@@ -513,9 +513,10 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
     } else {
       // one piece per ~1300 FMAs of the whole program (sweep r2g, 32-thread blocks with zero runs written out: four
       // pieces for the 5090-FMA LGL5 low-thrust segment run the step in 0.81 ms, two in 0.88, one leaves a single
-      // block per SM)
+      // block per SM); at most six (LGL7 low-thrust, 100 k segments: 1.17 ms with six, 1.20 with eight, 1.22 with four;
+      // the small programs -- LGL3, trapezoidal, VanDerPol, HyperSens -- are fastest as one piece; sweep r2q)
       build_pieces(even(1));
-      const int np = std::min<long long>(std::min<long long>(8, s), std::max(1, (FP.pieces[0].prog.n_fma + 650) / 1300));
+      const int np = std::min<long long>(std::min<long long>(6, s), std::max(1, (FP.pieces[0].prog.n_fma + 650) / 1300));
       if (np > 1) {
         if (getenv("ASSET_B200_FUSED_BALANCE")) balance(np);
         else build_pieces(even(np));

@@ -1,0 +1,78 @@
+"""Host side of the fused owner-writes evalKKT path (asset_asrl_b200/csrc/fused.cpp): template discovery on the analysed
+problem, the cut into row-block pieces and the PTX the specialiser emits for them.  No GPU: the PTX is assembled for
+sm_100a in-process.  Values are checked on the device in tests/test_gpu_fused.py.
+
+The reference has no counterpart of this structure -- it loops over applications and adds into the shared value array
+under a mutex (ConstraintFunction.h:80-109, NonLinearProgram.cpp:486-519); what has to agree is the result.
+"""
+import re
+
+import pytest
+
+from asset_asrl_b200 import workloads as W
+from asset_asrl_b200.Solvers import NonLinearProgram
+
+
+CASES = [
+    # ode, transcription, segments, pieces the automatic rule picks
+    ("lowthrust", "LGL5", 96, 4),
+    ("lowthrust", "LGL3", 96, 1),
+    ("lowthrust", "Trapezoidal", 96, 1),
+    ("vanderpol", "LGL5", 96, 1),
+    ("hypersens", "LGL5", 96, 1),
+]
+
+
+@pytest.mark.parametrize("ode,mode,nseg,pieces", CASES)
+def test_template_and_pieces(ode, mode, nseg, pieces):
+    nlp = W.make_phase(ode, mode, nseg).transcribe()
+    fi = nlp.fused_info()
+    assert fi["ok"] == 1, fi["why"]
+    # the periodic interior excludes a few segments at either end of the mesh and nothing else
+    assert 0 < fi["t_lo"] <= 8 and nseg - 8 <= fi["t_hi"] < nseg
+    assert fi["pieces"] == pieces
+    # every CSR slot of the owned rows has a source, so a thread's outputs are at least its region
+    assert fi["outputs"] >= fi["slots_per_segment"] > 0
+
+
+def test_lgl7_is_cut_into_at_most_six_pieces():
+    nlp = W.make_phase("lowthrust", "LGL7", 64).transcribe()
+    fi = nlp.fused_info()
+    assert fi["ok"] == 1, fi["why"]
+    assert fi["pieces"] == 6
+
+
+def _stores(ptx):
+    return len(re.findall(r"^st\.shared\.f64 \[%rso\+", ptx, flags=re.M))
+
+
+@pytest.mark.parametrize("ode,mode", [("lowthrust", "LGL5"), ("vanderpol", "LGL3")])
+def test_piece_ptx_assembles(ode, mode, monkeypatch):
+    nlp = W.make_phase(ode, mode, 96).transcribe()
+    fi = nlp.fused_info()
+    total = 0
+    for pc in range(fi["pieces"]):
+        ptx = nlp.fused_ptx(pc)
+        assert ".visible .entry ab_fused_kkt%d(" % pc in ptx
+        info = NonLinearProgram.assemble_ptx(ptx)
+        assert info["cubin_bytes"] > 0 and info["registers"] <= 255
+        total += _stores(ptx)
+    # the pieces together store every output of the thread once; only structural zeros outside the owned region (their
+    # destinations are zero-filled when the plan is built) may be left out
+    assert fi["slots_per_segment"] <= total <= fi["outputs"]
+    assert fi["outputs"] - total <= 8
+
+
+def test_ring_walk_variant_assembles_and_stores_the_same_outputs(monkeypatch):
+    nlp = W.make_phase("lowthrust", "LGL5", 96).transcribe()
+    fi = nlp.fused_info()
+    plain = [nlp.fused_ptx(pc) for pc in range(fi["pieces"])]
+    monkeypatch.setenv("ASSET_B200_FUSED_RING", "1")
+    ring = [nlp.fused_ptx(pc) for pc in range(fi["pieces"])]
+    for pc, (a, b) in enumerate(zip(plain, ring)):
+        assert "L_rg0:" in b and "L_rg0:" not in a
+        assert _stores(a) == _stores(b)
+        # one walk per 32 outputs of the leading run plus the walk that stores what the last chunk left behind
+        walks = len(re.findall(r"^L_rg\d+:", b, flags=re.M))
+        assert 2 <= walks <= _stores(b) // 32 + 1
+        assert NonLinearProgram.assemble_ptx(b)["cubin_bytes"] > 0

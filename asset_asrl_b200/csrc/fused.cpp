@@ -549,6 +549,15 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   if (const char* e = getenv("ASSET_B200_FUSED_RING")) sp.ring_stores = std::atoi(e) != 0;
   if (const char* e = getenv("ASSET_B200_FUSED_ZRUN")) sp.zero_run_min = std::max(1, std::atoi(e));
   if (const char* e = getenv("ASSET_B200_FUSED_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
+  if (const char* e = getenv("ASSET_B200_FUSED_REGS_BY_PIECE")) {  // comma-separated register budgets, one per piece
+    std::string list(e);
+    size_t pos = 0;
+    for (int k = 0; pos <= list.size(); k++) {
+      const size_t end = std::min(list.find(',', pos), list.size());
+      if (k == piece && end > pos) sp.reg_budget = std::max(16, std::atoi(list.substr(pos, end - pos).c_str()));
+      pos = end + 1;
+    }
+  }
   if (const char* e = getenv("ASSET_B200_FUSED_THREADS")) sp.nthreads = std::max(32, std::atoi(e) / 32 * 32);
   AffineMaps am;
   am.a0 = 0;

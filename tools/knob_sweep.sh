@@ -14,9 +14,11 @@ except Exception as e:
     print(sys.argv[1], "FAILED", e)
 PY
 }
-run ring0            ASSET_B200_FUSED_RING=0
-run ring1            ASSET_B200_JIT_VERBOSE=1
-run ring1_noalign    ASSET_B200_JIT_RING_NOALIGN=1
-run ring1_p3         ASSET_B200_FUSED_PIECES=3
-grep -h "ab_fused" $O/ring1.err | cut -c1-260
-timeout 900 python -m pytest tests/test_gpu_fused.py tests/test_gpu_multi.py -m gpu -x -q 2>&1 | tail -3
+run base             ASSET_B200_JIT_VERBOSE=1
+run light96          ASSET_B200_FUSED_REGS_BY_PIECE=112,112,96,96
+run light80          ASSET_B200_FUSED_REGS_BY_PIECE=112,112,80,80 ASSET_B200_JIT_VERBOSE=1
+run light64          ASSET_B200_FUSED_REGS_BY_PIECE=112,112,64,64 ASSET_B200_JIT_VERBOSE=1
+run light48          ASSET_B200_FUSED_REGS_BY_PIECE=112,112,48,48 ASSET_B200_JIT_VERBOSE=1
+run heavy120         ASSET_B200_FUSED_REGS_BY_PIECE=120,120,112,112
+run heavy104         ASSET_B200_FUSED_REGS_BY_PIECE=104,104,112,112
+grep -h "ab_fused" $O/light80.err $O/light64.err $O/light48.err | cut -c1-260

@@ -261,6 +261,8 @@ struct DagCopy {
 
 FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
   FusedPlan FP;
+  if (npieces == 0)
+    if (const char* e = getenv("ASSET_B200_FUSED_PIECES")) npieces = std::max(0, std::atoi(e));
   if (!prob.analyzed) {
     FP.why = "problem not analysed";
     return FP;
@@ -541,12 +543,14 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   // smaller block's third resident warp per SM helps.
   sp.nthreads = 32;
   sp.zero_run_min = 1000;
-  sp.ring_stores = false;  // line-aligned stores of the CSR run (jit.cpp ring_flush): measured no gain (sweeps r2k, r2l), off
+  // outputs leave straight from registers as whole 32-byte sectors (jit.hpp: direct_stores); ASSET_B200_FUSED_DIRECT=0
+  // brings back the shared-memory transposition walk for comparison
+  sp.direct_stores = true;
+  if (const char* e = getenv("ASSET_B200_FUSED_DIRECT")) sp.direct_stores = std::atoi(e) != 0;
   sp.fin = &fp.fin;
   sp.fout = &fp.pieces.at((size_t) piece).fout;
   jit_env_knobs(sp);
   // knobs of the fused kernels alone (sweeps)
-  if (const char* e = getenv("ASSET_B200_FUSED_RING")) sp.ring_stores = std::atoi(e) != 0;
   if (const char* e = getenv("ASSET_B200_FUSED_ZRUN")) sp.zero_run_min = std::max(1, std::atoi(e));
   if (const char* e = getenv("ASSET_B200_FUSED_REGS")) sp.reg_budget = std::max(16, std::atoi(e));
   if (const char* e = getenv("ASSET_B200_FUSED_REGS_BY_PIECE")) {  // comma-separated register budgets, one per piece

@@ -42,11 +42,20 @@ struct JitSpec {
   const std::vector<JitOut>* fout = nullptr;
   bool lockstep = false;        // bar.sync at every output flush: the warps of a block share instruction-cache fills
   bool prefetch_table = true;   // output-table entries of the next flush are loaded one flush ahead
-  bool unroll_flush = false;    // 32 unrolled load/store pairs per output chunk instead of a loop: measured SLOWER (more straight-line code, r1j)
   bool flush_unroll4 = true;    // output walk in trips of four segments with rotating data / address registers
   bool skip_zero_outputs = true;  // structural zeros of the dense blocks are written once (plan build), not per eval
-  bool ring_stores = false;        // a leading contiguous run of outputs is stored on 128-byte line boundaries (fused kernels)
   int zero_run_min = 1;           // minimum length of a zero run enclosed by stored values to be skipped (sweep r1r: 1 is fastest)
+  // Outputs leave straight from registers: runs of consecutive outputs are written with 32-byte vector stores on
+  // 32-byte boundaries (a whole sector per lane; 16- and 8-byte stores only at the ends of a run), no shared-memory
+  // transposition.  Measured (tools/direct_store_bench.cu, profiles/r2_sweeps/direct_store_r3a.txt): 6.2 TB/s at four
+  // resident warps per SM against 1.2 TB/s for the tile walk at the same residency.  Which outputs share a sector depends
+  // on where a thread's run starts; the start's phase is a function of (rel mod 4) known when the kernel is generated,
+  // so every phase gets its own predicated store of the same registers.
+  bool direct_stores = false;
+  // Parked values are written and read back with volatile shared-memory accesses.  ptxas 12.9 was caught sinking a
+  // plain st.shared of a recycled slot below the later ld.shared of the same address in a 6000-instruction block
+  // (LGL7 fused piece; the reload then returns the slot's previous value): volatile accesses keep program order.
+  bool volatile_parks = true;
   int debug = 0;                // measurement only (wrong results): 1 no global stores, 2 no output walk at all
   bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)
 };

@@ -378,9 +378,7 @@ int Plan::build(int dev, int rank_, int world_) {
   }
   if (const char* e = getenv("ASSET_B200_FUSED")) use_fused = std::atoi(e) != 0;
   if (use_fused && use_jit && (world == 1 || !getenv("ASSET_B200_NO_PRUNE"))) {
-    int npieces = 0;
-    if (const char* e = getenv("ASSET_B200_FUSED_PIECES")) npieces = std::max(0, std::atoi(e));
-    fused = build_fused(prob, jit_min_apps, npieces);
+    fused = build_fused(prob, jit_min_apps);
     if (fused.ok) {
       const long long R = fused.t_hi - fused.t_lo;
       // staging slots the fused kernels write (objective value per segment, entries of rows no segment owns)
@@ -975,9 +973,10 @@ int Plan::eval(int mode, double obj_scale) {
     fa.stage = d_stage;
     fa.appconst = d_appc_all;
     fa.vindex = (const int*) d_LI;  // multipliers of the inequalities (see JitSpec::fin)
-    fa.cindex = nullptr;
-    fa.kkt_dest = nullptr;
-    fa.f_dest = nullptr;
+    // direct stores address the small output arrays through the map slots (jit.cpp: out_param)
+    fa.cindex = (const int*) d_fxi;
+    fa.kkt_dest = (const int*) d_pgx;
+    fa.f_dest = (const int*) d_agx;
     fa.obj_scale = obj_scale;
     const long long R = fused.t_hi - fused.t_lo, EDGE = getenv("ASSET_B200_NO_EDGE_SPLIT") ? 0 : 64;
     f_b = R * rank / world;

@@ -56,6 +56,8 @@ struct JitSpec {
   // plain st.shared of a recycled slot below the later ld.shared of the same address in a 6000-instruction block
   // (LGL7 fused piece; the reload then returns the slot's previous value): volatile accesses keep program order.
   bool volatile_parks = true;
+  bool vector_loads = true;        // hoisted loads of consecutive inputs as ld.global.nc.v4 / .v2 where the alignment is thread-independent
+  bool streaming_stores = false;   // direct stores carry the .cs (evict-first) cache operator
   int debug = 0;                // measurement only (wrong results): 1 no global stores, 2 no output walk at all
   bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)
 };

@@ -1,0 +1,60 @@
+"""The specialiser's PTX executed on the CPU (tests/ptx_emu.py): the fused owner-writes kernels of several phases, a few
+threads each, against the CPU oracle -- no GPU and no assembler involved, so an emitter bug (wrong register, wrong store
+phase, a value parked before it is defined) shows up here, and an assembler bug does not.  The assembler's handling
+of the parked-value accesses is checked separately on the SASS (tools/sass_park_order.py)."""
+import os
+import shutil
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tools"))
+import oracle  # noqa: E402
+from emu_harness import emulate_fused  # noqa: E402
+from helpers import problem_inputs  # noqa: E402
+
+from asset_asrl_b200 import workloads as W  # noqa: E402
+
+CASES = {
+    "lowthrust_LGL5": lambda: W.make_phase("lowthrust", "LGL5", 60),
+    "lowthrust_LGL7": lambda: W.make_phase("lowthrust", "LGL7", 50),
+    "lowthrust_LGL7_highest_order_spline": lambda: W.make_phase("lowthrust", "LGL7", 50, control_mode="HighestOrderSpline"),
+    "lowthrust_LGL3": lambda: W.make_phase("lowthrust", "LGL3", 60),
+    "lowthrust_Trapezoidal": lambda: W.make_phase("lowthrust", "Trapezoidal", 60),
+    "vanderpol_LGL5": lambda: W.make_phase("vanderpol", "LGL5", 60),
+    "hypersens_LGL5": lambda: W.make_phase("hypersens", "LGL5", 60),
+    "brachistochrone_LGL3": lambda: W.make_phase("brachistochrone", "LGL3", 60),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_fused_ptx_on_the_emulator_matches_the_oracle(name):
+    ph = CASES[name]()
+    nlp = ph.transcribe()
+    X = ph.makeSolverInput()
+    LE, LI, sc = problem_inputs(nlp)
+    info = nlp.fused_info()
+    assert info["ok"], info["why"]
+    ref = oracle.Oracle.from_problem(nlp).eval("KKT", 0.7, X, LE, LI, sc)
+    R = info["t_hi"] - info["t_lo"]
+    res = emulate_fused(nlp, X, LE, LI, sc, 0.7, [0, 1, 2, 3, R // 2, R - 1])  # every store phase (rel mod 4) and both ends
+    wrote = 0
+    for k, (v, m) in res.items():
+        if not m.any():
+            continue
+        wrote += int(m.sum())
+        scale = max(float(np.abs(ref[k]).max()), 1e-300)
+        assert float(np.abs(v[m] - ref[k][m]).max()) <= 1e-12 * scale, (name, k)
+    assert wrote >= 6 * info["slots_per_segment"]
+
+
+@pytest.mark.skipif(shutil.which("ptxas") is None or shutil.which("cuobjdump") is None, reason="needs the CUDA toolkit's ptxas and cuobjdump")
+@pytest.mark.parametrize("name", ["lowthrust_LGL5", "lowthrust_LGL7_highest_order_spline"])
+def test_assembler_keeps_the_order_of_parked_value_accesses(name):
+    import sass_park_order
+    nlp = CASES[name]().transcribe()
+    info = nlp.fused_info()
+    for p in range(int(info["pieces"])):
+        assert sass_park_order.check(nlp.fused_ptx(p)) == [], (name, p)

@@ -43,7 +43,13 @@ def test_lgl7_is_cut_into_at_most_six_pieces():
 
 
 def _stores(ptx):
-    return len(re.findall(r"^st\.shared\.f64 \[%rso\+", ptx, flags=re.M))
+    """Outputs a thread stores: tile-walk kernels park each in the transposition tile; direct-store kernels write runs
+    with one predicated store sequence per alignment phase of the thread -- count the elements of phase 0."""
+    n = len(re.findall(r"^st\.shared\.f64 \[%rso\+", ptx, flags=re.M))
+    for pred, vec in re.findall(r"^(@%pm\d_\d )?st\.global(?:\.cs)?(\.v[24])?\.f64 \[%rg", ptx, flags=re.M):
+        if pred == "" or pred.endswith("_0 "):
+            n += int(vec[2]) if vec else 1
+    return n
 
 
 @pytest.mark.parametrize("ode,mode", [("lowthrust", "LGL5"), ("vanderpol", "LGL3")])
@@ -63,16 +69,18 @@ def test_piece_ptx_assembles(ode, mode, monkeypatch):
     assert fi["outputs"] - total <= 8
 
 
-def test_ring_walk_variant_assembles_and_stores_the_same_outputs(monkeypatch):
+def test_direct_and_tile_walk_variants_store_the_same_outputs(monkeypatch):
     nlp = W.make_phase("lowthrust", "LGL5", 96).transcribe()
     fi = nlp.fused_info()
-    plain = [nlp.fused_ptx(pc) for pc in range(fi["pieces"])]
-    monkeypatch.setenv("ASSET_B200_FUSED_RING", "1")
-    ring = [nlp.fused_ptx(pc) for pc in range(fi["pieces"])]
-    for pc, (a, b) in enumerate(zip(plain, ring)):
-        assert "L_rg0:" in b and "L_rg0:" not in a
+    direct = [nlp.fused_ptx(pc) for pc in range(fi["pieces"])]
+    monkeypatch.setenv("ASSET_B200_FUSED_DIRECT", "0")
+    walk = [nlp.fused_ptx(pc) for pc in range(fi["pieces"])]
+    for a, b in zip(direct, walk):
+        assert "st.global.v4.f64" in a and "st.global.v4.f64" not in b
         assert _stores(a) == _stores(b)
-        # one walk per 32 outputs of the leading run plus the walk that stores what the last chunk left behind
-        walks = len(re.findall(r"^L_rg\d+:", b, flags=re.M))
-        assert 2 <= walks <= _stores(b) // 32 + 1
-        assert NonLinearProgram.assemble_ptx(b)["cubin_bytes"] > 0
+        # every alignment phase of a run stores the same number of elements
+        for r in ("2", "4"):
+            per = [sum(int(v[2]) if v else 1 for v in re.findall(r"^@%%pm%s_%d st\.global(\.v[24])?\.f64 " % (r, k), a, flags=re.M))
+                   for k in range(int(r))]
+            assert len(set(per)) == 1, per
+

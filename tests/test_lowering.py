@@ -84,15 +84,71 @@ def test_tape_matches_golden_defects():
 
 
 def test_linearity_rules():
-    """Type-level linearity decides whether Hessian triplets exist (note L)."""
-    from helpers import vf
-    a = vf.Arguments(2)
-    assert (a[1] - a[0]).is_linear()                 # FunctionDifference<Segment,Segment>
-    assert not ((a[1] - a[0]) * 2.0).is_linear()     # Scaled<GenericFunction>: GenericFunction hides linearity
-    assert (a * 2.0).is_linear()                     # Scaled<Arguments>
-    assert not vf.sin(a).is_linear()
-    assert vf.stack([a[0], a[1]]).is_linear()
-
+    """Type-level linearity decides whether Hessian triplets exist (note L): one assert per row of
+    the rule table.  A function built by a Python operator is a GenericFunction (static IsLinearFunction false,
+    ComputableBase.h:90); the solver unwraps ONE level (SolverInterfaceSpecs.h:386-388), so an operator applied to
+    Arguments / Segments (concrete linear types) is linear, the same operator applied to an operator result is not."""
+    from helpers import vf, oc
+    a = vf.Arguments(3)
+    lin_of_args = {
+        "Arguments (Segment.h:102)": a,
+        "Segment": a.head(2),
+        "Elements (Elements.h:21)": a[[0, 2]],
+        "coeff": a[1],
+        "FunctionDifference<Segment,Segment> (Summation.h:132)": a[1] - a[0],
+        "TwoFunctionSum": a[1] + a[0],
+        "MultiFunctionSum (Summation.h:349)": vf.sum(a[0], a[1], a[2]),
+        "Scaled<Arguments> (Scaled.h:81)": a * 2.0,
+        "Scaled by division": a / 4.0,
+        "negation": -a,
+        "RowScaled (Scaled.h:320)": a * np.array([1.0, 2.0, 3.0]),
+        "FunctionPlusVector (FunctionVectorSums.h:30)": a + np.array([1.0, 2.0, 3.0]),
+        "VectorMinusFunction": np.array([1.0, 2.0, 3.0]) - a,
+        "function minus vector": a - np.array([1.0, 2.0, 3.0]),
+        "StackedOutputs of segments (Stacked.h:85)": vf.stack([a[0], a[1]]),
+        "CwiseSum (CwiseSum.h:28)": a.sum(),
+        "MatrixScaled (Scaled.h:483)": vf.matmul(np.arange(6.0).reshape(2, 3), a),
+        "IOScaled<Arguments> (IOScaled.h:14)": vf.ioscaled(a, [1.0, 2.0, 3.0], [2.0, 2.0, 2.0]),
+        "Constant (Constant.h:13)": vf.ConstantVector(3, [1.0, 2.0]),
+    }
+    for name, f in lin_of_args.items():
+        assert f.is_linear(), name
+    g = a[1] - a[0]           # a GenericFunction holding a linear type
+    h = a.head(2) * 3.0       # likewise
+    hidden = {
+        "Scaled<GenericFunction>": g * 2.0,
+        "FunctionPlusVector<GenericFunction>": h + np.array([1.0, 2.0]),
+        "VectorMinusFunction<GenericFunction>": np.array([1.0, 2.0]) - h,
+        "TwoFunctionSum<Generic,Generic>": g + g,
+        "FunctionDifference<Generic,Segment>": g - a[2],
+        "StackedOutputs<Generic,Segment> (all parts must be linear types)": vf.stack([g, a[2]]),
+        "Segment of a GenericFunction": h[0],
+        "CwiseSum<GenericFunction>": h.sum(),
+        "RowScaled<GenericFunction>": h * np.array([1.0, 2.0]),
+        "MatrixScaled<GenericFunction>": vf.matmul(np.eye(2), h),
+        "IOScaled<GenericFunction>": vf.ioscaled(h, [1.0, 1.0, 1.0], [2.0, 2.0]),
+        "NestedFunction<Generic,Generic> (outer && inner, NestedFunction.h:38)": h.eval(a * 2.0),
+    }
+    for name, f in hidden.items():
+        assert not f.is_linear(), name
+    nonlinear = {
+        "sin": vf.sin(a), "cos": vf.cos(a), "exp": vf.exp(a[0]), "squared": a[0].squared(), "sqrt": vf.sqrt(a[0]),
+        "inverse": a[0].inverse(), "pow": a[0] ** 3, "abs": abs(a[0]), "sign": a[0].sign(),
+        "norm": a.norm(), "squared_norm": a.squared_norm(), "inverse_norm": a.inverse_norm(), "normalized": a.normalized(),
+        "dot": a.dot(a), "cross": a.cross(a), "cwiseProduct": a.cwiseProduct(a), "cwiseQuotient": a.cwiseQuotient(a),
+        "scalar product of functions": a[0] * a[1], "function quotient": a[0] / a[1], "vector times scalar function": a * a[0],
+        "arctan2": vf.arctan2(a[0], a[1]), "ifelse": vf.ifelse(a[0] < 0.0, a[1], a[2]),
+    }
+    for name, f in nonlinear.items():
+        assert not f.is_linear(), name
+    # helpers the reference builds in C++ keep their concrete type: addLUVarBound is
+    # StackedOutputs<Scaled<FunctionPlusVector<Scaled<Arguments<1>>>>, Scaled<FunctionPlusVector<Arguments<1>>>>
+    # (ODEPhaseBase.cpp:110-130), linear; the norm bound composes it with a norm (:226-260), non-linear
+    assert oc._lu_bound(-1.0, 1.0, 2.0, 2.0).is_linear()
+    ph = __import__("asset_asrl_b200").workloads.make_phase("lowthrust", "LGL3", 4)
+    nlp = ph.transcribe()
+    lin = {nlp.function_info(f)["linear"] for f in range(nlp.dims()["nfuncs"])}
+    assert lin == {0, 1}
 
 def test_link_index_maps_follow_the_reference_layout():
     """make_link_Vindex_Cindex (OptimalControlProblem.cpp:659-764) on a hand-computed case: phase variables are

@@ -261,6 +261,24 @@ class NonLinearProgram:
             dist.all_reduce(cut, op=dist.ReduceOp.SUM, group=self.group)
         _lib.check0(lib.ab_plan_cut_unpack(self.plan))
 
+    def device_tensor(self, name):
+        """Output / input array `name` (X, LE, LI, KKT, FXE, FXI, PGX, AGX, val) as a torch tensor aliasing the plan's
+        device memory (ab_plan_device_ptr; no copy) -- what a device-resident consumer of the values would read."""
+        import torch
+        self._need_plan()
+        d = self.dims()
+        which = {"X": (0, d["nvars"]), "LE": (1, d["neq"]), "LI": (2, d["niq"]), "KKT": (3, d["nnz"]), "FXE": (4, d["neq"]),
+                 "FXI": (5, d["niq"]), "PGX": (6, d["nvars"]), "AGX": (7, d["nvars"]), "val": (8, 1)}[name]
+        if which[1] == 0:
+            return torch.zeros(0, dtype=torch.float64, device=torch.device("cuda", self.device))
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (int(which[1]),), "typestr": "<f8", "version": 3, "strides": None,
+                                        "data": (int(lib.ab_plan_device_ptr(self.plan, which[0])), False)}
+        return torch.as_tensor(raw, device=torch.device("cuda", self.device))
+
     def cut_tensor(self):
         """The packed cut buffer as a torch tensor aliasing the plan's device memory (no copy)."""
         import torch

@@ -532,7 +532,7 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
   return FP;
 }
 
-std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats) {
+std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats, int reg_budget) {
   JitSpec sp;
   sp.name = "ab_fused_kkt" + std::to_string(piece);
   sp.role = 1;  // multipliers and the objective scale are table entries, not the role's implicit operand
@@ -563,6 +563,8 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
     }
   }
   if (const char* e = getenv("ASSET_B200_FUSED_THREADS")) sp.nthreads = std::max(32, std::atoi(e) / 32 * 32);
+  if (reg_budget > 0) sp.reg_budget = reg_budget;
+  if (stats) stats->reg_budget = sp.reg_budget;
   AffineMaps am;
   am.a0 = 0;
   am.a1 = fp.t_hi - fp.t_lo;

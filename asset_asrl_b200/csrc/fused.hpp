@@ -59,6 +59,7 @@ struct FusedPlan {
 FusedPlan build_fused(const Problem& prob, int min_threads, int npieces = 0 /* 0: by program size */);
 
 // PTX of one piece of the fused evaluation (entry "ab_fused_kkt<piece>"); fills the output table entries (emission order) and the statistics.
-std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats);
+// reg_budget > 0 overrides the default number of values kept in registers (the plan lowers it when the assembler spills)
+std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats, int reg_budget = 0);
 
 }  // namespace ab

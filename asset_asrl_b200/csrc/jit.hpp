@@ -58,6 +58,11 @@ struct JitSpec {
   bool volatile_parks = true;
   bool vector_loads = true;        // hoisted loads of consecutive inputs as ld.global.nc.v4 / .v2 where the alignment is thread-independent
   bool streaming_stores = false;   // direct stores carry the .cs (evict-first) cache operator
+  // Direct stores only: finished outputs wait in a queue and leave spread evenly over the program's arithmetic instead
+  // of in the bursts they are finished in (jit.cpp: drain_outputs); at most pace_burst outputs per arithmetic bundle.
+  bool phase_bases = true;         // one base register per (address group, alignment phase) for the 32-byte stores (jit.cpp: addr_sector)
+  bool pace_outputs = false;
+  int pace_burst = 2;
   int debug = 0;                // measurement only (wrong results): 1 no global stores, 2 no output walk at all
   bool hoist_loads = true;      // every input load is issued at the top of the kernel (one DRAM round trip, not 30)
 };
@@ -66,6 +71,7 @@ struct JitStats {
   unsigned smem_bytes = 0;  // dynamic shared memory per block (transposition tile + parked values)
   int parked_slots = 0;     // lane-private shared-memory slots
   int parks = 0, reloads = 0;
+  int reg_budget = 0;       // values kept in registers (as used)
 };
 
 // Kernel parameters, in order (see launch_jit).  begin/end: application range, relative to the first affine

@@ -383,7 +383,7 @@ int Plan::build(int dev, int rank_, int world_) {
       const long long R = fused.t_hi - fused.t_lo;
       // staging slots the fused kernels write (objective value per segment, entries of rows no segment owns)
       std::vector<unsigned char> fslot;
-      if (world > 1) {
+      {
         fslot.assign((size_t) std::max<long long>(prob.stage_size, 1), 0);
         for (const auto& pc: fused.pieces)
           for (const JitOut& w: pc.fout)
@@ -399,13 +399,16 @@ int Plan::build(int dev, int rank_, int world_) {
       for (int a = 0; a < OA_COUNT; a++) base[a] = world > 1 ? pruned_full[a] : gsrc[a];
       const long long own_lo[OA_COUNT] = {fused.kb, fused.vb, fused.vb, 0, 0, 0};
       const long long own_hi[OA_COUNT] = {fused.kb + R * fused.ks, fused.vb + R * fused.vs, fused.vb + R * fused.vs, 0, 0, 0};
-      GatherList fl[OA_COUNT][2];
+      // fl: targets that must wait for the fused kernels (fed by their staged outputs) and every high fan-in target;
+      // flE ("early"): low fan-in targets fed by the mesh ends and the solver coefficients alone -- most of what is
+      // left, the pivot and slack rows -- which are summed on the side stream beside the bulk kernels
+      GatherList fl[OA_COUNT][2], flE[OA_COUNT][2];
       std::vector<int> cut_t[OA_COUNT];
       for (int a = 0; a < OA_COUNT; a++) {
         for (int w = 0; w < 2; w++) {
           const GatherList& g = base[a][w];
-          GatherList& o = fl[a][w];
-          o.ptr.assign(1, 0);
+          fl[a][w].ptr.assign(1, 0);
+          flE[a][w].ptr.assign(1, 0);
           // solver-only targets of this list (outside the fused rows), for an even spread over the ranks
           long long total_solver_only = 0, n_solver_only = 0;
           if (world > 1)
@@ -421,8 +424,9 @@ int Plan::build(int dev, int rank_, int world_) {
           for (int t = 0; t < g.ntargets(); t++) {
             if (g.target[t] >= own_lo[a] && g.target[t] < own_hi[a]) continue;
             bool fed = false;
-            if (world > 1)
-              for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) fed = fed || fslot[(size_t) g.src[(size_t) k]] != 0;
+            for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) fed = fed || fslot[(size_t) g.src[(size_t) k]] != 0;
+            const bool early = !fed && w == 0 && (a == OA_KKT || a == OA_PGX || a == OA_AGX);
+            GatherList& o = early ? flE[a][w] : fl[a][w];
             // targets fed only by solver coefficients (pivot and slack rows: most of what is left) are spread over the
             // ranks by position; everything else that no fused kernel feeds belongs to rank 0, which runs the mesh ends
             bool solver_only = world > 1 && !fed && g.ptr[(size_t) t + 1] > g.ptr[t];
@@ -452,7 +456,8 @@ int Plan::build(int dev, int rank_, int world_) {
       std::vector<double> appc;
       for (const FuncRec& fr: prob.funcs) appc.insert(appc.end(), fr.appconst.begin(), fr.appconst.end());
       d_appc_all = dupload(appc);
-      bool ok = d_appc_all && up_gather(*this, fl[OA_KKT], gkF) && up_gather(*this, fl[OA_PGX], gpF) && up_gather(*this, fl[OA_AGX], gaF);
+      bool ok = d_appc_all && up_gather(*this, fl[OA_KKT], gkF) && up_gather(*this, fl[OA_PGX], gpF) && up_gather(*this, fl[OA_AGX], gaF)
+                && up_gather(*this, flE[OA_KKT], gkE) && up_gather(*this, flE[OA_PGX], gpE) && up_gather(*this, flE[OA_AGX], gaE);
       if (ok && world > 1) {
         ok = up_gather(*this, fl[OA_FXE], geF) && up_gather(*this, fl[OA_FXI], giF) && up_gather(*this, fl[OA_VAL], gvF);
         cutF_count = 0;
@@ -481,7 +486,10 @@ int Plan::build(int dev, int rank_, int world_) {
           }
         for (int a = 0; a < OA_COUNT; a++)
           for (int w = 0; w < 2; w++)
+          {
             for (int t: fl[a][w].target) touch(a, t);
+            for (int t: flE[a][w].target) touch(a, t);
+          }
         if (rank == 0) {
           std::vector<int> clr[OA_COUNT];
           for (const auto& pc: fused.pieces)
@@ -539,7 +547,7 @@ int Plan::build(int dev, int rank_, int world_) {
   }
   {
     size_t need = 1;
-    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF, &geF, &giF, &gvF})
+    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF, &geF, &giF, &gvF, &gkE, &gpE, &gaE})
       need = std::max(need, (size_t) g->dev[1].ntargets * (size_t) g->dev[1].maxparts);
     d_gscratch = dalloc<double>(need);
     if (!d_gscratch) {
@@ -590,6 +598,7 @@ namespace {
 struct CubinEntry {
   std::vector<char> cubin;
   int nregs = 0, spill = 0;
+  unsigned smem = 0;  // fused kernels: dynamic shared memory of the variant that was kept (0: as emitted)
 };
 std::mutex g_cubin_mu;
 std::unordered_map<std::string, CubinEntry> g_cubins;
@@ -641,11 +650,29 @@ int Plan::ensure_fused() {
         last_error = "fused kernel: " + log;
         return -(int) cudaErrorInvalidPtx;
       }
+      // The assembler's own spills go to local memory, whose reloads queue behind the output stream (ncu, capture s2: a
+      // reload of a spilled address pair waited ~2500 cycles): give it room by keeping fewer values in registers.
+      const std::string first = ptx;
+      int budget = js.reg_budget;
+      ce.smem = js.smem_bytes;
+      for (int tries = 0; ce.spill > 0 && tries < 5 && !getenv("ASSET_B200_FUSED_KEEP_SPILLS"); tries++) {
+        JitStats s2;
+        budget -= 3;
+        if (budget < 48) break;
+        const std::string p2 = fused_ptx(fused, (int) pc, nullptr, &s2, budget);
+        if ((int) s2.smem_bytes > dev_smem) break;
+        CubinEntry c2;
+        if (!assemble_ptx(p2, c2.cubin, log, &c2.nregs, &c2.spill)) break;
+        if (c2.spill < ce.spill) {
+          ce = c2;
+          ce.smem = s2.smem_bytes;
+        }
+      }
       std::lock_guard<std::mutex> lk(g_cubin_mu);
-      g_cubins.emplace(ptx, ce);
+      g_cubins.emplace(first, ce);
     }
     JitKernel& jk = fused_jits[pc];
-    jk.smem_bytes = js.smem_bytes;
+    jk.smem_bytes = ce.smem ? ce.smem : js.smem_bytes;
     cudaError_t e = load_jit(ce.cubin, "ab_fused_kkt" + std::to_string(pc), jk);
     if (e != cudaSuccess) {
       last_error = std::string("loading the fused kernel: ") + cudaGetErrorString(e);
@@ -684,7 +711,7 @@ int Plan::ensure_fused() {
       fprintf(stderr, "[asset_b200] ab_fused_kkt%zu of %zu: segments [%d, %d), %zu application families, %zu loads, %zu stored "
                       "outputs, %d FMA, %d regs, %d B assembler spill, %u B smem/block, %d parked slots, cubin %zu B\n",
               pc, fused.pieces.size(), fused.t_lo, fused.t_hi, fused.insts.size(), fused.fin.size(), outs.size(),
-              fused.pieces[pc].prog.n_fma, ce.nregs, ce.spill, js.smem_bytes, js.parked_slots, ce.cubin.size());
+              fused.pieces[pc].prog.n_fma, ce.nregs, ce.spill, jk.smem_bytes, js.parked_slots, ce.cubin.size());
   }
   fused_state = 1;
   return 1;
@@ -803,7 +830,30 @@ int Plan::eval(int mode, double obj_scale) {
   // independent: the bulk kernels run back to back on `stream`, the small ones (mesh ends, functions with a handful of
   // applications) overlap them on `side`.  With per-launch profiling on everything is serialised on `stream`.
   const bool overlap = !profiling;
-  bool forked = false;
+  bool forked = false, forked2 = false, joined = false;
+  // the forked streams are joined on every way out of this function: an error return between fork and join must not
+  // leave side-stream work running beside the next evaluation
+  struct Joiner {
+    Plan& P;
+    bool &f1, &f2, &done;
+    ~Joiner() {
+      if (done) return;
+      if (f1 && cudaEventRecord(P.ev_join, P.side) == cudaSuccess) cudaStreamWaitEvent(P.stream, P.ev_join, 0);
+      if (f2 && cudaEventRecord(P.ev_join2, P.bulk2) == cudaSuccess) cudaStreamWaitEvent(P.stream, P.ev_join2, 0);
+    }
+  } joiner{*this, forked, forked2, joined};
+  // ASSET_B200_TIMELINE=1 (measurement): device time stamps on every stream of this evaluation, printed after a
+  // synchronisation -- what ran beside what
+  static const bool timeline = getenv("ASSET_B200_TIMELINE") != nullptr;
+  std::vector<std::pair<std::string, cudaEvent_t>> marks;
+  auto mark = [&](const char* label, cudaStream_t st) {
+    if (!timeline) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    marks.emplace_back(label, e);
+  };
+  mark("start", stream);
   auto small_stream = [&]() -> cudaStream_t {
     if (!overlap) return stream;
     if (!forked) {
@@ -813,7 +863,6 @@ int Plan::eval(int mode, double obj_scale) {
     }
     return side;
   };
-  bool forked2 = false;
   auto bulk_stream = [&](size_t k) -> cudaStream_t {
     if (!overlap || heavy_fn < 0 || (int) k == heavy_fn) return stream;
     if (!forked2) {
@@ -887,7 +936,9 @@ int Plan::eval(int mode, double obj_scale) {
       if (int rc = prof_begin(name + suffix)) return rc;
       const int jr = ensure_jit(k, fm, 1);
       if (jr < 0) return -jr;
-      cudaStream_t st = (e - b <= 4096) ? small_stream() : stream;
+      // fused evaluation: the mesh ends and the fused edge segments may write the same entries, so they stay on one
+      // stream whatever their size (the edge segments follow them there)
+      cudaStream_t st = (e - b <= 4096 || fused_eval) ? small_stream() : stream;
       if (jr > 0) {
         JitArgs a = ja;
         a.begin = b;
@@ -992,12 +1043,32 @@ int Plan::eval(int mode, double obj_scale) {
       cudaStreamWaitEvent(bulk2, ev_fork, 0);
       forked2 = true;
     }
+    mark("side: mesh ends done", small_stream());
     if (int rc = fused_launch(f_blo, f_bhi, stream, true)) return rc;
+    mark("stream: bulk pieces done", stream);
+    if (forked2) mark("bulk2: bulk pieces done", bulk2);
     // the edge segments follow the mesh ends on the side stream, beside the bulk
     cudaStream_t es = small_stream();
     if (int rc = fused_launch(f_b, f_blo, es)) return rc;
     if (int rc = fused_launch(f_bhi, f_e, es)) return rc;
+    mark("side: edge segments done", es);
+    if (int rc = prof_end()) return rc;
+    // targets that do not depend on the fused kernels are summed here, beside the bulk
+    struct {
+      DevGather* g;
+      double* out;
+      bool on;
+    } early[3] = {{&gkE, d_kkt, out_kkt}, {&gpE, d_pgx, out_pgx}, {&gaE, d_agx, out_agx}};
+    for (auto& eg: early)
+      if (eg.on && eg.g->dev[0].ntargets > 0) {
+        if (int rc = prof_begin("gather:early")) return rc;
+        AB_CUDA(launch_gather(eg.g->dev[0], eg.g->dev[1], d_stage, eg.out, d_gscratch, es));
+        launches++;
+        if (int rc = prof_end()) return rc;
+      }
   }
+  if (forked) mark("side: early gathers done", side);
+  joined = true;
   if (forked) {
     AB_CUDA(cudaEventRecord(ev_join, side));
     AB_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
@@ -1015,7 +1086,6 @@ int Plan::eval(int mode, double obj_scale) {
           launches++;
         }
     }
-    if (int rc = prof_end()) return rc;
   }
   auto G = [&](DevGather& g, double* out, const char* label) -> int {
     const int n = (g.dev[0].ntargets > 0) + (g.dev[1].ntargets > 0);
@@ -1032,6 +1102,16 @@ int Plan::eval(int mode, double obj_scale) {
   const bool fsh = fused_eval && world > 1;
   if (out_fx && ((rc = G(fsh ? geF : ge, d_fxe, "gather:FXE")) || (rc = G(fsh ? giF : gi, d_fxi, "gather:FXI")))) return rc;
   if (out_val && (rc = G(fsh ? gvF : gv, d_val, "gather:val"))) return rc;
+  if (timeline) {
+    mark("end", stream);
+    cudaStreamSynchronize(stream);
+    for (size_t k = 1; k < marks.size(); k++) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, marks[0].second, marks[k].second);
+      fprintf(stderr, "[asset_b200 timeline] %-28s %8.3f ms\n", marks[k].first.c_str(), ms);
+    }
+    for (auto& m: marks) cudaEventDestroy(m.second);
+  }
   return 0;
 }
 

@@ -68,6 +68,7 @@ struct Plan {
   std::vector<JitKernel> fused_jits;  // one kernel per piece (row block)
   signed char fused_state = 0;  // 0 not tried, 1 ready, -1 unavailable
   DevGather gkF, gpF, gaF;      // gather lists without the targets the fused kernel writes
+  DevGather gkE, gpE, gaE;      // ... of which the low fan-in targets no fused kernel feeds: summed on the side stream
   DevGather geF, giF, gvF;      // sharded plans: this rank's share of the constraint-row / objective-value lists
   // cut set of the fused evaluation on a sharded plan: every gather target fed by the fused kernels' staged outputs
   // (objective value, entries of rows no segment owns); rank 0 owns them all

@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--no-extras", action="store_true", help="defect constraints only (no bounds / integral objective)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the (untimed) oracle-window comparison before the timed region")
     ap.add_argument("--shard", default="one-phase", choices=["one-phase", "phases"],
                     help="N > 1: one phase of N x segments split across the ranks with the NCCL cut-set reduce (default), "
                          "or one independent phase per rank (no collective)")
@@ -141,6 +142,39 @@ def run_reference(a):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------ parity leg
+def parity_check(nlp, ph, nseg_total, world, rank, X, LE, LI, sc, dist=None):
+    """Not timed: one evalKKT of the bench problem against oracle windows (oracle/windows.py) of 128 segments at both
+    mesh ends, the middle and every rank cut; the ranks' disjoint slices are summed over NCCL first.  Returns the worst
+    relative difference (rank 0) -- the value evidence that travels with the throughput line."""
+    import torch
+    from asset_asrl_b200.Solvers import EVAL_KKT
+    from oracle.windows import WindowCheck
+    pd = ph.dims()
+    vs = pd["XtUVars"] * (pd["cardinalStates"] - 1)
+    if pd["blocked"]:
+        return None
+    centres = [64, nseg_total // 2, nseg_total - 64] + [nseg_total * r // world for r in range(1, world)]
+    windows = [(max(c - 64, 0) * vs, min(c + 64, nseg_total) * vs) for c in centres]
+    wc = WindowCheck(nlp, windows)
+    nlp.set_inputs(X, LE, LI)
+    nlp.eval_device(EVAL_KKT, 0.7)
+    nlp.sync()
+    slices = {}
+    for k in ("KKT", "AGX", "PGX", "FXE", "FXI"):
+        idx = torch.from_numpy(wc.index[k]).cuda()
+        t = nlp.device_tensor(k)[idx] if idx.numel() else torch.zeros(0, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t)
+        slices[k] = t.cpu().numpy()
+    if rank != 0:
+        return None
+    worst = wc.compare(slices, 0.7, X, LE, LI, sc)
+    return {"max_rel": max(worst[k] for k in ("KKT", "AGX", "PGX", "FXE", "FXI") if k in worst), "per_array": {k: worst[k] for k in worst if k in ("KKT", "AGX", "PGX", "FXE", "FXI")},
+            "windows": len(windows), "rows": worst["rows"], "applications": worst["applications"],
+            "how": "oracle windows of 128 segments at both mesh ends, the middle and every rank cut; tolerance 1e-12 of the window's max-norm"}
+
+
 # ------------------------------------------------------------------------------------------------ GPU arm
 def _lib_cut_count(nlp):
     from asset_asrl_b200._lib import lib
@@ -187,8 +221,15 @@ def run_b200(a):
         X = ph.makeSolverInput()
         LE, LI = W.multipliers(nlp, seed=67890 + rank)
         nlp.to_device(local)
-    nlp.set_solver_coeffs(np.ones(d["n_solver"]))
+    sc = np.linspace(0.5, 1.5, d["n_solver"])
+    nlp.set_solver_coeffs(sc)
     t_setup = time.time() - t_setup
+    parity = None
+    if not a.no_parity and (sharded or world == 1):
+        parity = parity_check(nlp, ph, a.segments * (world if sharded else 1), world if sharded else 1, rank, X, LE, LI, sc,
+                              dist if world > 1 else None)
+        if parity is not None and not parity["max_rel"] < 1e-12:
+            raise SystemExit(f"bench.py: the CUDA path differs from the oracle: {parity}")
     stream = torch.cuda.ExternalStream(nlp.stream(), device=local)
 
     def barrier():
@@ -325,6 +366,7 @@ def run_b200(a):
                                        ("one independent phase per rank, no collective" if world > 1 else "single GPU"),
                            "l2": f"no flush: per-eval working set {b_alg_eval / 1e6:.0f} MB of values (+ index maps) > 126 MB L2",
                            "setup_s": round(t_setup, 2)},
+                "parity_max_rel": parity["max_rel"] if parity else None, "parity": parity,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "specialised_launches": specialised, "clocks": clk,
                 "kernels_ms": kernels}
         print(json.dumps(line), flush=True)

@@ -31,7 +31,8 @@ class Kernel:
         body = ptx[ptx.index(".visible .entry"):]
         self.lines = [ln.strip() for ln in body.split("\n")]
         self.groups = {}  # %rgN -> (param index, byte stride per rel, byte offset)
-        pend = None
+        self.sector = {}  # %rhN -> (param index, byte stride per rel, byte offset, multiplier of the alignment term)
+        pend = pend_m = None
         for ln in self.lines:
             m = re.match(r"mul\.wide\.s32 %rt, %rel, (-?\d+);", ln)
             if m:
@@ -44,6 +45,23 @@ class Kernel:
             m = re.match(r"add\.s64 %rg(\d+), %rg\1, (-?\d+);", ln)
             if m:
                 self.groups[int(m.group(1))][2] += int(m.group(2))
+                continue
+            # sector base registers: %rh<g> = array + rel * stride + constant + ((-(rel * m)) mod 4) * 8
+            m = re.match(r"add\.s64 %rh(\d+), %rt, %rp(\d+);", ln)
+            if m:
+                self.sector[int(m.group(1))] = [int(m.group(2)), pend, 0, 0]
+                continue
+            m = re.match(r"add\.s64 %rh(\d+), %rh\1, (-?\d+);", ln)
+            if m:
+                self.sector[int(m.group(1))][2] += int(m.group(2))
+                continue
+            m = re.match(r"mul\.lo\.s32 %ri, %rel, (\d+);", ln)
+            if m:
+                pend_m = int(m.group(1))
+                continue
+            m = re.match(r"add\.s64 %rh(\d+), %rh\1, %rt;", ln)
+            if m:
+                self.sector[int(m.group(1))][3] = pend_m
 
     def run(self, arrays, rel, scale=1.0):
         """Executes thread `rel`; `arrays` maps parameter index (see PARAMS) -> float64 numpy array (modified in place)."""
@@ -60,9 +78,13 @@ class Kernel:
             return R[tok]
 
         def gaddr(expr):
-            m = re.match(r"\[%rg(\d+)(?:\+(-?\d+))?\]", expr)
-            par, st, off = self.groups[int(m.group(1))]
-            b = st * rel + off + int(m.group(2) or 0)
+            m = re.match(r"\[%r([gh])(\d+)(?:\+(-?\d+))?\]", expr)
+            if m.group(1) == "g":
+                par, st, off = self.groups[int(m.group(2))]
+                b = st * rel + off + int(m.group(3) or 0)
+            else:
+                par, st, off, mul = self.sector[int(m.group(2))]
+                b = st * rel + off + ((-(rel * mul)) & 3) * 8 + int(m.group(3) or 0)
             assert b % 8 == 0
             return par, b // 8, b
 
@@ -123,7 +145,7 @@ class Kernel:
             elif op.startswith(("setp", "selp")):
                 _cmp(op, rest, R, preds, val)
             elif op.startswith(("ld.param", "cvta", "mov.u32", "mad.", "add.s", "add.u", "and.b32", "mul.wide", "sub.s32", "min.s32",
-                                "shl.", "cvt.", "bra", "bar.", "not.", "mov.b32")):
+                                "shl.", "cvt.", "bra", "bar.", "not.", "mov.b32", "mul.lo", "neg.s32")):
                 continue  # prologue / address set-up, handled through the groups table
             else:
                 raise NotImplementedError("ptx_emu: " + ln)

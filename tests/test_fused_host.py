@@ -46,7 +46,7 @@ def _stores(ptx):
     """Outputs a thread stores: tile-walk kernels park each in the transposition tile; direct-store kernels write runs
     with one predicated store sequence per alignment phase of the thread -- count the elements of phase 0."""
     n = len(re.findall(r"^st\.shared\.f64 \[%rso\+", ptx, flags=re.M))
-    for pred, vec in re.findall(r"^(@%pm\d_\d )?st\.global(?:\.cs)?(\.v[24])?\.f64 \[%rg", ptx, flags=re.M):
+    for pred, vec in re.findall(r"^(@%pm\d_\d )?st\.global(?:\.cs)?(\.v[24])?\.f64 \[%r[gh]", ptx, flags=re.M):
         if pred == "" or pred.endswith("_0 "):
             n += int(vec[2]) if vec else 1
     return n

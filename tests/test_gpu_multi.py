@@ -76,6 +76,52 @@ def test_sharded_plans_on_one_device(name, world):
                 assert min(nz) > 0.2 * max(nz), "the value array is not split evenly"
 
 
+
+def test_world8_sharded_plans_at_20k_segments():
+    """World 8 (the north-star box): eight sharded plans of one 20 000-segment phase on one device, the cut set reduced by
+    hand, every output against the full oracle and -- through oracle windows -- around each of the seven cuts."""
+    import torch
+    from oracle.windows import check_windows
+    world, nseg = 8, 20000
+    ph = W.make_phase("lowthrust", "LGL5", nseg)
+    nlp0 = ph.transcribe()
+    X = ph.makeSolverInput()
+    LE, LI, sc = problem_inputs(nlp0)
+    ref = oracle.Oracle.from_problem(nlp0).eval("KKT", 0.7, X, LE, LI, sc, threads=oracle.hardware_threads())
+    plans = []
+    for r in range(world):
+        nlp = clone_problem(ph)
+        nlp.to_device(0, rank=r, world=world)
+        nlp.set_solver_coeffs(sc)
+        nlp.set_inputs(X, LE, LI)
+        plans.append(nlp)
+    for p in plans:
+        p.world = 1
+        p.eval_device(EVAL_KKT, 0.7)
+        p.world = world
+        p.cut_pack()
+        p.sync()
+    total = sum(p.cut_tensor().clone() for p in plans)
+    for p in plans:
+        p.cut_tensor().copy_(total)
+        torch.cuda.synchronize()
+        p.cut_unpack()
+        p.sync()
+    outs = [p.get_outputs() for p in plans]
+    summed = {}
+    for k in KEYS:
+        stack = np.stack([o[k] for o in outs])
+        assert np.all((stack != 0).sum(axis=0) <= 1), (k, "an output is held by more than one rank")
+        summed[k] = stack.sum(axis=0)
+        assert rel_err(summed[k], ref[k]) < TOL, k
+    tot = sum(o["val"] for o in outs)
+    assert abs(tot - ref["val"]) <= TOL * max(abs(ref["val"]), 1.0)
+    assert all(p.fused_segments() > 0 for p in plans)
+    windows = [(max(nseg * r // world - 64, 0) * 20, (nseg * r // world + 64) * 20) for r in range(1, world)]
+    worst = check_windows(nlp0, summed, windows, 0.7, X, LE, LI, sc)
+    for k in KEYS:
+        assert worst[k] < TOL, (k, worst)
+
 def _nccl_worker(rank, world, port, q):
     import torch
     import torch.distributed as dist

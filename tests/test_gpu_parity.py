@@ -158,3 +158,56 @@ def test_full_size_properties():
     LEw[:12 * nw] = LE[12 * w0:12 * (w0 + nw)]
     refw = orc.eval("KKT", 1.0, phw.makeSolverInput(), LEw, np.zeros(nlpw.dims()["niq"]))
     assert rel_err(a["FXE"][12 * w0:12 * (w0 + nw)], refw["FXE"][:12 * nw]) < TOL
+
+
+def test_full_size_every_output_against_the_oracle():
+    """The bench workload at its benchmarked size (2*10^5 low-thrust LGL5 segments, fused kernels): every output array of
+    evalKKT -- KKT values, FXE, FXI, PGX, AGX, val -- against the oracle evaluated on the whole problem, and the CSR
+    pattern bit-exact."""
+    nseg = 200000
+    ph = W.make_phase("lowthrust", "LGL5", nseg)
+    nlp = ph.transcribe()
+    d = nlp.dims()
+    X = ph.makeSolverInput()
+    LE, LI = W.multipliers(nlp)
+    sc = np.random.default_rng(5).uniform(0.5, 1.5, d["n_solver"])
+    nlp.to_device(0)
+    nlp.set_solver_coeffs(sc)
+    out = nlp.evalKKT(0.7, X, LE, LI)
+    assert nlp.fused_segments() > 0.99 * nseg
+    orc = oracle.Oracle.from_problem(nlp)
+    ip, ix, loc = orc.pattern()
+    ip2, ix2 = nlp.pattern()
+    assert np.array_equal(ip, ip2) and np.array_equal(ix, ix2) and np.array_equal(loc, nlp.kkt_locations())
+    ref = orc.eval("KKT", 0.7, X, LE, LI, sc, threads=oracle.hardware_threads())
+    check(out, ref, MODES["KKT"], "full size")
+    # block-wise as well: a wrong value in a small block must not hide behind the largest entry of the whole array
+    nb = 4096
+    for k in ("KKT", "AGX", "FXE"):
+        a, b = out[k], ref[k]
+        n = a.size // nb * nb
+        blk = np.abs(b[:n]).reshape(-1, nb).max(axis=1)
+        err = np.abs(a[:n] - b[:n]).reshape(-1, nb).max(axis=1)
+        assert np.all(err <= TOL * np.maximum(blk, 1e-300) + 1e-300), (k, float((err / np.maximum(blk, 1e-300)).max()))
+
+
+def test_full_size_oracle_windows():
+    """The same mesh through oracle windows (oracle/windows.py): both mesh ends, the middle, and the seven cuts of a
+    world-8 partition of the fused segments, 256 segments each."""
+    from oracle.windows import check_windows
+    nseg = 200000
+    ph = W.make_phase("lowthrust", "LGL5", nseg)
+    nlp = ph.transcribe()
+    d = nlp.dims()
+    X = ph.makeSolverInput()
+    LE, LI = W.multipliers(nlp)
+    sc = np.random.default_rng(5).uniform(0.5, 1.5, d["n_solver"])
+    nlp.to_device(0)
+    nlp.set_solver_coeffs(sc)
+    out = nlp.evalKKT(0.7, X, LE, LI)
+    vs = 20  # variables per segment: two nodes of 10
+    centres = [128, nseg // 2, nseg - 128] + [nseg * r // 8 for r in range(1, 8)]
+    windows = [(max(c - 128, 0) * vs, min(c + 128, nseg) * vs) for c in centres]
+    worst = check_windows(nlp, out, windows, 0.7, X, LE, LI, sc)
+    for k in ("KKT", "AGX", "PGX", "FXE", "FXI"):
+        assert worst[k] < TOL, (k, worst)

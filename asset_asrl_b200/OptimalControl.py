@@ -398,6 +398,28 @@ class ODEPhase:
         self.nlp = nlp
         return nlp
 
+    def transcribe_window(self, rank, world, halo=8):
+        """This rank's share of the phase, analysed locally: the transcription of the whole phase restricted to the
+        applications within ``halo`` segments of mesh segments [N*rank/world, N*(rank+1)/world) before the sparsity
+        analysis (replaces the whole-problem pass of NonLinearProgram.cpp:267-344; cost and memory follow the share,
+        not the phase).  Returns a NonLinearProgram for ``to_device(device, rank=rank, world=world)``; indices and
+        dimensions are those of the whole problem, the CSR pattern is the window's own."""
+        if not self.h:
+            raise RuntimeError("setTraj must be called before transcribe")
+        d = self.dims()
+        if d["blocked"]:
+            raise NotImplementedError("windowed transcription of block-constant controls")
+        nlp = NonLinearProgram()
+        out = (C.c_int * 3)()
+        _lib.check(lib.ab_phase_transcribe(self.h, nlp.h, 0, 0, 0, out))
+        nlp.set_dims(out[0], out[1], out[2])
+        n = d["numDefects"]
+        seg_vars = d["XtUVars"] * (d["cardinalStates"] - 1)
+        mesh_vars = d["numStates"] * d["XtUVars"]
+        nlp.window(mesh_vars, seg_vars, n, n * rank // world, n * (rank + 1) // world, halo)
+        nlp.analyze()
+        return nlp
+
     def optimize(self, *a, **k):
         raise NotImplementedError("PSIOPT's interior-point loop and sparse LDLT are out of scope for this build "
                                   "(SURVEY.md section 2 row 13); use phase.transcribe() and nlp.evalKKT(...)")

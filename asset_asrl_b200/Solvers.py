@@ -54,6 +54,18 @@ class NonLinearProgram:
         return _lib.check(lib.ab_problem_add_function(self.h, role, tape, int(linear), int(unique_constraints), nappl, vp,
                                                       cp if cindex is not None else None, ap if appconst is not None else None))
 
+    def window(self, mesh_vars, seg_vars, nseg, seg_lo, seg_hi, halo=8):
+        """Rank-local analysis (ab_problem_window): keep the applications homed within ``halo`` segments of
+        [seg_lo, seg_hi), own those homed inside it.  Call before analyze()."""
+        _lib.check(lib.ab_problem_window(self.h, int(mesh_vars), int(seg_vars), int(nseg), int(seg_lo), int(seg_hi), int(halo)))
+        self._dims = None
+        self.windowed = True
+
+    def window_info(self, f):
+        out = (C.c_int * 4)()
+        _lib.check(lib.ab_problem_window_info(self.h, f, out))
+        return dict(zip(["app_base", "nappl_whole", "own_lo", "own_hi"], list(out)))
+
     def analyze(self):
         _lib.check(lib.ab_problem_analyze(self.h))
         self._dims = None

@@ -104,6 +104,8 @@ SIGNATURES = {
     "ab_plan_profile_read": (_i, [_vp, C.POINTER(C.c_float), _i]),
     "ab_plan_profile_label": (_ll, [_vp, _i, _cp, _ll]),
     "ab_plan_device_ptr": (_vp, [_vp, _i]),
+    "ab_problem_window": (_i, [_vp, _ll, _i, _ll, _ll, _ll, _i]),
+    "ab_problem_window_info": (_i, [_vp, _i, _ip]),
     "ab_plan_stream": (_vp, [_vp]),
     "ab_plan_launches": (_ll, [_vp]),
     "ab_plan_specialised_launches": (_ll, [_vp]),

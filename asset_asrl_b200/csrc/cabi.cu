@@ -197,6 +197,25 @@ int ab_problem_add_function(ab_problem* p, int role, int tape, int linear, int u
   AB_CATCH
 }
 
+int ab_problem_window(ab_problem* p, long long mesh_vars, int seg_vars, long long nseg, long long seg_lo, long long seg_hi, int halo) {
+  AB_TRY
+  p->p.window(mesh_vars, seg_vars, nseg, seg_lo, seg_hi, halo);
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_window_info(const ab_problem* p, int fidx, int out[4]) {
+  AB_TRY
+  const Problem::Window& W = p->p.win;
+  if (!W.on) return fail(AB_ERR_INVALID, "not a windowed problem");
+  if (fidx < 0 || fidx >= (int) W.app_base.size()) return fail(AB_ERR_INVALID, "bad function index");
+  out[0] = W.app_base[(size_t) fidx];
+  out[1] = W.nappl_whole[(size_t) fidx];
+  out[2] = W.own_lo[(size_t) fidx];
+  out[3] = W.own_hi[(size_t) fidx];
+  return AB_OK;
+  AB_CATCH
+}
+
 int ab_problem_analyze(ab_problem* p) {
   AB_TRY
   p->p.analyze();
@@ -609,6 +628,7 @@ int ab_plan_create_sharded(const ab_problem* p, int device, int rank, int world,
 void ab_plan_destroy(ab_plan* plan) { delete plan; }
 long long ab_plan_cut_count(const ab_plan* plan) { return plan->plan.active_cut_count(); }
 int ab_plan_fused_segments(const ab_plan* plan) {
+  if (plan->plan.windowed) return plan->plan.last_fused ? (int) (plan->plan.win_f_e - plan->plan.win_f_b) : 0;
   return plan->plan.last_fused ? plan->plan.fused.t_hi - plan->plan.fused.t_lo : 0;
 }
 int ab_plan_output_ranges(const ab_plan* plan, int array, long long* out, int cap) {

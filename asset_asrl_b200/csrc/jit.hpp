@@ -60,6 +60,7 @@ struct JitSpec {
   bool streaming_stores = false;   // direct stores carry the .cs (evict-first) cache operator
   // Direct stores only: finished outputs wait in a queue and leave spread evenly over the program's arithmetic instead
   // of in the bursts they are finished in (jit.cpp: drain_outputs); at most pace_burst outputs per arithmetic bundle.
+  bool park_indexed = true;        // indexed variant: register budget with shared-memory parking like the affine variant (false: all values left to the assembler)
   bool phase_bases = true;         // one base register per (address group, alignment phase) for the 32-byte stores (jit.cpp: addr_sector)
   bool pace_outputs = false;
   int pace_burst = 2;

@@ -58,6 +58,66 @@ void build_gather(const std::vector<int>& tgt_of_src,  // target id per source (
 
 }  // namespace
 
+void Problem::window(long long mesh_vars, int seg_vars, long long nseg, long long seg_lo, long long seg_hi, int halo) {
+  if (analyzed) throw std::logic_error("window: the problem has been analysed already");
+  if (seg_vars <= 0 || nseg <= 0 || seg_lo < 0 || seg_hi > nseg || seg_lo >= seg_hi || mesh_vars > nvars)
+    throw std::invalid_argument("window: bad segment range");
+  win = Window();
+  win.on = true;
+  win.mesh_vars = mesh_vars;
+  win.seg_vars = seg_vars;
+  win.nseg = nseg;
+  win.seg_lo = seg_lo;
+  win.seg_hi = seg_hi;
+  win.halo = halo;
+  win.first = seg_lo == 0;
+  win.last = seg_hi == nseg;
+  const long long k_lo = std::max<long long>(seg_lo - halo, 0), k_hi = std::min<long long>(seg_hi + halo, nseg);
+  const size_t nf = funcs.size();
+  win.app_base.assign(nf, 0);
+  win.nappl_whole.assign(nf, 0);
+  win.own_lo.assign(nf, 0);
+  win.own_hi.assign(nf, 0);
+  for (size_t f = 0; f < nf; f++) {
+    FuncRec& fn = funcs[f];
+    win.nappl_whole[f] = fn.nappl;
+    int keep_lo = -1, keep_hi = -1, own_lo = -1, own_hi = -1;
+    for (int a = 0; a < fn.nappl; a++) {
+      long long vmin = -1;
+      for (int i = 0; i < fn.ir; i++) {
+        const long long v = fn.vindex[(size_t) a * fn.ir + i];
+        if (v < mesh_vars && (vmin < 0 || v < vmin)) vmin = v;
+      }
+      const long long home = vmin < 0 ? -1 : std::min(vmin / seg_vars, nseg - 1);
+      const bool keep = home < 0 || (home >= k_lo && home < k_hi);
+      const bool own = home < 0 ? win.last : (home >= seg_lo && home < seg_hi);
+      if (keep) {
+        if (keep_lo < 0) keep_lo = a;
+        else if (keep_hi != a) throw std::runtime_error("window: kept applications of " + fn.name + " are not contiguous");
+        keep_hi = a + 1;
+      }
+      if (own) {
+        if (own_lo < 0) own_lo = a;
+        else if (own_hi != a) throw std::runtime_error("window: owned applications of " + fn.name + " are not contiguous");
+        own_hi = a + 1;
+      }
+    }
+    if (keep_lo < 0) keep_lo = keep_hi = 0;
+    if (own_lo < 0) own_lo = own_hi = keep_lo;
+    win.app_base[f] = keep_lo;
+    win.own_lo[f] = own_lo - keep_lo;
+    win.own_hi[f] = own_hi - keep_lo;
+    const int n = keep_hi - keep_lo;
+    fn.vindex = std::vector<int>(fn.vindex.begin() + (size_t) keep_lo * fn.ir, fn.vindex.begin() + (size_t) keep_hi * fn.ir);
+    if (fn.role != 0)
+      fn.cindex = std::vector<int>(fn.cindex.begin() + (size_t) keep_lo * fn.orows, fn.cindex.begin() + (size_t) keep_hi * fn.orows);
+    if (fn.nappconst > 0)
+      fn.appconst = std::vector<double>(fn.appconst.begin() + (size_t) keep_lo * fn.nappconst,
+                                        fn.appconst.begin() + (size_t) keep_hi * fn.nappconst);
+    fn.nappl = n;
+  }
+}
+
 void Problem::analyze() {
   const int PV = nvars, SV = niq, EC = neq, IC = niq;
   kktdim = PV + SV + EC + IC;

@@ -7,6 +7,7 @@
 // DenseFunctionBase::getKKTSpace (/root/reference/src/VectorFunctions/DenseFunctionBase.h:1097-1129).
 // The canonical triplet order is the reference's Threads=1 order.
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -69,6 +70,35 @@ struct Problem {
 
   void analyze();
   long long nnz() const { return (long long) indices.size(); }
+
+  // ---- window of a single-phase problem (rank-local analysis, SURVEY.md section 8e / NonLinearProgram.cpp:267-344) ----
+  // A rank that evaluates mesh segments [seg_lo, seg_hi) of one long phase needs the structure of those segments and of a
+  // few neighbours only.  window() keeps, of every function, the applications whose *home segment* -- the segment of the
+  // lowest mesh variable they read -- lies within `halo` segments of the range, with all indices still global (variables,
+  // constraint rows, dimensions), so that analyze() yields, for the rows of the window's interior, exactly the rows of
+  // the whole problem's KKT pattern at a cost proportional to the window.  Applications homed inside [seg_lo, seg_hi)
+  // are *owned*: the rank evaluates those and nothing else.  Applications that read no mesh variable (parameter-only
+  // functions) are kept everywhere and owned by the last rank.
+  struct Window {
+    bool on = false;
+    long long mesh_vars = 0;  // variables [0, mesh_vars) belong to mesh nodes; the rest are parameters
+    int seg_vars = 0;         // variables per segment
+    long long nseg = 0, seg_lo = 0, seg_hi = 0;
+    int halo = 0;
+    bool first = false, last = false;     // the range starts / ends at a real mesh end
+    std::vector<int> app_base;            // per function: application number (in the whole problem) of the first kept one
+    std::vector<int> nappl_whole;         // per function: applications in the whole problem
+    std::vector<int> own_lo, own_hi;      // per function: kept applications [own_lo, own_hi) are owned
+    // does this rank own mesh variable / far (parameter) variable v?
+    bool owns_var(long long v) const {
+      if (v >= mesh_vars) return false;
+      const long long sg = std::min(v / seg_vars, nseg - 1);
+      return sg >= seg_lo && sg < seg_hi;
+    }
+  } win;
+  // Restricts the function list to the window (before analyze()); throws if the kept or owned applications of a function
+  // are not one contiguous range.
+  void window(long long mesh_vars, int seg_vars, long long nseg, long long seg_lo, long long seg_hi, int halo);
 };
 
 constexpr int LARGE_FANIN = 96;

@@ -1,6 +1,7 @@
 #include "plan.hpp"
 
 #include <algorithm>
+#include <stdexcept>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -40,8 +41,15 @@ Plan::~Plan() {
     for (auto& a: v)
       for (JitKernel& k: a) unload_jit(k);
   for (JitKernel& k: fused_jits) unload_jit(k);
+  for (EvalGraph& g: graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
+  for (int i = 1; i < SIDE_POOL; i++)
+    if (side_pool[i]) cudaStreamDestroy(side_pool[i]);
+  for (int i = 0; i < SIDE_POOL; i++)
+    if (ev_pool[i]) cudaEventDestroy(ev_pool[i]);
+  if (ev_ends) cudaEventDestroy(ev_ends);
   if (side) cudaStreamDestroy(side);
   if (bulk2) cudaStreamDestroy(bulk2);
   if (ev_join2) cudaEventDestroy(ev_join2);
@@ -146,11 +154,145 @@ static bool up_gather(Plan& P, const GatherList gl[2], DevGather& dg) {
   return true;
 }
 
+// Windowed plan: of the fused evaluation's gather lists keep what this rank owns, and make the cut set.
+//   * a target in a row of a mesh variable or of a constraint the rank owns stays as it is -- every source of it must
+//     be something the rank evaluates (checked);
+//   * a target in a row this rank does not own (the window's halo) goes;
+//   * a *far* target -- rows of parameter variables, accumulated constraint rows, the objective value -- stays on every
+//     rank with the sources the rank itself writes (the solver coefficients on rank 0 only) and joins the cut set, which
+//     is summed over the ranks after the evaluation; far targets are the same on every rank, in the same order, because
+//     they do not depend on the window.
+// Also fills own_app_lo / own_app_hi, the fused thread range, and the output blocks.
+void Plan::window_filter(GatherList (*fl)[2], GatherList (*flE)[2], std::vector<int>* cut_t, int true_world) {
+  const Problem::Window& W = prob.win;
+  const long long R = fused.t_hi - fused.t_lo;
+  const long long abase = W.app_base[(size_t) fused.anchor];
+  // fused threads of owned segments, in thread numbers relative to t_lo
+  win_f_b = std::min(std::max<long long>(W.seg_lo - abase - fused.t_lo, 0), R);
+  win_f_e = std::min(std::max<long long>(W.seg_hi - abase - fused.t_lo, 0), R);
+  if (!W.first && W.seg_lo - abase < fused.t_lo) throw std::runtime_error("window: the halo is shorter than the non-periodic margin of the mesh");
+  if (!W.last && W.seg_hi - abase > fused.t_hi) throw std::runtime_error("window: the halo is shorter than the non-periodic margin of the mesh");
+  // staging slots this rank writes in an evaluation
+  std::vector<unsigned char> wr((size_t) prob.stage_size + 1, 0);
+  std::vector<unsigned char> own_eq((size_t) std::max(prob.neq, 1), 0), own_iq((size_t) std::max(prob.niq, 1), 0);
+  for (size_t k = 0; k < fns.size(); k++) {
+    const int fi = prob.order[k];
+    const FuncRec& fr = prob.funcs[fi];
+    const int E = fr.triplets_per_app();
+    for (int ap = W.own_lo[(size_t) fi]; ap < W.own_hi[(size_t) fi]; ap++) {
+      if (fr.role != 0 && fr.unique_constraints)
+        for (int o = 0; o < fr.orows; o++) (fr.role == 1 ? own_eq : own_iq)[(size_t) fr.cindex[(size_t) ap * fr.orows + o]] = 1;
+      if (ap >= fused.ex_lo[fi] && ap < fused.ex_hi[fi]) continue;  // a fused thread evaluates it
+      for (int e = 0; e < E; e++) {
+        const int d = prob.kkt_dest[(size_t) (prob.trip_base[fi] + (long long) ap * E + e)];
+        if (d < 0) wr[(size_t) ~d] = 1;
+      }
+      if (fr.role != 0)
+        for (int o = 0; o < fr.orows; o++) {
+          const int d = prob.f_dest[(size_t) (prob.fdest_base[fi] + (long long) ap * fr.orows + o)];
+          if (d < 0) wr[(size_t) ~d] = 1;
+        }
+      for (int i = 0; i < fr.ir; i++) wr[(size_t) (prob.g_stage[fi] + (long long) ap * fr.ir + i)] = 1;
+      if (fr.role == 0) wr[(size_t) (prob.v_stage[fi] + ap)] = 1;
+    }
+  }
+  for (const auto& pc: fused.pieces)
+    for (const JitOut& w: pc.fout)
+      if (w.arr == FA_STAGE)
+        for (long long r = win_f_b; r < win_f_e; r++) wr[(size_t) (w.base + r * w.stride)] = 1;
+  const long long s0 = prob.stage_solver, s1 = prob.stage_solver + prob.n_solver;
+  const int PV = prob.nvars, SV = prob.niq, EC = prob.neq;
+  // 0 not owned, 1 owned, 2 far
+  auto var_class = [&](long long v) { return v >= W.mesh_vars ? 2 : (W.owns_var(v) ? 1 : 0); };
+  auto row_class = [&](long long r) {
+    if (r < PV) return var_class(r);
+    if (r < PV + SV) return own_iq[(size_t) (r - PV)] ? 1 : 0;
+    if (r < PV + SV + EC) return own_eq[(size_t) (r - PV - SV)] ? 1 : 0;
+    return own_iq[(size_t) (r - PV - SV - EC)] ? 1 : 0;
+  };
+  for (int a = 0; a < OA_COUNT; a++) {
+    cut_t[a].clear();
+    for (int which = 0; which < 2; which++)
+      for (int w = 0; w < 2; w++) {
+        GatherList& g = which ? flE[a][w] : fl[a][w];
+        GatherList o;
+        o.ptr.assign(1, 0);
+        for (int t = 0; t < g.ntargets(); t++) {
+          const long long tg = g.target[(size_t) t];
+          int cls;
+          if (a == OA_KKT) cls = row_class((long long) (std::upper_bound(prob.indptr.begin(), prob.indptr.end(), (int) tg) - prob.indptr.begin()) - 1);
+          else if (a == OA_PGX || a == OA_AGX) cls = var_class(tg);
+          else cls = 2;  // accumulated constraint rows, the objective value
+          if (cls == 0) continue;
+          for (long long q = g.ptr[(size_t) t]; q < g.ptr[(size_t) t + 1]; q++) {
+            const int sidx = g.src[(size_t) q];
+            const bool solver = sidx >= s0 && sidx < s1;
+            if (cls == 1) {
+              if (!solver && !wr[(size_t) sidx]) throw std::runtime_error("window: an owned output has a source this rank does not evaluate (halo too short)");
+              o.src.push_back(sidx);
+            } else if (solver ? rank == 0 : wr[(size_t) sidx] != 0) {
+              o.src.push_back(sidx);
+            }
+          }
+          o.ptr.push_back((long long) o.src.size());
+          o.target.push_back((int) tg);
+          if (cls == 2) cut_t[a].push_back((int) tg);
+        }
+        g = std::move(o);
+      }
+    // far targets must sit in the late lists (they are summed after the fused kernels) and be identical on every rank
+    std::sort(cut_t[a].begin(), cut_t[a].end());
+  }
+  (void) true_world;
+  // what this rank writes: output blocks
+  const long long sizes[OA_COUNT] = {prob.nnz(), prob.nvars, prob.nvars, prob.neq, prob.niq, 1};
+  for (int a = 0; a < OA_COUNT; a++) out_blocks[a].assign((size_t) ((sizes[a] + OUT_BLOCK - 1) / OUT_BLOCK) + 1, 0);
+  auto touch = [&](int a, long long i) { out_blocks[a][(size_t) (i / OUT_BLOCK)] = 1; };
+  auto arr_of = [](int fa) {
+    return fa == FA_KKT ? (int) OA_KKT : fa == FA_FXE ? (int) OA_FXE : fa == FA_FXI ? (int) OA_FXI
+           : fa == FA_PGX ? (int) OA_PGX : fa == FA_AGX ? (int) OA_AGX : -1;
+  };
+  for (const auto& pc: fused.pieces)
+    for (const JitOut& w: pc.fout) {
+      const int a = arr_of(w.arr);
+      if (a < 0 || win_f_e <= win_f_b) continue;
+      const long long i0 = w.base + win_f_b * w.stride, i1 = w.base + (win_f_e - 1) * w.stride;
+      for (long long i = std::min(i0, i1) / OUT_BLOCK; i <= std::max(i0, i1) / OUT_BLOCK; i++) out_blocks[a][(size_t) i] = 1;
+    }
+  for (int a = 0; a < OA_COUNT; a++)
+    for (int w = 0; w < 2; w++) {
+      for (int t: fl[a][w].target) touch(a, t);
+      for (int t: flE[a][w].target) touch(a, t);
+    }
+  for (size_t k = 0; k < fns.size(); k++) {
+    const int fi = prob.order[k];
+    const FuncRec& fr = prob.funcs[fi];
+    const int E = fr.triplets_per_app();
+    for (int ap = W.own_lo[(size_t) fi]; ap < W.own_hi[(size_t) fi]; ap++) {
+      if (ap >= fused.ex_lo[fi] && ap < fused.ex_hi[fi]) continue;
+      for (int e = 0; e < E; e++) {
+        const int d = prob.kkt_dest[(size_t) (prob.trip_base[fi] + (long long) ap * E + e)];
+        if (d >= 0) touch(OA_KKT, d);
+      }
+      if (fr.role != 0)
+        for (int o = 0; o < fr.orows; o++) {
+          const int d = prob.f_dest[(size_t) (prob.fdest_base[fi] + (long long) ap * fr.orows + o)];
+          if (d >= 0) touch(fr.role == 1 ? OA_FXE : OA_FXI, d);
+        }
+    }
+  }
+}
+
 int Plan::build(int dev, int rank_, int world_) {
   if (!prob.analyzed) prob.analyze();
   device = dev;
   rank = rank_;
   world = world_;
+  // A windowed problem (Problem::window) is this rank's share already: the plan is built like a single-device plan on it,
+  // then restricted to what the rank owns (window_filter below); rank / world matter for the cut set only.
+  windowed = prob.win.on;
+  const int true_world = world;
+  if (windowed) world = 1;
   if (world > 1) {
     try {
       part = make_partition(prob, rank, world);
@@ -181,6 +323,15 @@ int Plan::build(int dev, int rank_, int world_) {
     int prio_lo = 0, prio_hi = 0;
     AB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     AB_CUDA(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, getenv("ASSET_B200_NO_PRIORITY") ? prio_lo : prio_hi));
+  }
+  {
+    int prio_lo = 0, prio_hi = 0;
+    AB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    side_pool[0] = side;
+    for (int i = 1; i < SIDE_POOL; i++)
+      AB_CUDA(cudaStreamCreateWithPriority(&side_pool[i], cudaStreamNonBlocking, getenv("ASSET_B200_NO_PRIORITY") ? prio_lo : prio_hi));
+    for (int i = 0; i < SIDE_POOL; i++) AB_CUDA(cudaEventCreateWithFlags(&ev_pool[i], cudaEventDisableTiming));
+    AB_CUDA(cudaEventCreateWithFlags(&ev_ends, cudaEventDisableTiming));
   }
   AB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   AB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
@@ -285,7 +436,7 @@ int Plan::build(int dev, int rank_, int world_) {
   d_pgx = dalloc<double>(prob.nvars);
   d_agx = dalloc<double>(prob.nvars);
   d_val = dalloc<double>(1);
-  d_stage = dalloc<double>((size_t) prob.stage_size);
+  d_stage = dalloc<double>((size_t) prob.stage_size + 1);  // + the trash slot of the fused evaluation's redirected maps
   if (!d_X || !d_LE || !d_LI || !d_kkt || !d_fxe || !d_fxi || !d_pgx || !d_agx || !d_val || !d_stage) {
     last_error = "out of device memory for the value arrays";
     return (int) cudaErrorMemoryAllocation;
@@ -453,11 +604,31 @@ int Plan::build(int dev, int rank_, int world_) {
           }
         }
       }
+      if (windowed) {
+        try {
+          window_filter(fl, flE, cut_t, true_world);
+        } catch (const std::exception& ex) {
+          last_error = ex.what();
+          return (int) cudaErrorInvalidValue;
+        }
+      }
       std::vector<double> appc;
       for (const FuncRec& fr: prob.funcs) appc.insert(appc.end(), fr.appconst.begin(), fr.appconst.end());
       d_appc_all = dupload(appc);
       bool ok = d_appc_all && up_gather(*this, fl[OA_KKT], gkF) && up_gather(*this, fl[OA_PGX], gpF) && up_gather(*this, fl[OA_AGX], gaF)
                 && up_gather(*this, flE[OA_KKT], gkE) && up_gather(*this, flE[OA_PGX], gpE) && up_gather(*this, flE[OA_AGX], gaE);
+      if (ok && windowed) {
+        ok = up_gather(*this, fl[OA_FXE], geF) && up_gather(*this, fl[OA_FXI], giF) && up_gather(*this, fl[OA_VAL], gvF);
+        cutF_count = 0;
+        for (int a = 0; a < OA_COUNT && ok; a++) {
+          cutF_n[a] = (long long) cut_t[a].size();
+          cutF_count += cutF_n[a];
+          std::vector<unsigned char> flag(cut_t[a].size(), (unsigned char) (rank == 0 ? 3 : 1));
+          d_cutF_target[a] = dupload(cut_t[a]);
+          d_cutF_flag[a] = dupload(flag);
+          ok = d_cutF_target[a] && d_cutF_flag[a];
+        }
+      }
       if (ok && world > 1) {
         ok = up_gather(*this, fl[OA_FXE], geF) && up_gather(*this, fl[OA_FXI], giF) && up_gather(*this, fl[OA_VAL], gvF);
         cutF_count = 0;
@@ -524,6 +695,41 @@ int Plan::build(int dev, int rank_, int world_) {
           }
         }
       }
+      // destination maps of the applications left to the per-function kernels, fused-owned slots redirected to the trash
+      // slot (see plan.hpp: kdF)
+      if (ok) {
+        const long long own_k0 = fused.kb, own_k1 = fused.kb + R * fused.ks;
+        const int trash = ~(int) prob.stage_size;
+        kdF.assign(fns.size(), nullptr);
+        kdF_lo.assign(fns.size(), 0);
+        kdF_hi.assign(fns.size(), 0);
+        for (size_t k = 0; k < fns.size() && ok; k++) {
+          const int fi = prob.order[k];
+          const FuncRec& fr = prob.funcs[fi];
+          const int E = fr.triplets_per_app();
+          int xl = fused.ex_lo[fi], xh = fused.ex_hi[fi];
+          if (xh <= xl) xl = xh = fr.nappl;  // not covered by the fused kernels: every application, one chunk
+          const long long rows = (long long) xl + (fr.nappl - xh);
+          if (rows > (1 << 20)) {  // a large function outside the template: keep its own map (it cannot touch fused rows)
+            kdF_lo[k] = kdF_hi[k] = -1;
+            continue;
+          }
+          std::vector<int> m((size_t) (rows * E));
+          const int* src = prob.kkt_dest.data() + prob.trip_base[fi];
+          for (long long r = 0; r < rows; r++) {
+            const long long a = r < xl ? r : xh + (r - xl);
+            for (int e = 0; e < E; e++) {
+              const int d = src[(size_t) (a * E + e)];
+              m[(size_t) (r * E + e)] = (d >= own_k0 && d < own_k1) ? trash : d;
+            }
+          }
+          if (m.empty()) m.push_back(0);
+          kdF[k] = dupload(m);
+          kdF_lo[k] = xl;
+          kdF_hi[k] = xh;
+          ok = kdF[k] != nullptr;
+        }
+      }
       if (!ok) {
         last_error = "out of device memory for the fused evaluation's gather lists";
         return (int) cudaErrorMemoryAllocation;
@@ -532,7 +738,19 @@ int Plan::build(int dev, int rank_, int world_) {
       jit_log = "no fused interior: " + fused.why;
     }
   }
-  if (world > 1) {
+  if (windowed) {
+    if (!fused.ok) {
+      last_error = "a windowed plan needs the fused evaluation: " + (fused.why.empty() ? jit_log : fused.why);
+      return (int) cudaErrorInvalidValue;
+    }
+    world = true_world;
+    d_cutbuf = dalloc<double>((size_t) std::max<long long>(cutF_count, 1));
+    if (!d_cutbuf) {
+      last_error = "out of device memory for the cut buffer";
+      return (int) cudaErrorMemoryAllocation;
+    }
+    finalize_out_ranges();
+  } else if (world > 1) {
     d_cutbuf = dalloc<double>((size_t) std::max<long long>(std::max(cut_count, cutF_count), 1));
     if (!d_cutbuf) {
       last_error = "out of device memory for the cut buffer";
@@ -735,13 +953,20 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
   sp.indexed = variant == 1;
   sp.g_stage = fns[k].g_stage;
   sp.v_stage = fns[k].v_stage;
-  sp.nthreads = 64;
+  sp.nthreads = variant ? 32 : 64;
   std::string ptx;
   std::vector<JitOut> outs;
   JitStats js;
   jit_env_knobs(sp);
+  if (variant == 1 && getenv("ASSET_B200_IDX_NO_PARK")) sp.park_indexed = false;
   try {
     ptx = emit_ptx(host_progs[k][fm], sp, am, &outs, &js);
+    int dev_smem = 0;
+    cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (variant == 1 && (int) js.smem_bytes > dev_smem) {  // more live values than one block can park: leave them to the assembler
+      sp.park_indexed = false;
+      ptx = emit_ptx(host_progs[k][fm], sp, am, &outs, &js);
+    }
   } catch (const std::exception& e) {
     jit_log = std::string(e.what()) + " (" + fr.name + ")";
     return 0;
@@ -804,6 +1029,60 @@ int Plan::ensure_jit(size_t k, int fm, int variant) {
 
 int Plan::eval(int mode, double obj_scale) {
   AB_CUDA(cudaSetDevice(device));
+  static const bool graphs_off = getenv("ASSET_B200_GRAPH") && std::atoi(getenv("ASSET_B200_GRAPH")) == 0;
+  static const bool timeline_on = getenv("ASSET_B200_TIMELINE") != nullptr;
+  const bool fused_now = mode == EM_KKT && fused.ok && fused_state >= 0;
+  // a sharded plan zero-fills its outputs when the evaluation path changes: that call is not the one to capture or replay
+  const bool transition = world > 1 && !windowed && fused_now != last_fused;
+  if (!use_graphs || graphs_off || timeline_on || profiling || mode < 0 || mode >= 8 || transition) return enqueue(mode, obj_scale);
+  EvalGraph& g = graphs[mode];
+  if (g.failed) return enqueue(mode, obj_scale);
+  if (g.exec && g.obj_scale == obj_scale) {
+    AB_CUDA(cudaGraphLaunch(g.exec, stream));
+    launches = g.launches;
+    jit_launches = g.jit_launches;
+    last_mode = mode;
+    last_fused = fused_now && fused_state > 0;
+    return 0;
+  }
+  if (g.evals < 1) {  // first evaluation of the mode: kernels are assembled and tables uploaded on the way
+    g.evals++;
+    return enqueue(mode, obj_scale);
+  }
+  if (g.exec) {
+    cudaGraphExecDestroy(g.exec);
+    g.exec = nullptr;
+  }
+  cudaGraph_t graph = nullptr;
+  if (cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    g.failed = true;
+    return enqueue(mode, obj_scale);
+  }
+  const int rc = enqueue(mode, obj_scale);
+  const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+  if (rc != 0 || ce != cudaSuccess || !graph) {
+    cudaGetLastError();
+    if (graph) cudaGraphDestroy(graph);
+    g.failed = true;
+    return rc != 0 ? rc : enqueue(mode, obj_scale);
+  }
+  const cudaError_t ie = cudaGraphInstantiate(&g.exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ie != cudaSuccess) {
+    cudaGetLastError();
+    g.exec = nullptr;
+    g.failed = true;
+    return enqueue(mode, obj_scale);
+  }
+  g.obj_scale = obj_scale;
+  g.launches = launches;
+  g.jit_launches = jit_launches;
+  AB_CUDA(cudaGraphLaunch(g.exec, stream));
+  return 0;
+}
+
+int Plan::enqueue(int mode, double obj_scale) {
   int obj_mode = -1, con_mode = -1;
   bool out_kkt = false, out_pgx = false, out_agx = false, out_fx = false, out_val = false;
   switch (mode) {
@@ -816,6 +1095,10 @@ int Plan::eval(int mode, double obj_scale) {
     case EM_OCC: obj_mode = FM_VALUES; con_mode = FM_VALUES; out_fx = out_val = true; break;
     case EM_OBJ: obj_mode = FM_VALUES; out_val = true; break;
     default: last_error = "unknown eval mode"; return (int) cudaErrorInvalidValue;
+  }
+  if (windowed && mode != EM_KKT) {
+    last_error = "a windowed plan evaluates evalKKT only";
+    return (int) cudaErrorNotSupported;
   }
   launches = 0;
   jit_launches = 0;
@@ -833,15 +1116,20 @@ int Plan::eval(int mode, double obj_scale) {
   bool forked = false, forked2 = false, joined = false;
   // the forked streams are joined on every way out of this function: an error return between fork and join must not
   // leave side-stream work running beside the next evaluation
+  unsigned pool_used = 0;  // side_pool streams (beyond `side`) that carry work of this evaluation
+  int pool_next = 0;
   struct Joiner {
     Plan& P;
     bool &f1, &f2, &done;
+    unsigned& pool;
     ~Joiner() {
       if (done) return;
+      for (int i = 1; i < SIDE_POOL; i++)
+        if ((pool >> i & 1u) && cudaEventRecord(P.ev_pool[i], P.side_pool[i]) == cudaSuccess) cudaStreamWaitEvent(P.stream, P.ev_pool[i], 0);
       if (f1 && cudaEventRecord(P.ev_join, P.side) == cudaSuccess) cudaStreamWaitEvent(P.stream, P.ev_join, 0);
       if (f2 && cudaEventRecord(P.ev_join2, P.bulk2) == cudaSuccess) cudaStreamWaitEvent(P.stream, P.ev_join2, 0);
     }
-  } joiner{*this, forked, forked2, joined};
+  } joiner{*this, forked, forked2, joined, pool_used};
   // ASSET_B200_TIMELINE=1 (measurement): device time stamps on every stream of this evaluation, printed after a
   // synchronisation -- what ran beside what
   static const bool timeline = getenv("ASSET_B200_TIMELINE") != nullptr;
@@ -863,6 +1151,26 @@ int Plan::eval(int mode, double obj_scale) {
     }
     return side;
   };
+  // fused evaluation: the launches of the mesh ends are independent of each other and of the fused kernels (plan.hpp:
+  // kdF), so they are dealt round-robin over a pool of side streams instead of queueing up on one
+  auto pool_stream = [&]() -> cudaStream_t {
+    if (!overlap) return stream;
+    small_stream();  // forks `side` (= side_pool[0]) off the main stream on first use
+    const int i = pool_next++ % SIDE_POOL;
+    if (i != 0 && !(pool_used >> i & 1u)) {
+      cudaStreamWaitEvent(side_pool[i], ev_fork, 0);
+      pool_used |= 1u << i;
+    }
+    return side_pool[i];
+  };
+  // everything queued on the pool so far has finished when `side` gets here
+  auto pool_gather = [&]() {
+    for (int i = 1; i < SIDE_POOL; i++)
+      if (pool_used >> i & 1u) {
+        cudaEventRecord(ev_pool[i], side_pool[i]);
+        cudaStreamWaitEvent(side, ev_pool[i], 0);
+      }
+  };
   auto bulk_stream = [&](size_t k) -> cudaStream_t {
     if (!overlap || heavy_fn < 0 || (int) k == heavy_fn) return stream;
     if (!forked2) {
@@ -878,7 +1186,11 @@ int Plan::eval(int mode, double obj_scale) {
     if (fr < 0) return -fr;
     fused_eval = fr > 0;
   }
-  if (world > 1 && fused_eval != last_fused) {
+  if (windowed && !fused_eval) {
+    last_error = "a windowed plan needs the fused kernels: " + jit_log;
+    return (int) cudaErrorNotSupported;
+  }
+  if (world > 1 && !windowed && fused_eval != last_fused) {
     // The fused evaluation and the per-function evaluation split the outputs between the ranks along slightly different
     // lines; entries this rank wrote under the other split must read as zero again ("every output is non-zero on
     // exactly one rank").
@@ -897,7 +1209,10 @@ int Plan::eval(int mode, double obj_scale) {
     // applications this plan evaluates through the per-function kernels: its share of the function, except in the fused
     // evaluation of a sharded plan, where rank 0 alone runs what the fused kernels leave (the mesh ends)
     int fb = f.app_begin, fe = f.app_end;
-    if (fused_eval && world > 1) {
+    if (windowed) {  // the applications this rank owns (the fused kernels take most of them below)
+      fb = prob.win.own_lo[(size_t) prob.order[k]];
+      fe = prob.win.own_hi[(size_t) prob.order[k]];
+    } else if (fused_eval && world > 1) {
       if (rank != 0) continue;
       fb = 0;
       fe = prob.funcs[prob.order[k]].nappl;
@@ -936,19 +1251,24 @@ int Plan::eval(int mode, double obj_scale) {
       if (int rc = prof_begin(name + suffix)) return rc;
       const int jr = ensure_jit(k, fm, 1);
       if (jr < 0) return -jr;
-      // fused evaluation: the mesh ends and the fused edge segments may write the same entries, so they stay on one
-      // stream whatever their size (the edge segments follow them there)
-      cudaStream_t st = (e - b <= 4096 || fused_eval) ? small_stream() : stream;
+      cudaStream_t st = fused_eval ? pool_stream() : (e - b <= 4096) ? small_stream() : stream;
+      // fused evaluation: destinations inside the fused rows are redirected to the trash slot (plan.hpp: kdF); [b, e) lies
+      // in one of the two chunks of the redirected map
+      const int* kd = f.kkt_dest;
+      if (fused_eval && k < kdF.size() && kdF[k] && kdF_lo[k] >= 0)
+        kd = (b < kdF_lo[k]) ? kdF[k] : kdF[k] + ((long long) kdF_lo[k] - kdF_hi[k]) * f.E;
       if (jr > 0) {
         JitArgs a = ja;
         a.begin = b;
         a.end = e;
+        a.kkt_dest = kd;
         AB_CUDA(launch_jit(jits[1][k][fm], a, st));
         jit_launches++;
       } else {
         FnDev h = fd;
         h.app_begin = b;
         h.app_end = e;
+        h.kkt_dest = kd;
         AB_CUDA(launch_eval(h, st, io));
       }
       launches++;
@@ -988,7 +1308,7 @@ int Plan::eval(int mode, double obj_scale) {
   // (evaluated above on the side stream); they are launched after that stream has been joined, so that where both
   // write a value the fused result stands.  Everything between runs concurrently with the mesh ends.
   JitArgs fa;
-  long long f_b = 0, f_e = 0, f_blo = 0, f_bhi = 0;
+  long long f_b = 0, f_e = 0;
   // `spread`: the pieces write disjoint rows, so odd pieces go to the second bulk stream and run beside the even ones
   // (the piece holding the shared node leaves room for another block per SM)
   const bool spread_pieces = overlap && !getenv("ASSET_B200_NO_PIECE_OVERLAP");
@@ -1029,11 +1349,10 @@ int Plan::eval(int mode, double obj_scale) {
     fa.kkt_dest = (const int*) d_pgx;
     fa.f_dest = (const int*) d_agx;
     fa.obj_scale = obj_scale;
-    const long long R = fused.t_hi - fused.t_lo, EDGE = getenv("ASSET_B200_NO_EDGE_SPLIT") ? 0 : 64;
+    const long long R = fused.t_hi - fused.t_lo;
     f_b = R * rank / world;
     f_e = R * (rank + 1) / world;
-    f_blo = f_b < EDGE ? std::min(f_e, EDGE) : f_b;
-    f_bhi = f_e > R - EDGE ? std::max(f_blo, R - EDGE) : f_e;
+    if (windowed) f_b = win_f_b, f_e = win_f_e;
     if (overlap && !forked) {  // fork the side streams before the bulk is queued, or they would wait for it
       cudaEventRecord(ev_fork, stream);
       cudaStreamWaitEvent(side, ev_fork, 0);
@@ -1043,16 +1362,14 @@ int Plan::eval(int mode, double obj_scale) {
       cudaStreamWaitEvent(bulk2, ev_fork, 0);
       forked2 = true;
     }
-    mark("side: mesh ends done", small_stream());
-    if (int rc = fused_launch(f_blo, f_bhi, stream, true)) return rc;
-    mark("stream: bulk pieces done", stream);
-    if (forked2) mark("bulk2: bulk pieces done", bulk2);
-    // the edge segments follow the mesh ends on the side stream, beside the bulk
-    cudaStream_t es = small_stream();
-    if (int rc = fused_launch(f_b, f_blo, es)) return rc;
-    if (int rc = fused_launch(f_bhi, f_e, es)) return rc;
-    mark("side: edge segments done", es);
+    // the mesh ends write nothing a fused thread owns (redirected maps), so the pieces cover the whole range at once
+    if (int rc = fused_launch(f_b, f_e, stream, true)) return rc;
+    mark("stream: fused pieces done", stream);
+    if (forked2) mark("bulk2: fused pieces done", bulk2);
     if (int rc = prof_end()) return rc;
+    pool_gather();
+    cudaStream_t es = small_stream();
+    mark("side pool: mesh ends done", es);
     // targets that do not depend on the fused kernels are summed here, beside the bulk
     struct {
       DevGather* g;
@@ -1078,7 +1395,7 @@ int Plan::eval(int mode, double obj_scale) {
     AB_CUDA(cudaStreamWaitEvent(stream, ev_join2, 0));
   }
   if (fused_eval) {
-    if (world > 1 && rank == 0) {
+    if (world > 1 && rank == 0 && !windowed) {
       double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
       for (int a = 0; a < OA_COUNT; a++)
         if (clear_n[a] > 0) {
@@ -1099,7 +1416,7 @@ int Plan::eval(int mode, double obj_scale) {
   if (out_kkt && (rc = G(fused_eval ? gkF : gk, d_kkt, "gather:KKT"))) return rc;
   if (out_pgx && (rc = G(fused_eval ? gpF : gp, d_pgx, "gather:PGX"))) return rc;
   if (out_agx && (rc = G(fused_eval ? gaF : ga, d_agx, "gather:AGX"))) return rc;
-  const bool fsh = fused_eval && world > 1;
+  const bool fsh = fused_eval && (world > 1 || windowed);
   if (out_fx && ((rc = G(fsh ? geF : ge, d_fxe, "gather:FXE")) || (rc = G(fsh ? giF : gi, d_fxi, "gather:FXI")))) return rc;
   if (out_val && (rc = G(fsh ? gvF : gv, d_val, "gather:val"))) return rc;
   if (timeline) {

@@ -68,6 +68,18 @@ struct Plan {
   std::vector<JitKernel> fused_jits;  // one kernel per piece (row block)
   signed char fused_state = 0;  // 0 not tried, 1 ready, -1 unavailable
   DevGather gkF, gpF, gaF;      // gather lists without the targets the fused kernel writes
+  // Fused evaluation: destination maps of the applications the per-function kernels still evaluate (the mesh ends),
+  // with every CSR slot that a fused thread owns redirected to a trash slot of the staging buffer.  The fused kernels
+  // and the mesh ends then never write the same entry, so nothing orders them: the ends run beside the bulk on a pool
+  // of side streams and the fused kernels cover their whole segment range in one launch per piece.  Per function (in
+  // evaluation order): device array of the rows of applications [0, lo) followed by [hi, nappl); kdF_hi_off = rows in
+  // the first chunk.
+  std::vector<int*> kdF;
+  std::vector<int> kdF_lo, kdF_hi;
+  static constexpr int SIDE_POOL = 4;
+  cudaStream_t side_pool[SIDE_POOL] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_pool[SIDE_POOL] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_ends = nullptr;
   DevGather gkE, gpE, gaE;      // ... of which the low fan-in targets no fused kernel feeds: summed on the side stream
   DevGather geF, giF, gvF;      // sharded plans: this rank's share of the constraint-row / objective-value lists
   // cut set of the fused evaluation on a sharded plan: every gather target fed by the fused kernels' staged outputs
@@ -120,7 +132,24 @@ struct Plan {
   int last_mode = 0;
   int cut_pack();    // after eval(): partial sums of the cut set -> cut buffer (zeros where this rank has no sources)
   int cut_unpack();  // after the all-reduce: the owner keeps the sum, other contributors clear their partial
+  // windowed plans (Problem::window): this rank's share of one long phase, analysed locally
+  bool windowed = false;
+  long long win_f_b = 0, win_f_e = 0;  // fused threads of the owned segments, relative to t_lo
+  void window_filter(GatherList (*fl)[2], GatherList (*flE)[2], std::vector<int>* cut_t, int true_world);
   int eval(int mode, double obj_scale);
+  // eval() = enqueue() on the plan's streams, or -- from the second evaluation of a mode on, when every kernel it needs
+  // has been built -- the replay of a CUDA graph captured from one enqueue(): the ~25 dependent launches and the
+  // fork / join events of an evaluation then cost one graph launch on the host instead of one driver call each.
+  int enqueue(int mode, double obj_scale);
+  struct EvalGraph {
+    cudaGraphExec_t exec = nullptr;
+    double obj_scale = 0.0;
+    long long launches = 0, jit_launches = 0;
+    int evals = 0;      // eager evaluations of this mode so far
+    bool failed = false;
+  };
+  EvalGraph graphs[8];
+  bool use_graphs = true;
   int set_solver_coeffs(const double* host_coeffs);
 
   template<class T>

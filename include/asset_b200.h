@@ -127,6 +127,19 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_p
 long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long out[12], char* why, long long cap);
 /* PTX text of one piece of the fused evaluation (0 if there is none); buf == NULL only sizes. */
 long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap);
+/* Rank-local analysis of one long phase (replaces the whole-problem pass of NonLinearProgram::analyzeSparsity,
+ * /root/reference/src/Solvers/NonLinearProgram.cpp:267-344, by a pass over the rank's own segments).  Call between the
+ * transcription and ab_problem_analyze: keeps, of every function, the applications whose lowest mesh variable lies in
+ * segments [seg_lo - halo, seg_hi + halo) -- indices and dimensions stay those of the whole problem -- and marks those
+ * homed in [seg_lo, seg_hi) as owned.  Variables [0, mesh_vars) belong to mesh nodes, seg_vars of them per segment.
+ * A plan created from a windowed problem (ab_plan_create_sharded with the rank and world of the split) evaluates evalKKT
+ * for the owned applications only: the CSR rows of the owned segments come out complete, in the windowed problem's own
+ * pattern, whose rows inside the window are the whole problem's rows; entries that every rank contributes to (parameter
+ * rows, accumulated constraints, the objective value) go through the cut buffer as for any sharded plan. */
+int ab_problem_window(ab_problem* p, long long mesh_vars, int seg_vars, long long nseg, long long seg_lo, long long seg_hi, int halo);
+/* out = {application number in the whole problem of the first kept one, applications in the whole problem, first owned
+ * (kept numbering), one past the last owned} of function `fidx` */
+int ab_problem_window_info(const ab_problem* p, int fidx, int out[4]);
 int ab_plan_create(const ab_problem* p, int device, ab_plan** out);
 /* One rank's share of a problem split over `world` GPUs (the thread split of
  * SolverIndexingData::thread_split, src/VectorFunctions/IndexingData.h:117-146, across devices).  After ab_plan_eval:

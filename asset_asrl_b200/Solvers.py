@@ -66,6 +66,12 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_window_info(self.h, f, out))
         return dict(zip(["app_base", "nappl_whole", "own_lo", "own_hi"], list(out)))
 
+    def window_far_vars(self):
+        n = int(lib.ab_problem_window_far_vars(self.h, None, 0))
+        out = np.zeros(max(n, 1), dtype=np.int32)
+        lib.ab_problem_window_far_vars(self.h, out.ctypes.data_as(_lib._ip), n)
+        return out[:n]
+
     def analyze(self):
         _lib.check(lib.ab_problem_analyze(self.h))
         self._dims = None

@@ -106,6 +106,7 @@ SIGNATURES = {
     "ab_plan_device_ptr": (_vp, [_vp, _i]),
     "ab_problem_window": (_i, [_vp, _ll, _i, _ll, _ll, _ll, _i]),
     "ab_problem_window_info": (_i, [_vp, _i, _ip]),
+    "ab_problem_window_far_vars": (_i, [_vp, _ip, _i]),
     "ab_plan_stream": (_vp, [_vp]),
     "ab_plan_launches": (_ll, [_vp]),
     "ab_plan_specialised_launches": (_ll, [_vp]),

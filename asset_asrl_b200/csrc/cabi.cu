@@ -216,6 +216,12 @@ int ab_problem_window_info(const ab_problem* p, int fidx, int out[4]) {
   AB_CATCH
 }
 
+int ab_problem_window_far_vars(const ab_problem* p, int* out, int cap) {
+  const auto& v = p->p.win.far_mesh_vars;
+  for (size_t k = 0; k < v.size() && (int) k < cap; k++) out[k] = v[k];
+  return (int) v.size();
+}
+
 int ab_problem_analyze(ab_problem* p) {
   AB_TRY
   p->p.analyze();

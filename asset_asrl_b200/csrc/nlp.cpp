@@ -82,9 +82,20 @@ void Problem::window(long long mesh_vars, int seg_vars, long long nseg, long lon
     FuncRec& fn = funcs[f];
     win.nappl_whole[f] = fn.nappl;
     int keep_lo = -1, keep_hi = -1, own_lo = -1, own_hi = -1;
+    // inputs that are the same variable in every application do not place an application on the mesh
+    std::vector<char> fixed((size_t) fn.ir, 0);
+    if (fn.nappl > 1)
+      for (int i = 0; i < fn.ir; i++) {
+        fixed[(size_t) i] = 1;
+        const int v0 = fn.vindex[(size_t) i];
+        for (int a = 1; a < fn.nappl && fixed[(size_t) i]; a++)
+          if (fn.vindex[(size_t) a * fn.ir + i] != v0) fixed[(size_t) i] = 0;
+        if (fixed[(size_t) i] && v0 < mesh_vars) win.far_mesh_vars.push_back(v0);
+      }
     for (int a = 0; a < fn.nappl; a++) {
       long long vmin = -1;
       for (int i = 0; i < fn.ir; i++) {
+        if (fixed[(size_t) i]) continue;
         const long long v = fn.vindex[(size_t) a * fn.ir + i];
         if (v < mesh_vars && (vmin < 0 || v < vmin)) vmin = v;
       }
@@ -116,6 +127,8 @@ void Problem::window(long long mesh_vars, int seg_vars, long long nseg, long lon
                                         fn.appconst.begin() + (size_t) keep_hi * fn.nappconst);
     fn.nappl = n;
   }
+  std::sort(win.far_mesh_vars.begin(), win.far_mesh_vars.end());
+  win.far_mesh_vars.erase(std::unique(win.far_mesh_vars.begin(), win.far_mesh_vars.end()), win.far_mesh_vars.end());
 }
 
 void Problem::analyze() {

@@ -77,8 +77,10 @@ struct Problem {
   // lowest mesh variable they read -- lies within `halo` segments of the range, with all indices still global (variables,
   // constraint rows, dimensions), so that analyze() yields, for the rows of the window's interior, exactly the rows of
   // the whole problem's KKT pattern at a cost proportional to the window.  Applications homed inside [seg_lo, seg_hi)
-  // are *owned*: the rank evaluates those and nothing else.  Applications that read no mesh variable (parameter-only
-  // functions) are kept everywhere and owned by the last rank.
+  // are *owned*: the rank evaluates those and nothing else.  For a function with several applications the home is taken
+  // over the inputs that change from one application to the next (a mesh-spacing constraint reads the phase's first and
+  // last time in every application; its home is the node in between).  Applications that read no such variable
+  // (parameter-only functions) are kept everywhere and owned by the last rank.
   struct Window {
     bool on = false;
     long long mesh_vars = 0;  // variables [0, mesh_vars) belong to mesh nodes; the rest are parameters
@@ -89,7 +91,14 @@ struct Problem {
     std::vector<int> app_base;            // per function: application number (in the whole problem) of the first kept one
     std::vector<int> nappl_whole;         // per function: applications in the whole problem
     std::vector<int> own_lo, own_hi;      // per function: kept applications [own_lo, own_hi) are owned
-    // does this rank own mesh variable / far (parameter) variable v?
+    // Far variables: parameters and the mesh variables that every application of some function reads (the phase's first
+    // and last time in the mesh-spacing constraints): their gradient entries and the KKT entries among them collect
+    // contributions from every rank.
+    std::vector<int> far_mesh_vars;  // sorted
+    bool is_far(long long v) const {
+      return v >= mesh_vars || std::binary_search(far_mesh_vars.begin(), far_mesh_vars.end(), (int) v);
+    }
+    // does this rank own the rows of (ordinary) mesh variable v?
     bool owns_var(long long v) const {
       if (v >= mesh_vars) return false;
       const long long sg = std::min(v / seg_vars, nseg - 1);

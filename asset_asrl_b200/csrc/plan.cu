@@ -202,13 +202,26 @@ void Plan::window_filter(GatherList (*fl)[2], GatherList (*flE)[2], std::vector<
         for (long long r = win_f_b; r < win_f_e; r++) wr[(size_t) (w.base + r * w.stride)] = 1;
   const long long s0 = prob.stage_solver, s1 = prob.stage_solver + prob.n_solver;
   const int PV = prob.nvars, SV = prob.niq, EC = prob.neq;
-  // 0 not owned, 1 owned, 2 far
-  auto var_class = [&](long long v) { return v >= W.mesh_vars ? 2 : (W.owns_var(v) ? 1 : 0); };
-  auto row_class = [&](long long r) {
-    if (r < PV) return var_class(r);
-    if (r < PV + SV) return own_iq[(size_t) (r - PV)] ? 1 : 0;
-    if (r < PV + SV + EC) return own_eq[(size_t) (r - PV - SV)] ? 1 : 0;
-    return own_iq[(size_t) (r - PV - SV - EC)] ? 1 : 0;
+  // constraint rows that several applications add into (accumulations) belong to no rank
+  std::vector<unsigned char> acc_eq((size_t) std::max(prob.neq, 1), 0), acc_iq((size_t) std::max(prob.niq, 1), 0);
+  for (const FuncRec& fr: prob.funcs)
+    if (fr.role != 0 && !fr.unique_constraints)
+      for (int c: fr.cindex) (fr.role == 1 ? acc_eq : acc_iq)[(size_t) c] = 1;
+  // 0 not owned, 1 owned, 2 far (every rank contributes, summed through the cut buffer)
+  auto var_class = [&](long long v) { return W.is_far(v) ? 2 : (W.owns_var(v) ? 1 : 0); };
+  auto con_class = [&](long long r) {  // row / column index >= nvars: slack, equality or inequality row
+    const bool iq = r < PV + SV || r >= PV + SV + EC;
+    const long long c = r < PV + SV ? r - PV : (r < PV + SV + EC ? r - PV - SV : r - PV - SV - EC);
+    if ((iq ? acc_iq : acc_eq)[(size_t) c]) return 2;
+    return (iq ? own_iq : own_eq)[(size_t) c] ? 1 : 0;
+  };
+  // KKT entry (r, c), r <= c: the row of an ordinary mesh variable belongs to its segment's rank; in the row of a far
+  // variable an entry goes with its column -- another far variable: far; an ordinary variable or a constraint: that one's owner
+  auto entry_class = [&](long long r, long long c) {
+    if (r >= PV) return con_class(r);
+    if (!W.is_far(r)) return W.owns_var(r) ? 1 : 0;
+    if (c < PV) return var_class(c);
+    return con_class(c);
   };
   for (int a = 0; a < OA_COUNT; a++) {
     cut_t[a].clear();
@@ -220,9 +233,13 @@ void Plan::window_filter(GatherList (*fl)[2], GatherList (*flE)[2], std::vector<
         for (int t = 0; t < g.ntargets(); t++) {
           const long long tg = g.target[(size_t) t];
           int cls;
-          if (a == OA_KKT) cls = row_class((long long) (std::upper_bound(prob.indptr.begin(), prob.indptr.end(), (int) tg) - prob.indptr.begin()) - 1);
+          if (a == OA_KKT)
+            cls = entry_class((long long) (std::upper_bound(prob.indptr.begin(), prob.indptr.end(), (int) tg) - prob.indptr.begin()) - 1,
+                              prob.indices[(size_t) tg]);
           else if (a == OA_PGX || a == OA_AGX) cls = var_class(tg);
-          else cls = 2;  // accumulated constraint rows, the objective value
+          else if (a == OA_FXE || a == OA_FXI)  // accumulated rows are far; rows nobody in the window writes are not this rank's
+            cls = (a == OA_FXE ? acc_eq : acc_iq)[(size_t) tg] ? 2 : 0;
+          else cls = 2;  // the objective value
           if (cls == 0) continue;
           for (long long q = g.ptr[(size_t) t]; q < g.ptr[(size_t) t + 1]; q++) {
             const int sidx = g.src[(size_t) q];
@@ -553,7 +570,10 @@ int Plan::build(int dev, int rank_, int world_) {
       // fl: targets that must wait for the fused kernels (fed by their staged outputs) and every high fan-in target;
       // flE ("early"): low fan-in targets fed by the mesh ends and the solver coefficients alone -- most of what is
       // left, the pivot and slack rows -- which are summed on the side stream beside the bulk kernels
-      GatherList fl[OA_COUNT][2], flE[OA_COUNT][2];
+      // flS: KKT targets fed by solver coefficients alone (pivot, slack and diagonal entries outside the fused rows): they
+      // change only when the coefficients do, so set_solver_coeffs() writes them and an evaluation leaves them alone
+      GatherList fl[OA_COUNT][2], flE[OA_COUNT][2], flS[2];
+      for (int w = 0; w < 2; w++) flS[w].ptr.assign(1, 0);
       std::vector<int> cut_t[OA_COUNT];
       for (int a = 0; a < OA_COUNT; a++) {
         for (int w = 0; w < 2; w++) {
@@ -577,7 +597,12 @@ int Plan::build(int dev, int rank_, int world_) {
             bool fed = false;
             for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1]; k++) fed = fed || fslot[(size_t) g.src[(size_t) k]] != 0;
             const bool early = !fed && w == 0 && (a == OA_KKT || a == OA_PGX || a == OA_AGX);
-            GatherList& o = early ? flE[a][w] : fl[a][w];
+            bool sonly = early && a == OA_KKT && world == 1 && g.ptr[(size_t) t + 1] > g.ptr[t];
+            for (long long k = g.ptr[t]; k < g.ptr[(size_t) t + 1] && sonly; k++) {
+              const int sidx = g.src[(size_t) k];
+              if (sidx < prob.stage_solver || sidx >= prob.stage_solver + prob.n_solver) sonly = false;
+            }
+            GatherList& o = sonly ? flS[w] : early ? flE[a][w] : fl[a][w];
             // targets fed only by solver coefficients (pivot and slack rows: most of what is left) are spread over the
             // ranks by position; everything else that no fused kernel feeds belongs to rank 0, which runs the mesh ends
             bool solver_only = world > 1 && !fed && g.ptr[(size_t) t + 1] > g.ptr[t];
@@ -606,7 +631,36 @@ int Plan::build(int dev, int rank_, int world_) {
       }
       if (windowed) {
         try {
+          // the solver-only entries go through the same ownership rules
+          for (int w = 0; w < 2; w++) {
+            GatherList& e = flE[OA_KKT][w];
+            const GatherList& q = flS[w];
+            for (int t = 0; t < q.ntargets(); t++) {
+              e.src.insert(e.src.end(), q.src.begin() + q.ptr[(size_t) t], q.src.begin() + q.ptr[(size_t) t + 1]);
+              e.ptr.push_back((long long) e.src.size());
+              e.target.push_back(q.target[(size_t) t]);
+            }
+            flS[w] = GatherList();
+            flS[w].ptr.assign(1, 0);
+          }
           window_filter(fl, flE, cut_t, true_world);
+          // ... and come out again: owned entries fed by solver coefficients alone
+          for (int w = 0; w < 2; w++) {
+            GatherList keep;
+            keep.ptr.assign(1, 0);
+            GatherList& e = flE[OA_KKT][w];
+            const auto& cut = cut_t[OA_KKT];
+            for (int t = 0; t < e.ntargets(); t++) {
+              bool so = e.ptr[(size_t) t + 1] > e.ptr[(size_t) t] && !std::binary_search(cut.begin(), cut.end(), e.target[(size_t) t]);
+              for (long long k = e.ptr[(size_t) t]; k < e.ptr[(size_t) t + 1] && so; k++)
+                if (e.src[(size_t) k] < prob.stage_solver || e.src[(size_t) k] >= prob.stage_solver + prob.n_solver) so = false;
+              GatherList& o = so ? flS[w] : keep;
+              o.src.insert(o.src.end(), e.src.begin() + e.ptr[(size_t) t], e.src.begin() + e.ptr[(size_t) t + 1]);
+              o.ptr.push_back((long long) o.src.size());
+              o.target.push_back(e.target[(size_t) t]);
+            }
+            e = std::move(keep);
+          }
         } catch (const std::exception& ex) {
           last_error = ex.what();
           return (int) cudaErrorInvalidValue;
@@ -616,7 +670,8 @@ int Plan::build(int dev, int rank_, int world_) {
       for (const FuncRec& fr: prob.funcs) appc.insert(appc.end(), fr.appconst.begin(), fr.appconst.end());
       d_appc_all = dupload(appc);
       bool ok = d_appc_all && up_gather(*this, fl[OA_KKT], gkF) && up_gather(*this, fl[OA_PGX], gpF) && up_gather(*this, fl[OA_AGX], gaF)
-                && up_gather(*this, flE[OA_KKT], gkE) && up_gather(*this, flE[OA_PGX], gpE) && up_gather(*this, flE[OA_AGX], gaE);
+                && up_gather(*this, flE[OA_KKT], gkE) && up_gather(*this, flE[OA_PGX], gpE) && up_gather(*this, flE[OA_AGX], gaE)
+                && up_gather(*this, flS, gkS);
       if (ok && windowed) {
         ok = up_gather(*this, fl[OA_FXE], geF) && up_gather(*this, fl[OA_FXI], giF) && up_gather(*this, fl[OA_VAL], gvF);
         cutF_count = 0;
@@ -765,7 +820,7 @@ int Plan::build(int dev, int rank_, int world_) {
   }
   {
     size_t need = 1;
-    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF, &geF, &giF, &gvF, &gkE, &gpE, &gaE})
+    for (const DevGather* g: {&gk, &gp, &ga, &ge, &gi, &gv, &gkF, &gpF, &gaF, &geF, &giF, &gvF, &gkE, &gpE, &gaE, &gkS})
       need = std::max(need, (size_t) g->dev[1].ntargets * (size_t) g->dev[1].maxparts);
     d_gscratch = dalloc<double>(need);
     if (!d_gscratch) {
@@ -781,6 +836,7 @@ int Plan::set_solver_coeffs(const double* host) {
   AB_CUDA(cudaSetDevice(device));
   AB_CUDA(cudaMemcpyAsync(d_stage + prob.stage_solver, host, sizeof(double) * (size_t) prob.n_solver,
                           cudaMemcpyHostToDevice, stream));
+  solver_entries_valid = false;  // the next fused evaluation rewrites the entries that hold these coefficients alone
   AB_CUDA(cudaStreamSynchronize(stream));
   return 0;
 }
@@ -1032,6 +1088,11 @@ int Plan::eval(int mode, double obj_scale) {
   static const bool graphs_off = getenv("ASSET_B200_GRAPH") && std::atoi(getenv("ASSET_B200_GRAPH")) == 0;
   static const bool timeline_on = getenv("ASSET_B200_TIMELINE") != nullptr;
   const bool fused_now = mode == EM_KKT && fused.ok && fused_state >= 0;
+  if (fused_now && !solver_entries_valid && gkS.dev[0].ntargets + gkS.dev[1].ntargets > 0) {
+    // entries of the value array that hold solver coefficients alone (set_solver_coeffs): not part of an evaluation
+    AB_CUDA(launch_gather(gkS.dev[0], gkS.dev[1], d_stage, d_kkt, d_gscratch, stream));
+    solver_entries_valid = true;
+  }
   // a sharded plan zero-fills its outputs when the evaluation path changes: that call is not the one to capture or replay
   const bool transition = world > 1 && !windowed && fused_now != last_fused;
   if (!use_graphs || graphs_off || timeline_on || profiling || mode < 0 || mode >= 8 || transition) return enqueue(mode, obj_scale);
@@ -1108,6 +1169,7 @@ int Plan::enqueue(int mode, double obj_scale) {
     // partial matrix modes: entries this mode does not compute must read as zero
     AB_CUDA(cudaMemsetAsync(d_kkt, 0, sizeof(double) * (size_t) prob.nnz(), stream));
     AB_CUDA(cudaMemsetAsync(d_stage, 0, sizeof(double) * (size_t) prob.stage_solver, stream));
+    solver_entries_valid = false;
   }
   // Every function writes its own outputs (shared entries go through the staging buffer), so the launches are
   // independent: the bulk kernels run back to back on `stream`, the small ones (mesh ends, functions with a handful of
@@ -1148,6 +1210,7 @@ int Plan::enqueue(int mode, double obj_scale) {
       cudaEventRecord(ev_fork, stream);
       cudaStreamWaitEvent(side, ev_fork, 0);
       forked = true;
+      mark("side: released", side);
     }
     return side;
   };
@@ -1165,6 +1228,12 @@ int Plan::enqueue(int mode, double obj_scale) {
   };
   // everything queued on the pool so far has finished when `side` gets here
   auto pool_gather = [&]() {
+    if (timeline) {
+      static const char* const names[SIDE_POOL] = {"pool 0: its mesh ends done", "pool 1: its mesh ends done", "pool 2: its mesh ends done",
+                                                   "pool 3: its mesh ends done"};
+      for (int i = 0; i < SIDE_POOL; i++)
+        if (i == 0 ? forked : (pool_used >> i & 1u) != 0) mark(names[i], side_pool[i]);
+    }
     for (int i = 1; i < SIDE_POOL; i++)
       if (pool_used >> i & 1u) {
         cudaEventRecord(ev_pool[i], side_pool[i]);
@@ -1195,6 +1264,7 @@ int Plan::enqueue(int mode, double obj_scale) {
     // lines; entries this rank wrote under the other split must read as zero again ("every output is non-zero on
     // exactly one rank").
     AB_CUDA(cudaMemsetAsync(d_kkt, 0, sizeof(double) * (size_t) prob.nnz(), stream));
+    solver_entries_valid = false;
     AB_CUDA(cudaMemsetAsync(d_fxe, 0, sizeof(double) * (size_t) std::max(prob.neq, 1), stream));
     AB_CUDA(cudaMemsetAsync(d_fxi, 0, sizeof(double) * (size_t) std::max(prob.niq, 1), stream));
     AB_CUDA(cudaMemsetAsync(d_pgx, 0, sizeof(double) * (size_t) std::max(prob.nvars, 1), stream));

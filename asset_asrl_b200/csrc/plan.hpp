@@ -80,6 +80,8 @@ struct Plan {
   cudaStream_t side_pool[SIDE_POOL] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_pool[SIDE_POOL] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_ends = nullptr;
+  DevGather gkS;                // KKT entries that hold solver coefficients alone: written when those change, not per evaluation
+  bool solver_entries_valid = false;
   DevGather gkE, gpE, gaE;      // ... of which the low fan-in targets no fused kernel feeds: summed on the side stream
   DevGather geF, giF, gvF;      // sharded plans: this rank's share of the constraint-row / objective-value lists
   // cut set of the fused evaluation on a sharded plan: every gather target fed by the fused kernels' staged outputs

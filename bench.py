@@ -41,9 +41,11 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the (untimed) oracle-window comparison before the timed region")
-    ap.add_argument("--shard", default="one-phase", choices=["one-phase", "phases"],
-                    help="N > 1: one phase of N x segments split across the ranks with the NCCL cut-set reduce (default), "
-                         "or one independent phase per rank (no collective)")
+    ap.add_argument("--shard", default="windows", choices=["windows", "one-phase", "phases"],
+                    help="N > 1: one phase of N x segments split across the ranks -- 'windows' (default): every rank analyses "
+                         "only its own segments plus a halo (rank-local analysis, no cap on the total); 'one-phase': every "
+                         "rank analyses the whole problem and takes its share (capped by --max-total-segments); both sum "
+                         "the cut set over NCCL -- or 'phases': one independent phase per rank (no collective)")
     ap.add_argument("--max-total-segments", type=int, default=800000,
                     help="one-phase sharding: every rank analyses the whole problem on the host (about 45 KB and 0.1 ms "
                          "per segment), so the total is capped and segments per GPU shrink beyond the cap")
@@ -101,49 +103,70 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs
-def cpu_eval_rate(a, steps, warmup):
-    """Oracle (CPU port of the reference evaluation) on a bounded sample of the same workload, all host threads."""
+def cpu_eval_rate(a, steps, warmup, full_size=False):
+    """Oracle (CPU port of the reference evaluation) on a bounded sample of the same workload, all host threads: once
+    with the IEEE build used for parity and once built with the reference's own flags (-O2 -march=native -ffast-math,
+    CMakeLists.txt:55,:86,:160); the faster of the two is the reported value."""
     import asset_asrl_b200  # noqa: F401  (problem set-up runs through the product's host code; no GPU call is made)
     from asset_asrl_b200 import workloads as W
     import oracle
-    nseg = min(a.cpu_segments, a.segments)
+    nseg = a.segments if full_size else min(a.cpu_segments, a.segments)
     ph = W.make_phase(a.ode, a.mode, nseg, extras=not a.no_extras)
     nlp = ph.transcribe()
     X = ph.makeSolverInput()
     LE, LI = W.multipliers(nlp)
-    orc = oracle.Oracle.from_problem(nlp)
     threads = max(1, min(oracle.hardware_threads(), os.cpu_count() or 1))
-    times = []
-    for k in range(warmup + steps):
-        t0 = time.perf_counter()
-        orc.eval("KKT", 1.0, X, LE, LI, threads=threads)
-        dt = time.perf_counter() - t0
-        if k >= warmup:
-            times.append(dt)
-    t = float(np.mean(times))
+    rates = {}
+    for variant in ("ieee", "fast"):
+        try:
+            oracle.use_variant(variant)
+            orc = oracle.Oracle.from_problem(nlp)
+        except Exception as e:  # no compiler on the box: the IEEE copy travels prebuilt, the native one may be missing
+            rates[variant] = None
+            sys.stderr.write(f"bench.py: oracle variant {variant} unavailable: {e}\n")
+            continue
+        times = []
+        for k in range(warmup + steps):
+            t0 = time.perf_counter()
+            orc.eval("KKT", 1.0, X, LE, LI, threads=threads)
+            dt = time.perf_counter() - t0
+            if k >= warmup:
+                times.append(dt)
+        rates[variant] = float(np.mean(times))
+        del orc
+    oracle.use_variant("ieee")
+    t = min(v for v in rates.values() if v)
     return {"value": nseg / t, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"{nseg} segments of {workload_name(a)} per step, {steps} timed evalKKT calls, "
-                      f"{threads} threads over contiguous application chunks; oracle/oracle.cpp (reference binary unbuildable here)",
-            "ms_per_step": t * 1e3}
+                      f"{threads} threads over contiguous application chunks; oracle/oracle.cpp (reference binary unbuildable here); "
+                      "value = the faster of the two builds",
+            "segments_per_sec_ieee_build": nseg / rates["ieee"] if rates.get("ieee") else None,
+            "segments_per_sec_reference_flags_build": nseg / rates["fast"] if rates.get("fast") else None,
+            "segments": nseg, "ms_per_step": t * 1e3}
 
 
 def run_reference(a):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    steps, warmup = max(1, min(a.steps, 5)), max(1, min(a.warmup, 2))
-    cb = cpu_eval_rate(a, steps, warmup)
+    # the driver's step counts are honoured; the workload is the GPU arm's (same segment count) as long as a step stays
+    # within seconds on the host cores (200 k low-thrust LGL5 segments take about one second on 16 threads)
+    steps, warmup = max(1, a.steps), max(0, a.warmup)
+    full = a.segments <= 400000
+    cb = cpu_eval_rate(a, steps, warmup, full_size=full)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "segments_per_step": min(a.cpu_segments, a.segments), "eval": "evalKKT"},
-            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "config": {"workload": workload_name(a), "segments_per_gpu": cb["segments"], "segments_total": cb["segments"],
+                       "eval": "evalKKT", "same_segments_as_gpu_arm": full},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "segments_per_sec_ieee_build",
+                                                "segments_per_sec_reference_flags_build")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------------ parity leg
-def parity_check(nlp, ph, nseg_total, world, rank, X, LE, LI, sc, dist=None):
+def parity_check(nlp, ph, nseg_total, world, rank, X, LE, LI, sc, dist=None, windowed=False):
     """Not timed: one evalKKT of the bench problem against oracle windows (oracle/windows.py) of 128 segments at both
     mesh ends, the middle and every rank cut; the ranks' disjoint slices are summed over NCCL first.  Returns the worst
     relative difference (rank 0) -- the value evidence that travels with the throughput line."""
@@ -154,6 +177,34 @@ def parity_check(nlp, ph, nseg_total, world, rank, X, LE, LI, sc, dist=None):
     vs = pd["XtUVars"] * (pd["cardinalStates"] - 1)
     if pd["blocked"]:
         return None
+    if windowed:
+        # rank-local analysis: every rank checks the rows it owns on its side of its two cuts (or mesh ends) and in the
+        # middle of its range, in its own CSR pattern; nothing to sum, the worst difference is maximised over the ranks
+        lo, hi = nseg_total * rank // world, nseg_total * (rank + 1) // world
+        windows = [(lo * vs, min(lo + 64, hi) * vs), (max((lo + hi) // 2 - 32, lo) * vs, min((lo + hi) // 2 + 32, hi) * vs),
+                   (max(hi - 64, lo) * vs, hi * vs)]
+        wc = WindowCheck(nlp, windows)
+        nlp.set_inputs(X, LE, LI)
+        nlp.eval_device(EVAL_KKT, 0.7)
+        nlp.sync()
+        slices = {}
+        for k in ("KKT", "AGX", "PGX", "FXE", "FXI"):
+            idx = torch.from_numpy(wc.index[k]).cuda()
+            slices[k] = (nlp.device_tensor(k)[idx] if idx.numel() else torch.zeros(0, dtype=torch.float64, device="cuda")).cpu().numpy()
+        worst = wc.compare(slices, 0.7, X, LE, LI, sc)
+        keys = ("KKT", "AGX", "PGX", "FXE", "FXI")
+        t = torch.tensor([worst.get(k, 0.0) for k in keys], device="cuda", dtype=torch.float64)
+        rows = torch.tensor([float(worst["rows"]), float(worst["applications"])], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(rows)
+        if rank != 0:
+            return None
+        per = {k: float(v) for k, v in zip(keys, t.tolist())}
+        return {"max_rel": max(per.values()), "per_array": per, "windows": 3 * world, "rows": int(rows[0].item()),
+                "applications": int(rows[1].item()),
+                "how": "per rank: oracle windows of 64 segments on its side of both cuts (or mesh ends) and in the middle of its "
+                       "range, compared in the rank's own CSR pattern; maximum over the ranks; tolerance 1e-12 of the window's max-norm"}
     centres = [64, nseg_total // 2, nseg_total - 64] + [nseg_total * r // world for r in range(1, world)]
     windows = [(max(c - 64, 0) * vs, min(c + 64, nseg_total) * vs) for c in centres]
     wc = WindowCheck(nlp, windows)
@@ -198,8 +249,18 @@ def run_b200(a):
     from asset_asrl_b200.Solvers import EVAL_KKT
 
     t_setup = time.time()
-    sharded = world > 1 and a.shard == "one-phase"
-    if sharded:
+    sharded = world > 1 and a.shard in ("one-phase", "windows")
+    windows = world > 1 and a.shard == "windows"
+    requested_segments = a.segments
+    if windows:
+        # one phase of world x segments; every rank transcribes it, keeps its own segments plus a halo and analyses those
+        ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345)
+        nlp = ph.transcribe_window(rank, world)
+        d = nlp.dims()
+        X = ph.makeSolverInput()
+        LE, LI = W.multipliers(nlp, seed=67890)
+        nlp.to_device(local, rank=rank, world=world)
+    elif sharded:
         # one phase of world x segments; every rank builds the same problem and evaluates its share of every function
         cap = a.max_total_segments
         try:  # every rank holds the whole analysed problem on the host: stay well inside the box's memory
@@ -227,7 +288,7 @@ def run_b200(a):
     parity = None
     if not a.no_parity and (sharded or world == 1):
         parity = parity_check(nlp, ph, a.segments * (world if sharded else 1), world if sharded else 1, rank, X, LE, LI, sc,
-                              dist if world > 1 else None)
+                              dist if world > 1 else None, windows)
         if parity is not None and not parity["max_rel"] < 1e-12:
             raise SystemExit(f"bench.py: the CUDA path differs from the oracle: {parity}")
     stream = torch.cuda.ExternalStream(nlp.stream(), device=local)
@@ -294,7 +355,10 @@ def run_b200(a):
     except OSError:
         pass
     peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    b_alg_eval = W.algorithmic_bytes(nlp) // (world if sharded else 1)  # per GPU
+    if windows:  # per GPU: the rank's share of the inputs and outputs, its segments' CSR rows
+        b_alg_eval = 8 * ((3 * d["nvars"] + 2 * (d["neq"] + d["niq"])) // world + nlp.fused_info()["slots_per_segment"] * a.segments)
+    else:
+        b_alg_eval = W.algorithmic_bytes(nlp) // (world if sharded else 1)  # per GPU
     if dom == "defect":
         bytes_launch = b_seg_defect * a.segments
     else:  # another kernel dominates: charge it the whole evaluation's algorithmic bytes (upper bound on its share)
@@ -352,17 +416,22 @@ def run_b200(a):
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
         cb = cpu_eval_rate(a, 3, 1)
-        cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "segments_per_sec_ieee_build",
+                                  "segments_per_sec_reference_flags_build")}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak" if a.segments == requested_segments else "neither (segments per GPU were reduced to fit the host analysis)",
+                "segments_per_gpu_reduced": a.segments != requested_segments, "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": workload_name(a), "segments_per_gpu": a.segments, "segments_total": world * a.segments,
                            "eval": "evalKKT", "nvars": d["nvars"], "neq": d["neq"], "niq": d["niq"], "nnz": d["nnz"],
                            "kkt_evals_per_sec": 1e3 / ms_step,
-                           "sharding": ("one phase split into contiguous application ranges, NCCL all-reduce of the cut set ("
-                                        + str(int(_lib_cut_count(nlp))) + " doubles)") if sharded else
+                           "sharding": (("one phase, rank-local analysis (own segments + halo of 8), each rank fills the CSR rows of "
+                                         "its segments, NCCL all-reduce of the cut set (" if windows else
+                                         "one phase split into contiguous application ranges, every rank analyses the whole problem, "
+                                         "NCCL all-reduce of the cut set (") + str(int(_lib_cut_count(nlp))) + " doubles)") if sharded else
                                        ("one independent phase per rank, no collective" if world > 1 else "single GPU"),
                            "l2": f"no flush: per-eval working set {b_alg_eval / 1e6:.0f} MB of values (+ index maps) > 126 MB L2",
                            "setup_s": round(t_setup, 2)},

@@ -40,6 +40,34 @@ enum { AB_ROLE_OBJECTIVE = 0, AB_ROLE_EQUALITY = 1, AB_ROLE_INEQUALITY = 2, AB_R
 /* device pointers handed to a device-resident consumer */
 enum { AB_PTR_X = 0, AB_PTR_LE = 1, AB_PTR_LI = 2, AB_PTR_KKT = 3, AB_PTR_FXE = 4, AB_PTR_FXI = 5, AB_PTR_PGX = 6, AB_PTR_AGX = 7, AB_PTR_VAL = 8 };
 
+/* expression node kinds (ab_graph_node); children / dparams / iparams per kind as listed */
+enum {
+  AB_VK_ARGS = 0,        /* Arguments(ir): identity */
+  AB_VK_SEGMENT = 1,     /* child[start : start+size]        iparams = {start, size} */
+  AB_VK_ELEMENTS = 2,    /* child[iparams...] */
+  AB_VK_CONSTANT = 3,    /* constant vector dparams */
+  AB_VK_STACK = 4,       /* concatenated outputs of the children */
+  AB_VK_SUM = 5,         /* sum of the children */
+  AB_VK_DIFF = 6,        /* child0 - child1 */
+  AB_VK_SCALED = 7,      /* child0 * dparams[0] */
+  AB_VK_ROWSCALED = 8,   /* child0 .* dparams */
+  AB_VK_ADDVEC = 9,      /* child0 + dparams */
+  AB_VK_VECMINUS = 10,   /* dparams - child0 */
+  AB_VK_UNARY = 11,      /* cwise scalar op iparams[0] on child0 (dparams[0] = power for pow) */
+  AB_VK_NORM = 12,       /* |child0|^p, iparams = {p} */
+  AB_VK_NORMALIZED = 13, /* child0 / |child0|^p, iparams = {p} */
+  AB_VK_DOT = 14, AB_VK_CROSS = 15, AB_VK_CWISEPROD = 16, AB_VK_CWISEQUOT = 17,
+  AB_VK_VSPROD = 18,     /* vector child0 * scalar child1 */
+  AB_VK_VSDIV = 19, AB_VK_CWISESUM = 20, AB_VK_ATAN2 = 21,
+  AB_VK_NESTED = 22,     /* child0(child1(x)) */
+  AB_VK_IFELSE = 23, AB_VK_COMPARE = 24, AB_VK_BOOL = 25, AB_VK_IOSCALED = 26, AB_VK_APPCONST = 27, AB_VK_MATVEC = 28
+};
+/* PhaseRegionFlags and TranscriptionModes of the reference (src/OptimalControl/OptimalControlFlags.h) */
+enum { AB_REGION_FRONT = 1, AB_REGION_BACK = 2, AB_REGION_FRONTANDBACK = 3, AB_REGION_BACKANDFRONT = 4, AB_REGION_PATH = 5,
+       AB_REGION_INNERPATH = 6, AB_REGION_NODALPATH = 7, AB_REGION_PAIRWISEPATH = 9, AB_REGION_PARAMS = 12,
+       AB_REGION_ODEPARAMS = 13, AB_REGION_STATICPARAMS = 14 };
+enum { AB_TM_LGL3 = 0, AB_TM_LGL5 = 1, AB_TM_LGL7 = 2, AB_TM_TRAPEZOIDAL = 3 };
+
 const char* ab_last_error(void);
 int ab_version(void);
 int ab_device_count(void);
@@ -140,6 +168,9 @@ int ab_problem_window(ab_problem* p, long long mesh_vars, int seg_vars, long lon
 /* out = {application number in the whole problem of the first kept one, applications in the whole problem, first owned
  * (kept numbering), one past the last owned} of function `fidx` */
 int ab_problem_window_info(const ab_problem* p, int fidx, int out[4]);
+/* mesh variables that every application of some function reads (entries among them are summed over the ranks); returns
+ * their number and fills up to `cap` of them, ascending */
+int ab_problem_window_far_vars(const ab_problem* p, int* out, int cap);
 int ab_plan_create(const ab_problem* p, int device, ab_plan** out);
 /* One rank's share of a problem split over `world` GPUs (the thread split of
  * SolverIndexingData::thread_split, src/VectorFunctions/IndexingData.h:117-146, across devices).  After ab_plan_eval:

@@ -4,4 +4,4 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 the product (asset_asrl_b200/) never does.  See oracle/oracle.cpp for what is restated and how it is pinned
 ("parity unpinned" against the reference binary, which cannot be built in this image).
 """
-from .binding import Oracle, computeall, build, hardware_threads  # noqa: F401
+from .binding import Oracle, computeall, build, hardware_threads, use_variant  # noqa: F401

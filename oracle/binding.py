@@ -32,6 +32,35 @@ def build(force=False):
     return LIB_PATH
 
 
+def use_variant(name):
+    """Switch every Oracle created from now on to another build of oracle.cpp: "ieee" (default, the parity copy) or
+    "fast" (-O2 -march=native -ffast-math, the reference's flags; timing only, built on first use)."""
+    global _lib, LIB_PATH
+    if name == "fast":
+        path = os.path.join(_HERE, "_build", "liboracle_fast.so")
+        # -march=native: rebuild when the copy was made on another machine (built files travel with the repository)
+        stamp, cpu = os.path.join(_HERE, "_build", "fast.host"), ""
+        try:
+            with open("/proc/cpuinfo") as f:
+                cpu = next((ln for ln in f if ln.startswith("flags")), "")
+        except OSError:
+            pass
+        import hashlib
+        tag = hashlib.sha1(cpu.encode()).hexdigest()
+        if not os.path.exists(stamp) or open(stamp).read() != tag:
+            if os.path.exists(path):
+                os.remove(path)
+        subprocess.check_call(["make", "-C", _HERE, "-s", "fast"])
+        with open(stamp, "w") as f:
+            f.write(tag)
+    elif name == "ieee":
+        path = os.path.join(_HERE, "_build", "liboracle.so")
+    else:
+        raise ValueError(name)
+    LIB_PATH = path
+    _lib = None
+
+
 def lib():
     global _lib
     if _lib is None:

@@ -54,3 +54,34 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".hpp")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt and "liboracle" not in txt, f
+
+
+def _build_cpp_client():
+    import subprocess
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cabi_client")
+    root = os.path.dirname(os.path.dirname(here))
+    exe = os.path.join(here, "client")
+    subprocess.check_call(["/usr/bin/g++", "-std=c++17", "-O1", "-I" + os.path.join(root, "include"), os.path.join(here, "client.cpp"),
+                           "-o", exe, "-L" + os.path.join(root, "asset_asrl_b200"), "-l:libasset_b200.so",
+                           "-Wl,-rpath," + os.path.join(root, "asset_asrl_b200")])
+    return exe
+
+
+def test_cpp_client_of_the_header_builds_and_runs():
+    """A translation unit that includes only include/asset_b200.h (tests/cabi_client/client.cpp) compiles, links against
+    the shared library and drives graph -> phase -> problem -> pattern; on a box without a GPU plan creation must fail
+    with AB_ERR_NO_DEVICE (no CPU fallback)."""
+    import subprocess
+    exe = _build_cpp_client()
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    assert "cabi client ok" in out.stdout
+
+
+@pytest.mark.gpu
+def test_cpp_client_evaluates_on_the_device():
+    import subprocess
+    exe = _build_cpp_client()
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr
+    assert "cabi client ok (device)" in out.stdout, out.stdout

@@ -1,0 +1,46 @@
+"""Rank-local analysis on the host (Problem::window): ownership tiles the applications, and inside the rows a rank owns
+the windowed problem's CSR pattern is the whole problem's, column for column."""
+import numpy as np
+import pytest
+
+from asset_asrl_b200 import workloads as W
+
+
+@pytest.mark.parametrize("ode,mode,nseg,world", [("lowthrust", "LGL5", 400, 4), ("vanderpol", "LGL3", 300, 3),
+                                                 ("lowthrust", "LGL7", 200, 2), ("hypersens", "Trapezoidal", 500, 5)])
+def test_owned_rows_have_the_whole_problems_pattern(ode, mode, nseg, world):
+    ph = W.make_phase(ode, mode, nseg)
+    whole = ph.transcribe()
+    d = whole.dims()
+    gip, gix = whole.pattern()
+    pd = ph.dims()
+    vs = pd["XtUVars"] * (pd["cardinalStates"] - 1)
+    owned_apps = [np.zeros(whole.function_info(f)["nappl"], dtype=np.int32) for f in range(d["nfuncs"])]
+    for r in range(world):
+        nlp = ph.transcribe_window(r, world)
+        dl = nlp.dims()
+        assert (dl["nvars"], dl["neq"], dl["niq"], dl["kktdim"]) == (d["nvars"], d["neq"], d["niq"], d["kktdim"])
+        assert dl["n_user"] < 1.3 * d["n_user"] / world + 20 * d["n_user"] / nseg
+        lip, lix = nlp.pattern()
+        lo, hi = nseg * r // world, nseg * (r + 1) // world
+        v_hi = hi * vs if r < world - 1 else pd["numStates"] * pd["XtUVars"]
+        far = set(int(v) for v in nlp.window_far_vars())
+        for v in range(lo * vs, v_hi):
+            a0, a1, b0, b1 = int(gip[v]), int(gip[v + 1]), int(lip[v]), int(lip[v + 1])
+            if v in far:  # a row every rank adds entries to (its own applications' columns): a subset of the whole row
+                assert np.all(np.isin(lix[b0:b1], gix[a0:a1])), (r, v)
+                continue
+            assert a1 - a0 == b1 - b0 and np.array_equal(gix[a0:a1], lix[b0:b1]), (r, v)
+        for f in range(d["nfuncs"]):
+            wi = nlp.window_info(f)
+            assert wi["nappl_whole"] == owned_apps[f].size
+            owned_apps[f][wi["app_base"] + wi["own_lo"]:wi["app_base"] + wi["own_hi"]] += 1
+            # index maps of the kept applications are the whole problem's
+            Vw, Cw = whole.function_indices(f)
+            Vl, Cl = nlp.function_indices(f)
+            assert np.array_equal(Vl, Vw[wi["app_base"]:wi["app_base"] + Vl.shape[0]])
+            assert np.array_equal(Cl, Cw[wi["app_base"]:wi["app_base"] + Cl.shape[0]])
+        fi = nlp.fused_info()
+        assert fi["ok"] == 1, fi["why"]
+    for f, cnt in enumerate(owned_apps):
+        assert np.all(cnt == 1), (f, "every application is owned by exactly one rank")

@@ -51,6 +51,16 @@ struct FnDev {
   long long v_stage;       // objective value contributions go to stage[v_stage + app]
 };
 
+// cut set of a sharded plan, all output arrays (k_cut_all)
+struct CutAll {
+  double* arr[6];
+  const int* target[6];
+  const unsigned char* flag[6];
+  long long off[7];  // entries of array a sit at buf[off[a] .. off[a + 1])
+  int active[6];     // does the last evaluation's mode produce the array
+  double* buf;
+};
+
 struct EvalIO {
   const double* X;
   const double* L;   // LE or LI for constraints (indexed by cindex); unused for objectives

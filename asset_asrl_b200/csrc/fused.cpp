@@ -508,8 +508,53 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       if (mx > best_max) build_pieces(best);
     }
   };
+  // Greedy split by on-chip state: a piece takes as many whole rows as keep its parked values within `slot_limit`
+  // lane-private shared-memory slots (256 = 64 KB per 32-thread block, three blocks per SM), so that the number of
+  // pieces -- each re-reads the inputs and recomputes what it shares with its neighbours -- is the smallest the shared
+  // memory allows.  Sweeps s10 / s16: LGL5 low-thrust is fastest as two pieces although four would fit four blocks per
+  // SM; LGL7 wants its heavy first rows (the node shared with the previous segment) in pieces of their own.
+  auto slots_of = [&](long long r0, long long r1) {
+    std::vector<ProgOut> outs;
+    FusedPlan::Piece pc;
+    for (const Rec& r: recs) {
+      const bool in = r.row < 0 ? r1 == s : (r.row >= r0 && r.row < r1);
+      if (!in) continue;
+      pc.fout.push_back(r.where);
+      outs.push_back({r.node, PO_TABLE, (uint32_t) pc.fout.size() - 1});
+    }
+    pc.prog = emit_program_outs(fused, outs);
+    FusedPlan tmp;
+    tmp.fin = FP.fin;
+    tmp.t_lo = FP.t_lo;
+    tmp.t_hi = FP.t_hi;
+    tmp.pieces.push_back(std::move(pc));
+    JitStats st;
+    fused_ptx(tmp, 0, nullptr, &st);
+    return st.parked_slots;
+  };
+  auto by_slots = [&](int slot_limit) {
+    std::vector<long long> bnd {0};
+    while (bnd.back() < s) {
+      const long long r0 = bnd.back();
+      long long lo = r0 + 1, hi = s;  // the largest r1 in [lo, hi] that fits (lo always taken)
+      if (slots_of(r0, s) <= slot_limit) lo = s;
+      while (lo < hi) {
+        const long long mid = (lo + hi + 1) / 2;
+        if (slots_of(r0, mid) <= slot_limit) lo = mid;
+        else hi = mid - 1;
+      }
+      bnd.push_back(lo);
+      if (bnd.size() > 17) break;
+    }
+    if (bnd.back() != s) bnd.push_back(s);
+    return bnd;
+  };
   try {
-    if (npieces > 0) {
+    if (npieces == 0 && !getenv("ASSET_B200_FUSED_EVEN_SPLIT")) {
+      int limit = 256;
+      if (const char* e = getenv("ASSET_B200_FUSED_SLOTS")) limit = std::max(16, std::atoi(e));
+      build_pieces(by_slots(limit));
+    } else if (npieces > 0) {
       if (getenv("ASSET_B200_FUSED_BALANCE")) balance((int) std::min<long long>(npieces, s));
       else build_pieces(even((int) std::min<long long>(npieces, s)));
     } else {

@@ -324,6 +324,29 @@ cudaError_t launch_clear(double* arr, const int* idx, long long n, cudaStream_t 
   k_clear<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(arr, idx, n);
   return cudaGetLastError();
 }
+// all output arrays' cut entries in one launch (the cut set is a handful of doubles: one launch instead of one per array)
+__global__ void __launch_bounds__(256) k_cut_all(CutAll c, int pack) {
+  const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c.off[6]) return;
+  int a = 0;
+  while (i >= c.off[a + 1]) a++;
+  const long long q = i - c.off[a];
+  const unsigned char fl = c.flag[a][q];
+  double* arr = c.arr[a];
+  const int t = c.target[a][q];
+  if (pack) {
+    c.buf[i] = (c.active[a] && (fl & 1)) ? arr[t] : 0.0;
+  } else if (c.active[a]) {
+    if (fl & 2) arr[t] = c.buf[i];
+    else if (fl & 1) arr[t] = 0.0;
+  }
+}
+cudaError_t launch_cut_all(const CutAll& c, bool pack, cudaStream_t st) {
+  if (c.off[6] <= 0) return cudaSuccess;
+  k_cut_all<<<(unsigned) ((c.off[6] + 255) / 256), 256, 0, st>>>(c, pack ? 1 : 0);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_cut(bool pack, bool active, double* arr, const int* target, const unsigned char* flag, long long n,
                        double* buf, cudaStream_t st) {
   const unsigned blocks = (unsigned) ((n + 255) / 256);

@@ -1381,7 +1381,9 @@ int Plan::enqueue(int mode, double obj_scale) {
   long long f_b = 0, f_e = 0;
   // `spread`: the pieces write disjoint rows, so odd pieces go to the second bulk stream and run beside the even ones
   // (the piece holding the shared node leaves room for another block per SM)
-  const bool spread_pieces = overlap && !getenv("ASSET_B200_NO_PIECE_OVERLAP");
+  // (measured, sweep s10/s11: with the mesh ends on their own streams the pieces are faster back to back on one stream,
+  // 0.558 against 0.597 ms; ASSET_B200_PIECE_OVERLAP=1 brings the second stream back)
+  const bool spread_pieces = overlap && getenv("ASSET_B200_PIECE_OVERLAP") && !getenv("ASSET_B200_NO_PIECE_OVERLAP");
   auto fused_launch = [&](long long lo, long long hi, cudaStream_t st, bool spread = false) -> int {
     if (hi <= lo) return 0;
     fa.begin = (int) lo;
@@ -1535,41 +1537,37 @@ void Plan::finalize_out_ranges() {
   }
 }
 
+static CutAll make_cut_all(Plan& P) {
+  bool on[OA_COUNT];
+  mode_outputs(P.last_mode, on);
+  double* arrs[OA_COUNT] = {P.d_kkt, P.d_pgx, P.d_agx, P.d_fxe, P.d_fxi, P.d_val};
+  CutAll c;
+  c.off[0] = 0;
+  for (int a = 0; a < OA_COUNT; a++) {
+    const long long n = P.last_fused ? P.cutF_n[a] : (long long) P.part.cut_target[a].size();
+    c.arr[a] = arrs[a];
+    c.target[a] = P.last_fused ? P.d_cutF_target[a] : P.d_cut_target[a];
+    c.flag[a] = P.last_fused ? P.d_cutF_flag[a] : P.d_cut_flag[a];
+    c.active[a] = on[a] ? 1 : 0;
+    c.off[a + 1] = c.off[a] + n;
+  }
+  c.buf = P.d_cutbuf;
+  return c;
+}
+
 int Plan::cut_pack() {
   if (world <= 1 || active_cut_count() == 0) return 0;
   AB_CUDA(cudaSetDevice(device));
-  bool on[OA_COUNT];
-  mode_outputs(last_mode, on);
-  double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
-  long long off = 0;
-  for (int a = 0; a < OA_COUNT; a++) {
-    const long long n = last_fused ? cutF_n[a] : (long long) part.cut_target[a].size();
-    if (n > 0) {
-      AB_CUDA(launch_cut(true, on[a], arrs[a], last_fused ? d_cutF_target[a] : d_cut_target[a],
-                         last_fused ? d_cutF_flag[a] : d_cut_flag[a], n, d_cutbuf + off, stream));
-      launches++;
-    }
-    off += n;
-  }
+  AB_CUDA(launch_cut_all(make_cut_all(*this), true, stream));
+  launches++;
   return 0;
 }
 
 int Plan::cut_unpack() {
   if (world <= 1 || active_cut_count() == 0) return 0;
   AB_CUDA(cudaSetDevice(device));
-  bool on[OA_COUNT];
-  mode_outputs(last_mode, on);
-  double* arrs[OA_COUNT] = {d_kkt, d_pgx, d_agx, d_fxe, d_fxi, d_val};
-  long long off = 0;
-  for (int a = 0; a < OA_COUNT; a++) {
-    const long long n = last_fused ? cutF_n[a] : (long long) part.cut_target[a].size();
-    if (n > 0 && on[a]) {
-      AB_CUDA(launch_cut(false, true, arrs[a], last_fused ? d_cutF_target[a] : d_cut_target[a],
-                         last_fused ? d_cutF_flag[a] : d_cut_flag[a], n, d_cutbuf + off, stream));
-      launches++;
-    }
-    off += n;
-  }
+  AB_CUDA(launch_cut_all(make_cut_all(*this), false, stream));
+  launches++;
   return 0;
 }
 

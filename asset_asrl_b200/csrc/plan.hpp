@@ -164,6 +164,7 @@ struct Plan {
 AffineMaps function_affine(const Problem& prob, int fi);
 cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io);
 // pack: buf[i] = (active && mine) ? arr[target[i]] : 0;  unpack: owner: arr[target[i]] = buf[i], other contributors: 0
+cudaError_t launch_cut_all(const CutAll& c, bool pack, cudaStream_t st);
 cudaError_t launch_cut(bool pack, bool active, double* arr, const int* target, const unsigned char* flag, long long n,
                        double* buf, cudaStream_t st);
 cudaError_t launch_clear(double* arr, const int* idx, long long n, cudaStream_t st);  // arr[idx[i]] = 0

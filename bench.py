@@ -183,7 +183,8 @@ def parity_check(nlp, ph, nseg_total, world, rank, X, LE, LI, sc, dist=None, win
         lo, hi = nseg_total * rank // world, nseg_total * (rank + 1) // world
         windows = [(lo * vs, min(lo + 64, hi) * vs), (max((lo + hi) // 2 - 32, lo) * vs, min((lo + hi) // 2 + 32, hi) * vs),
                    (max(hi - 64, lo) * vs, hi * vs)]
-        wc = WindowCheck(nlp, windows)
+        wc = WindowCheck(nlp, windows, skip_vars=nlp.window_far_vars(),
+                         own_apps=lambda f: (nlp.window_info(f)["own_lo"], nlp.window_info(f)["own_hi"]))
         nlp.set_inputs(X, LE, LI)
         nlp.eval_device(EVAL_KKT, 0.7)
         nlp.sync()

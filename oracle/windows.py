@@ -20,7 +20,10 @@ ARRAYS = ("KKT", "AGX", "PGX", "FXE", "FXI")
 
 
 class WindowCheck:
-    def __init__(self, nlp, windows, pattern=None):
+    def __init__(self, nlp, windows, pattern=None, skip_vars=(), own_apps=None):
+        """``skip_vars``: variables whose rows are not compared (a windowed problem's far variables: every rank adds to
+        them).  ``own_apps(f) -> (lo, hi)``: applications of function f whose constraint rows this rank holds (a windowed
+        problem keeps applications of its neighbours too; their rows live on the neighbour)."""
         d = nlp.dims()
         self.windows = [(int(a), int(b)) for a, b in windows]
         self.orc = Oracle(d["nvars"], d["neq"], d["niq"])
@@ -41,9 +44,16 @@ class WindowCheck:
                                   ac[hit] if ac.size else None)
             self.applications += int(hit.sum())
             if fi["role"] and fi["unique_constraints"]:
-                rows[fi["role"]].append(Cc[hit].ravel().astype(np.int64))
+                mine = hit.copy()
+                if own_apps is not None:
+                    lo_a, hi_a = own_apps(f)
+                    mine[:lo_a] = False
+                    mine[hi_a:] = False
+                rows[fi["role"]].append(Cc[mine].ravel().astype(np.int64))
         self.orc.analyze()
         vrows = np.concatenate([np.arange(a, b, dtype=np.int64) for a, b in self.windows])
+        if len(skip_vars):
+            vrows = vrows[~np.isin(vrows, np.asarray(list(skip_vars), dtype=np.int64))]
         empty = np.zeros(0, dtype=np.int64)
         # the product's CSR rows of the window variables against the sub-problem's: same columns, bit for bit
         ip, ix = pattern if pattern is not None else nlp.pattern()

@@ -168,6 +168,15 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_fused_ptx(self.h, min_threads, piece, buf, n + 1))
         return buf.value.decode()
 
+    def fused_residual_ptx(self, mode, min_threads=32):
+        """PTX of the residual-only fused kernel of eval mode 4 (RHS), 5 (OGC), 6 (OCC) or 7 (OBJ); None if there is none."""
+        n = _lib.check(lib.ab_problem_fused_residual_ptx(self.h, min_threads, mode, None, 0))
+        if n == 0:
+            return None
+        buf = C.create_string_buffer(n + 1)
+        _lib.check(lib.ab_problem_fused_residual_ptx(self.h, min_threads, mode, buf, n + 1))
+        return buf.value.decode()
+
     def kernel_ptx(self, f, mode=4, indexed=False):
         """PTX of the specialised kernel for function ``f``: the affine variant (None if the function has no affine
         application range) or the indexed variant that reads explicit index maps."""
@@ -278,6 +287,13 @@ class NonLinearProgram:
         with torch.cuda.stream(self._tstream):
             dist.all_reduce(cut, op=dist.ReduceOp.SUM, group=self.group)
         _lib.check0(lib.ab_plan_cut_unpack(self.plan))
+
+    def check_guards(self):
+        """0 if no kernel wrote outside a device array of this plan (needs ASSET_B200_GUARD=1 when the plan was made)."""
+        rc = int(lib.ab_plan_check_guards(self.plan))
+        if rc != 0:
+            raise _lib.AssetB200Error(f"guard check {rc}: {_lib.last_error()}")
+        return 0
 
     def device_tensor(self, name):
         """Output / input array `name` (X, LE, LI, KKT, FXE, FXI, PGX, AGX, val) as a torch tensor aliasing the plan's

@@ -75,6 +75,7 @@ SIGNATURES = {
     "ab_phase_make_input": (_i, [_vp, _dp, _dp, _dp]),
     "ab_problem_fused_info": (_ll, [_vp, _i, _llp, _cp, _ll]),
     "ab_problem_fused_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
+    "ab_problem_fused_residual_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
     "ab_plan_create": (_i, [_vp, _i, C.POINTER(_vp)]),
     "ab_plan_destroy": (None, [_vp]),
     "ab_plan_create_sharded": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
@@ -104,6 +105,7 @@ SIGNATURES = {
     "ab_plan_profile_read": (_i, [_vp, C.POINTER(C.c_float), _i]),
     "ab_plan_profile_label": (_ll, [_vp, _i, _cp, _ll]),
     "ab_plan_device_ptr": (_vp, [_vp, _i]),
+    "ab_plan_check_guards": (_i, [_vp]),
     "ab_problem_window": (_i, [_vp, _ll, _i, _ll, _ll, _ll, _i]),
     "ab_problem_window_info": (_i, [_vp, _i, _ip]),
     "ab_problem_window_far_vars": (_i, [_vp, _ip, _i]),

@@ -579,6 +579,22 @@ long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long 
   }
 }
 
+long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, int mode, char* buf, long long cap) {
+  try {
+    if (mode < 4 || mode > 7) return fail(AB_ERR_INVALID, "residual-only modes are AB_EVAL_RHS .. AB_EVAL_OBJ");
+    FusedPlan fp = build_fused(p->p, min_threads);
+    if (!fp.ok || fp.residual[mode].empty()) return 0;
+    const std::string s = fused_ptx(fp, 0, nullptr, nullptr, 0, mode);
+    if (buf && cap > 0) {
+      const size_t n = std::min<size_t>(s.size(), (size_t) cap - 1);
+      std::memcpy(buf, s.data(), n);
+      buf[n] = 0;
+    }
+    return (long long) s.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
 long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap) {
   try {
     FusedPlan fp = build_fused(p->p, min_threads);
@@ -814,6 +830,11 @@ int ab_plan_eval_host(ab_plan* plan, int mode, double obj_scale, const double* X
   rc = ab_plan_eval(plan, mode, obj_scale);
   if (rc) return rc;
   return ab_plan_get_outputs(plan, val, pgx, agx, fxe, fxi, kkt);
+}
+int ab_plan_check_guards(ab_plan* plan) {
+  const int rc = plan->plan.check_guards();
+  if (rc != 0) fail(rc, plan->plan.last_error);
+  return rc;
 }
 void* ab_plan_device_ptr(ab_plan* plan, int which) {
   Plan& P = plan->plan;

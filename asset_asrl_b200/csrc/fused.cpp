@@ -348,6 +348,8 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
   struct Extra {
     JitOut where;
     int node;
+    int kind = 0;  // far_out: 0 matrix entry, 1 gradient entry, 2 objective value
+    int role = 1;
   };
   std::vector<Extra> fx_out, far_out;
   const long long SV = prob.niq;
@@ -392,9 +394,9 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       } else if (q.home && q.vst[row_in] == 0) {
         // row of a variable no segment owns (parameters, the phase's end times): as in the per-function kernels
         if (q.d0[e] >= 0)
-          far_out.push_back({{FA_KKT, q.d0[e] + dlo * q.dst[e], q.dst[e]}, node});
+          far_out.push_back({{FA_KKT, q.d0[e] + dlo * q.dst[e], q.dst[e]}, node, 0, fn.role});
         else
-          far_out.push_back({{FA_STAGE, ~q.d0[e] - dlo * q.dst[e], -q.dst[e]}, node});
+          far_out.push_back({{FA_STAGE, ~q.d0[e] - dlo * q.dst[e], -q.dst[e]}, node, 0, fn.role});
       }
     };
     int e = 0;
@@ -407,7 +409,7 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       if (owned_var(i)) {
         (fn.role == 0 ? pg : ag)[(size_t) (q.v0[i] - F.vbr)].push_back(g);
       } else if (q.home && q.vst[i] == 0) {
-        far_out.push_back({{FA_STAGE, prob.g_stage[q.fi] + (q.a_ref + q.m * dlo) * ir + i, (long long) q.m * ir}, g});
+        far_out.push_back({{FA_STAGE, prob.g_stage[q.fi] + (q.a_ref + q.m * dlo) * ir + i, (long long) q.m * ir}, g, 1, fn.role});
       }
     }
     if (q.home) {
@@ -415,7 +417,7 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       for (int k = 0; k < orr; k++) {
         const int v = cp(cf.outs[(size_t) k]);
         if (fn.role == 0)
-          far_out.push_back({{FA_STAGE, prob.v_stage[q.fi] + q.a_ref + q.m * dlo, q.m}, D.mul(v, input(FA_SCALE, 0, 0))});
+          far_out.push_back({{FA_STAGE, prob.v_stage[q.fi] + q.a_ref + q.m * dlo, q.m}, D.mul(v, input(FA_SCALE, 0, 0)), 2, 0});
         else
           fx_out.push_back({{fn.role == 1 ? FA_FXE : FA_FXI, q.c0[k] + dlo * q.cst[k], q.cst[k]}, v});
       }
@@ -573,13 +575,44 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
     FP.why = std::string("fused program: ") + ex.what();
     return FP;
   }
+  // residual-only programs (no matrix entries): one piece each
+  try {
+    for (int mode = 4; mode <= 7; mode++) {
+      const bool want_ag = mode == 4, want_pg = mode == 4 || mode == 5, want_fx = mode != 7;
+      FusedPlan::Piece pc;
+      std::vector<ProgOut> outs;
+      auto add = [&](const JitOut& where, int node) {
+        pc.fout.push_back(where);
+        outs.push_back({node, PO_TABLE, (uint32_t) pc.fout.size() - 1});
+      };
+      if (want_fx)
+        for (const Extra& x: fx_out) add(x.where, x.node);
+      if (want_ag)
+        for (long long j = 0; j < s; j++)
+          if (!ag[(size_t) j].empty()) add({FA_AGX, FP.vb + j, s}, sum(ag[(size_t) j]));
+      if (want_pg)
+        for (long long j = 0; j < s; j++)
+          if (!pg[(size_t) j].empty()) add({FA_PGX, FP.vb + j, s}, sum(pg[(size_t) j]));
+      for (const Extra& x: far_out) {
+        if (x.kind == 0) continue;
+        if (x.kind == 1 && !(x.role == 0 ? want_pg : want_ag)) continue;
+        add(x.where, x.node);
+      }
+      if (outs.empty()) continue;
+      pc.prog = emit_program_outs(fused, outs);
+      FP.residual[mode].push_back(std::move(pc));
+    }
+  } catch (const std::exception& ex) {
+    for (auto& r: FP.residual) r.clear();  // the per-function kernels evaluate these modes
+  }
   FP.ok = true;
   return FP;
 }
 
-std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats, int reg_budget) {
+std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats, int reg_budget, int mode) {
   JitSpec sp;
-  sp.name = "ab_fused_kkt" + std::to_string(piece);
+  const std::vector<FusedPlan::Piece>& pieces = mode == 0 ? fp.pieces : fp.residual[mode & 7];
+  sp.name = mode == 0 ? "ab_fused_kkt" + std::to_string(piece) : "ab_fused_m" + std::to_string(mode) + "_" + std::to_string(piece);
   sp.role = 1;  // multipliers and the objective scale are table entries, not the role's implicit operand
   sp.indexed = false;
   // One warp per block and every zero between stored values written (ncu, capture r2f): with the structural zeros left
@@ -593,7 +626,7 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   sp.direct_stores = true;
   if (const char* e = getenv("ASSET_B200_FUSED_DIRECT")) sp.direct_stores = std::atoi(e) != 0;
   sp.fin = &fp.fin;
-  sp.fout = &fp.pieces.at((size_t) piece).fout;
+  sp.fout = &pieces.at((size_t) piece).fout;
   jit_env_knobs(sp);
   // knobs of the fused kernels alone (sweeps)
   if (const char* e = getenv("ASSET_B200_FUSED_ZRUN")) sp.zero_run_min = std::max(1, std::atoi(e));
@@ -613,7 +646,7 @@ std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs,
   AffineMaps am;
   am.a0 = 0;
   am.a1 = fp.t_hi - fp.t_lo;
-  return emit_ptx(fp.pieces.at((size_t) piece).prog, sp, am, outs, stats);
+  return emit_ptx(pieces.at((size_t) piece).prog, sp, am, outs, stats);
 }
 
 }  // namespace ab

@@ -49,6 +49,10 @@ struct FusedPlan {
     std::vector<JitOut> fout;
   };
   std::vector<Piece> pieces;
+  // Residual-only evaluations of the same threads (the modes PSIOPT's line search calls once to three times per iterate,
+  // /root/reference/src/Solvers/PSIOPT.cpp:811-978): evalRHS (4: gradients, constraint values, objective value), evalOGC
+  // (5), evalOCC (6), evalOBJ (7) -- the same DAG, fewer outputs, one piece each; empty when the mode has no fused program.
+  std::vector<Piece> residual[8];
   std::vector<JitOut> fin;
   std::vector<long long> appc_offset;  // per function: offset of its per-application constants in the concatenated array
   int n_inst_home = 0;
@@ -60,6 +64,7 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces = 0 /* 0
 
 // PTX of one piece of the fused evaluation (entry "ab_fused_kkt<piece>"); fills the output table entries (emission order) and the statistics.
 // reg_budget > 0 overrides the default number of values kept in registers (the plan lowers it when the assembler spills)
-std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats, int reg_budget = 0);
+// mode: 0 (evalKKT, fp.pieces) or 4..7 (fp.residual[mode], entry "ab_fused_m<mode>_<piece>")
+std::string fused_ptx(const FusedPlan& fp, int piece, std::vector<JitOut>* outs, JitStats* stats, int reg_budget = 0, int mode = 0);
 
 }  // namespace ab

@@ -19,13 +19,55 @@ namespace ab {
     }                                                                        \
   } while (0)
 
+// ASSET_B200_GUARD=1 (checking aid; compute-sanitizer is not available on every pool): every device allocation of the
+// plan is wrapped in two guard bands of GUARD_BYTES filled with a byte pattern, and Plan::check_guards() reports the
+// first band a kernel wrote into.  Together with the comparison of every output with the oracle this covers what
+// memcheck would: a store outside an array lands in a band (or in another array's interior, where the oracle sees it).
+static constexpr size_t GUARD_BYTES = 1 << 16;
+static constexpr unsigned char GUARD_PATTERN = 0xA5;
 template<class T>
 T* Plan::dalloc(size_t n) {
+  static const bool guard = getenv("ASSET_B200_GUARD") != nullptr;
   void* p = nullptr;
   if (n == 0) n = 1;
-  if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+  if (!guard) {
+    if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+    owned.push_back(p);
+    return (T*) p;
+  }
+  const size_t bytes = (n * sizeof(T) + 255) / 256 * 256;
+  if (cudaMalloc(&p, bytes + 2 * GUARD_BYTES) != cudaSuccess) return nullptr;
   owned.push_back(p);
-  return (T*) p;
+  cudaMemset(p, GUARD_PATTERN, GUARD_BYTES);
+  cudaMemset((char*) p + GUARD_BYTES + n * sizeof(T), GUARD_PATTERN, bytes - n * sizeof(T) + GUARD_BYTES);
+  guards.push_back({(char*) p, (char*) p + GUARD_BYTES + n * sizeof(T), bytes - n * sizeof(T) + GUARD_BYTES});
+  return (T*) ((char*) p + GUARD_BYTES);
+}
+
+// 0: every guard band is intact; k > 0: the k-th allocation's band was written (message in last_error); < 0 CUDA error
+int Plan::check_guards() {
+  if (guards.empty()) {
+    last_error = "guard bands are off (set ASSET_B200_GUARD=1 before the plan is created)";
+    return -1;
+  }
+  cudaDeviceSynchronize();
+  std::vector<unsigned char> h;
+  for (size_t k = 0; k < guards.size(); k++) {
+    const Guard& g = guards[k];
+    for (int side = 0; side < 2; side++) {
+      const char* at = side ? g.hi : g.lo;
+      const size_t nb = side ? g.hi_bytes : GUARD_BYTES;
+      h.resize(nb);
+      if (cudaMemcpy(h.data(), at, nb, cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+      for (size_t b = 0; b < nb; b++)
+        if (h[b] != GUARD_PATTERN) {
+          last_error = "allocation " + std::to_string(k) + ": the guard band " + (side ? "after" : "before") + " it was written at byte offset "
+                       + std::to_string(side ? (long long) b : (long long) b - (long long) GUARD_BYTES);
+          return (int) k + 1;
+        }
+    }
+  }
+  return 0;
 }
 template<class T>
 T* Plan::dupload(const std::vector<T>& v) {
@@ -41,6 +83,8 @@ Plan::~Plan() {
     for (auto& a: v)
       for (JitKernel& k: a) unload_jit(k);
   for (JitKernel& k: fused_jits) unload_jit(k);
+  for (auto& v: fused_res_jits)
+    for (JitKernel& k: v) unload_jit(k);
   for (EvalGraph& g: graphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
   if (ev_fork) cudaEventDestroy(ev_fork);
@@ -878,19 +922,23 @@ std::mutex g_cubin_mu;
 std::unordered_map<std::string, CubinEntry> g_cubins;
 }  // namespace
 
-int Plan::ensure_fused() {
+int Plan::ensure_fused(int mode) {
+  // mode 0: the evalKKT pieces; 4..7: the residual-only program of that evaluation mode (fused.hpp)
+  signed char& fused_state = mode == 0 ? this->fused_state : fused_res_state[mode & 7];
+  std::vector<JitKernel>& fused_jits = mode == 0 ? this->fused_jits : fused_res_jits[mode & 7];
+  const std::vector<FusedPlan::Piece>& pieces = mode == 0 ? fused.pieces : fused.residual[mode & 7];
   if (fused_state != 0) return fused_state > 0 ? 1 : 0;
   fused_state = -1;
-  if (!fused.ok) return 0;
+  if (!fused.ok || pieces.empty()) return 0;
   int dev_smem = 0;
   cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
-  fused_jits.assign(fused.pieces.size(), JitKernel());
-  for (size_t pc = 0; pc < fused.pieces.size(); pc++) {
+  fused_jits.assign(pieces.size(), JitKernel());
+  for (size_t pc = 0; pc < pieces.size(); pc++) {
     std::string ptx;
     std::vector<JitOut> outs;
     JitStats js;
     try {
-      ptx = fused_ptx(fused, (int) pc, &outs, &js);
+      ptx = fused_ptx(fused, (int) pc, &outs, &js, 0, mode);
     } catch (const std::exception& e) {
       jit_log = std::string("fused kernel: ") + e.what();
       return 0;
@@ -898,7 +946,7 @@ int Plan::ensure_fused() {
     if ((int) js.smem_bytes > dev_smem) {
       // too many values alive for one block: cut the rows into more pieces and start over
       const int np = (int) fused.pieces.size() + 1;
-      if (np > 8 || np > fused.vs) {
+      if (mode != 0 || np > 8 || np > fused.vs) {
         jit_log = "fused kernel needs " + std::to_string(js.smem_bytes) + " B of shared memory per block";
         return 0;  // the per-function path evaluates everything
       }
@@ -906,7 +954,7 @@ int Plan::ensure_fused() {
       fused = build_fused(prob, jit_min_apps, np);
       if (!fused.ok) return 0;
       fused_state = 0;
-      return ensure_fused();
+      return ensure_fused(0);
     }
     CubinEntry ce;
     bool have = false;
@@ -933,7 +981,7 @@ int Plan::ensure_fused() {
         JitStats s2;
         budget -= 3;
         if (budget < 48) break;
-        const std::string p2 = fused_ptx(fused, (int) pc, nullptr, &s2, budget);
+        const std::string p2 = fused_ptx(fused, (int) pc, nullptr, &s2, budget, mode);
         if ((int) s2.smem_bytes > dev_smem) break;
         CubinEntry c2;
         if (!assemble_ptx(p2, c2.cubin, log, &c2.nregs, &c2.spill)) break;
@@ -947,7 +995,7 @@ int Plan::ensure_fused() {
     }
     JitKernel& jk = fused_jits[pc];
     jk.smem_bytes = ce.smem ? ce.smem : js.smem_bytes;
-    cudaError_t e = load_jit(ce.cubin, "ab_fused_kkt" + std::to_string(pc), jk);
+    cudaError_t e = load_jit(ce.cubin, mode == 0 ? "ab_fused_kkt" + std::to_string(pc) : "ab_fused_m" + std::to_string(mode) + "_" + std::to_string(pc), jk);
     if (e != cudaSuccess) {
       last_error = std::string("loading the fused kernel: ") + cudaGetErrorString(e);
       return -(int) e;
@@ -984,8 +1032,8 @@ int Plan::ensure_fused() {
     if (getenv("ASSET_B200_JIT_VERBOSE"))
       fprintf(stderr, "[asset_b200] ab_fused_kkt%zu of %zu: segments [%d, %d), %zu application families, %zu loads, %zu stored "
                       "outputs, %d FMA, %d regs, %d B assembler spill, %u B smem/block, %d parked slots, cubin %zu B\n",
-              pc, fused.pieces.size(), fused.t_lo, fused.t_hi, fused.insts.size(), fused.fin.size(), outs.size(),
-              fused.pieces[pc].prog.n_fma, ce.nregs, ce.spill, jk.smem_bytes, js.parked_slots, ce.cubin.size());
+              pc, pieces.size(), fused.t_lo, fused.t_hi, fused.insts.size(), fused.fin.size(), outs.size(),
+              pieces[pc].prog.n_fma, ce.nregs, ce.spill, jk.smem_bytes, js.parked_slots, ce.cubin.size());
   }
   fused_state = 1;
   return 1;
@@ -1103,7 +1151,7 @@ int Plan::eval(int mode, double obj_scale) {
     launches = g.launches;
     jit_launches = g.jit_launches;
     last_mode = mode;
-    last_fused = fused_now && fused_state > 0;
+    last_fused = g.fused;
     return 0;
   }
   if (g.evals < 1) {  // first evaluation of the mode: kernels are assembled and tables uploaded on the way
@@ -1137,6 +1185,7 @@ int Plan::eval(int mode, double obj_scale) {
     return enqueue(mode, obj_scale);
   }
   g.obj_scale = obj_scale;
+  g.fused = last_fused;
   g.launches = launches;
   g.jit_launches = jit_launches;
   AB_CUDA(cudaGraphLaunch(g.exec, stream));
@@ -1250,11 +1299,14 @@ int Plan::enqueue(int mode, double obj_scale) {
     return bulk2;
   };
   bool fused_eval = false;
-  if (mode == EM_KKT && fused.ok) {
-    const int fr = ensure_fused();
+  // the fused kernels evaluate evalKKT and -- single-device plans -- the residual-only modes of the line search
+  const bool residual_mode = mode >= EM_RHS && mode <= EM_OBJ && world == 1 && !windowed && !getenv("ASSET_B200_NO_FUSED_RESIDUAL");
+  if ((mode == EM_KKT || residual_mode) && fused.ok) {
+    const int fr = ensure_fused(mode == EM_KKT ? 0 : mode);
     if (fr < 0) return -fr;
     fused_eval = fr > 0;
   }
+  const std::vector<JitKernel>& fjits = mode == EM_KKT ? fused_jits : fused_res_jits[mode & 7];
   if (windowed && !fused_eval) {
     last_error = "a windowed plan needs the fused kernels: " + jit_log;
     return (int) cudaErrorNotSupported;
@@ -1388,8 +1440,8 @@ int Plan::enqueue(int mode, double obj_scale) {
     if (hi <= lo) return 0;
     fa.begin = (int) lo;
     fa.end = (int) hi;
-    for (size_t pc = 0; pc < fused_jits.size(); pc++) {
-      const JitKernel& jk = fused_jits[pc];
+    for (size_t pc = 0; pc < fjits.size(); pc++) {
+      const JitKernel& jk = fjits[pc];
       fa.out_base = jk.out_base;
       fa.out_stride = jk.out_stride;
       cudaStream_t use = st;
@@ -1430,7 +1482,7 @@ int Plan::enqueue(int mode, double obj_scale) {
       cudaStreamWaitEvent(side, ev_fork, 0);
       forked = true;
     }
-    if (spread_pieces && fused_jits.size() > 1 && !forked2) {
+    if (spread_pieces && fjits.size() > 1 && !forked2) {
       cudaStreamWaitEvent(bulk2, ev_fork, 0);
       forked2 = true;
     }

@@ -96,7 +96,9 @@ struct Plan {
   long long clear_n[OA_COUNT] = {0, 0, 0, 0, 0, 0};
   long long active_cut_count() const { return last_fused ? cutF_count : cut_count; }
   double* d_appc_all = nullptr; // per-application constants of all functions, concatenated (fused.appc_offset)
-  int ensure_fused();           // 1 ready, 0 unavailable, < 0 CUDA error (negated)
+  int ensure_fused(int mode = 0);  // 1 ready, 0 unavailable, < 0 CUDA error (negated); mode 0 evalKKT, 4..7 residual-only modes
+  std::vector<JitKernel> fused_res_jits[8];
+  signed char fused_res_state[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   bool last_fused = false;      // the last eval ran the fused kernel
 
   double *d_X = nullptr, *d_LE = nullptr, *d_LI = nullptr;
@@ -147,6 +149,7 @@ struct Plan {
     cudaGraphExec_t exec = nullptr;
     double obj_scale = 0.0;
     long long launches = 0, jit_launches = 0;
+    bool fused = false;
     int evals = 0;      // eager evaluations of this mode so far
     bool failed = false;
   };
@@ -156,6 +159,13 @@ struct Plan {
 
   template<class T>
   T* dalloc(size_t n);
+  struct Guard {
+    char* lo;
+    char* hi;
+    size_t hi_bytes;
+  };
+  std::vector<Guard> guards;  // ASSET_B200_GUARD=1: guard bands around every device allocation
+  int check_guards();
   template<class T>
   T* dupload(const std::vector<T>& v);
 };

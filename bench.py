@@ -38,6 +38,11 @@ def parse_args():
                     help="mesh segments per GPU (weak scaling: each rank owns a contiguous range of the phase)")
     ap.add_argument("--cpu-segments", type=int, default=20000, help="segments of the bounded CPU sample")
     ap.add_argument("--no-extras", action="store_true", help="defect constraints only (no bounds / integral objective)")
+    ap.add_argument("--control-mode", default=None, choices=["HighestOrderSpline", "FirstOrderSpline", "NoSpline", "BlockConstant"],
+                    help="control parameterisation of the phase (default: the reference's, FirstOrderSpline)")
+    ap.add_argument("--eval", default="KKT", choices=["KKT", "KKTNO", "SOE", "AUG", "RHS", "OGC", "OCC", "OBJ"],
+                    help="which NonLinearProgram::eval* entry point a step is (default evalKKT, the headline metric; the parity "
+                         "leg, the roofline bytes and e2e are evalKKT's and are skipped for the others)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the (untimed) oracle-window comparison before the timed region")
@@ -53,7 +58,8 @@ def parse_args():
 
 
 def workload_name(a):
-    return f"{a.ode}_{a.mode.lower()}" + ("_defect_only" if a.no_extras else "_example_functions")
+    return (f"{a.ode}_{a.mode.lower()}" + ("_defect_only" if a.no_extras else "_example_functions")
+            + (f"_{a.control_mode.lower()}" if getattr(a, "control_mode", None) else ""))
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -70,7 +76,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -86,7 +92,9 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
-        rows = [ln.split(",") for (t, ln) in self.lines if t0 - 0.05 <= t <= t1 + 0.15] or [ln.split(",") for (_, ln) in self.lines]
+        # the timed region is a few milliseconds: take the samples inside it, else those of the loaded half second around it
+        rows = ([ln.split(",") for (t, ln) in self.lines if t0 - 0.02 <= t <= t1 + 0.02]
+                or [ln.split(",") for (t, ln) in self.lines if t0 - 0.5 <= t <= t1 + 0.1] or [ln.split(",") for (_, ln) in self.lines])
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in rows:
@@ -111,7 +119,7 @@ def cpu_eval_rate(a, steps, warmup, full_size=False):
     from asset_asrl_b200 import workloads as W
     import oracle
     nseg = a.segments if full_size else min(a.cpu_segments, a.segments)
-    ph = W.make_phase(a.ode, a.mode, nseg, extras=not a.no_extras)
+    ph = W.make_phase(a.ode, a.mode, nseg, extras=not a.no_extras, control_mode=a.control_mode)
     nlp = ph.transcribe()
     X = ph.makeSolverInput()
     LE, LI = W.multipliers(nlp)
@@ -247,7 +255,10 @@ def run_b200(a):
 
     import asset_asrl_b200  # noqa: F401
     from asset_asrl_b200 import workloads as W
-    from asset_asrl_b200.Solvers import EVAL_KKT
+    from asset_asrl_b200 import Solvers as _S
+    EVAL_KKT = getattr(_S, "EVAL_" + a.eval)  # the step's entry point (evalKKT unless --eval says otherwise)
+    if a.eval != "KKT":
+        a.no_parity = a.no_e2e = True
 
     t_setup = time.time()
     sharded = world > 1 and a.shard in ("one-phase", "windows")
@@ -255,7 +266,7 @@ def run_b200(a):
     requested_segments = a.segments
     if windows:
         # one phase of world x segments; every rank transcribes it, keeps its own segments plus a halo and analyses those
-        ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345)
+        ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345, control_mode=a.control_mode)
         nlp = ph.transcribe_window(rank, world)
         d = nlp.dims()
         X = ph.makeSolverInput()
@@ -270,14 +281,14 @@ def run_b200(a):
         except ImportError:
             pass
         a.segments = max(1000, min(a.segments, cap // world))
-        ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345)
+        ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345, control_mode=a.control_mode)
         nlp = ph.transcribe()
         d = nlp.dims()
         X = ph.makeSolverInput()
         LE, LI = W.multipliers(nlp, seed=67890)
         nlp.to_device(local, rank=rank, world=world)
     else:
-        ph = W.make_phase(a.ode, a.mode, a.segments, extras=not a.no_extras, seed=12345 + rank)
+        ph = W.make_phase(a.ode, a.mode, a.segments, extras=not a.no_extras, seed=12345 + rank, control_mode=a.control_mode)
         nlp = ph.transcribe()
         d = nlp.dims()
         X = ph.makeSolverInput()
@@ -308,6 +319,12 @@ def run_b200(a):
     nlp.sync()
     clocks = ClockSampler(local)
     clocks.start()
+    for _ in range(60):  # keep the device busy until the sampler has delivered, so that its lines are taken under load
+        for _ in range(50):
+            nlp.eval_device(EVAL_KKT, 1.0)
+        nlp.sync()
+        if len(clocks.lines) >= 3:
+            break
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     w0 = time.time()
@@ -356,7 +373,12 @@ def run_b200(a):
     except OSError:
         pass
     peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-    if windows:  # per GPU: the rank's share of the inputs and outputs, its segments' CSR rows
+    if a.eval != "KKT":  # inputs once, the arrays the mode produces once
+        prod = {"KKTNO": (1, 0, 1, 1), "SOE": (1, 0, 0, 1), "AUG": (1, 1, 1, 1), "RHS": (0, 1, 1, 1), "OGC": (0, 1, 0, 1), "OCC": (0, 0, 0, 1),
+                "OBJ": (0, 0, 0, 0)}[a.eval]
+        b_alg_eval = 8 * (d["nvars"] + d["neq"] + d["niq"] + prod[0] * (d["nnz"] - W._solver_only_slots(nlp)) + (prod[1] + prod[2]) * d["nvars"]
+                          + prod[3] * (d["neq"] + d["niq"])) // (world if sharded else 1)
+    elif windows:  # per GPU: the rank's share of the inputs and outputs, its segments' CSR rows
         b_alg_eval = 8 * ((3 * d["nvars"] + 2 * (d["neq"] + d["niq"])) // world + nlp.fused_info()["slots_per_segment"] * a.segments)
     else:
         b_alg_eval = W.algorithmic_bytes(nlp) // (world if sharded else 1)  # per GPU
@@ -373,8 +395,22 @@ def run_b200(a):
             traffic = ent["dram_bytes_per_segment"] * a.segments
     except (OSError, ValueError, KeyError):
         pass
+    # fp64 pipe: DFMAs of the fused programs against the measured DFMA peak (tools/dfma_bench.cu) -- far from binding
+    fp64 = None
+    try:
+        pk = json.load(open(os.path.join(ROOT, "profiles", "fp64_peak.json")))["fp64_tflops"]
+        fi = nlp.fused_info()
+        if fi["ok"] and dom == "fused":
+            fl = 2.0 * fi["fma"] * (nlp.fused_segments() or a.segments)
+            fp64 = {"tflops": fl / (kernels[dom] * 1e-3) / 1e12, "peak_tflops": pk, "frac": fl / (kernels[dom] * 1e-3) / 1e12 / pk,
+                    "dfma_per_segment": fi["fma"]}
+    except (OSError, ValueError, KeyError):
+        pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "traffic": traffic, "traffic_source": "profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum per segment from the "
+                                                      "committed ncu --set full capture, scaled by the segment count (not re-measured in this run)"
+                if traffic else None,
+                "fp64": fp64, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "kernel_ms": kernels[dom], "kernel_share_of_step": kernels[dom] / ms_step,
                 "eval_algorithmic_bytes": b_alg_eval, "eval_frac": b_alg_eval / (ms_step * 1e-3) / 1e9 / peak}
 
@@ -427,7 +463,7 @@ def run_b200(a):
                 "segments_per_gpu_reduced": a.segments != requested_segments, "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": workload_name(a), "segments_per_gpu": a.segments, "segments_total": world * a.segments,
-                           "eval": "evalKKT", "nvars": d["nvars"], "neq": d["neq"], "niq": d["niq"], "nnz": d["nnz"],
+                           "eval": "eval" + a.eval, "nvars": d["nvars"], "neq": d["neq"], "niq": d["niq"], "nnz": d["nnz"],
                            "kkt_evals_per_sec": 1e3 / ms_step,
                            "sharding": (("one phase, rank-local analysis (own segments + halo of 8), each rank fills the CSR rows of "
                                          "its segments, NCCL all-reduce of the cut set (" if windows else

@@ -155,6 +155,9 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_p
 long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long out[12], char* why, long long cap);
 /* PTX text of one piece of the fused evaluation (0 if there is none); buf == NULL only sizes. */
 long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap);
+/* ... of the residual-only fused kernel of an evaluation mode (AB_EVAL_RHS, _OGC, _OCC, _OBJ: the evaluations of PSIOPT's
+ * line search, src/Solvers/PSIOPT.cpp:811-978); 0 if the mode has none. */
+long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, int mode, char* buf, long long cap);
 /* Rank-local analysis of one long phase (replaces the whole-problem pass of NonLinearProgram::analyzeSparsity,
  * /root/reference/src/Solvers/NonLinearProgram.cpp:267-344, by a pass over the rank's own segments).  Call between the
  * transcription and ab_problem_analyze: keeps, of every function, the applications whose lowest mesh variable lies in
@@ -216,6 +219,10 @@ int ab_plan_eval_host(ab_plan* plan, int mode, double obj_scale, const double* X
 int ab_plan_profile(ab_plan* plan, int enable); /* 0 off, 1 last eval only, 2 accumulate over evals */
 int ab_plan_profile_read(ab_plan* plan, float* ms, int cap);
 long long ab_plan_profile_label(ab_plan* plan, int k, char* buf, long long cap);
+/* Checking aid: with ASSET_B200_GUARD=1 in the environment when the plan is created, every device allocation sits between
+ * two guard bands; returns 0 if all are intact, k > 0 if the k-th allocation's band was written (ab_last_error says
+ * where), a negative status if guard bands are off. */
+int ab_plan_check_guards(ab_plan* plan);
 void* ab_plan_device_ptr(ab_plan* plan, int which);
 void* ab_plan_stream(ab_plan* plan);
 long long ab_plan_launches(const ab_plan* plan);

@@ -20,7 +20,7 @@ def stage_solver_offset(nlp):
     return best
 
 
-def emulate_fused(nlp, X, LE, LI, sc, obj_scale, rels):
+def emulate_fused(nlp, X, LE, LI, sc, obj_scale, rels, residual_mode=None):
     """Returns {array name: (values, written mask)} after running every fused piece for the threads in `rels`."""
     d = nlp.dims()
     info = nlp.fused_info()
@@ -35,8 +35,11 @@ def emulate_fused(nlp, X, LE, LI, sc, obj_scale, rels):
            "PGX": np.full(d["nvars"], nan), "AGX": np.full(d["nvars"], nan)}
     arrays = {0: np.asarray(X, dtype=np.float64), 1: np.asarray(LE, dtype=np.float64), 2: out["KKT"], 3: out["FXE"], 4: stage,
               5: appc, 6: np.asarray(LI, dtype=np.float64) if d["niq"] else np.zeros(1), 7: out["FXI"], 8: out["PGX"], 9: out["AGX"]}
-    for p in range(int(info["pieces"])):
-        k = Kernel(nlp.fused_ptx(p))
+    ptxs = [nlp.fused_ptx(p) for p in range(int(info["pieces"]))] if residual_mode is None else [nlp.fused_residual_ptx(residual_mode)]
+    for ptx in ptxs:
+        k = Kernel(ptx)
         for rel in rels:
             k.run(arrays, rel, obj_scale)
-    return {k: (v, ~np.isnan(v)) for k, v in out.items()}
+    res = {k: (v, ~np.isnan(v)) for k, v in out.items()}
+    res["stage"] = stage
+    return res

@@ -88,3 +88,35 @@ def test_fused_is_used_for_the_bench_workload_and_agrees_with_the_per_function_p
     assert nlp2.fused_segments() == 0
     for k in KEYS:
         assert rel_err(a[k], b[k]) < TOL, k
+
+
+@pytest.mark.parametrize("name", ["lowthrust_LGL5", "lowthrust_LGL7", "vanderpol_LGL3", "hypersens_LGL5", "brachistochrone_LGL3"])
+def test_fused_residual_only_modes(name):
+    """evalRHS / OGC / OCC / OBJ on the fused kernels (the evaluations of PSIOPT's line search), interleaved with evalKKT
+    and repeated so that the graph replay of every mode is exercised; val included."""
+    ph = CASES[name]()
+    nlp = ph.transcribe()
+    X = ph.makeSolverInput()
+    LE, LI, sc = problem_inputs(nlp)
+    nlp.to_device(0)
+    nlp.set_solver_coeffs(sc)
+    orc = oracle.Oracle.from_problem(nlp)
+    calls = {"RHS": (lambda x: nlp.evalRHS(0.7, x, LE, LI), ("PGX", "AGX", "FXE", "FXI", "val")),
+             "OGC": (lambda x: nlp.evalOGC(0.7, x), ("PGX", "FXE", "FXI", "val")),
+             "OCC": (lambda x: nlp.evalOCC(0.7, x), ("FXE", "FXI", "val")),
+             "OBJ": (lambda x: nlp.evalOBJ(0.7, x), ("val",)),
+             "KKT": (lambda x: nlp.evalKKT(0.7, x, LE, LI), KEYS + ("val",))}
+    rng = np.random.default_rng(11)
+    for rep in range(3):
+        Xr = X + 1e-3 * rep * rng.uniform(-1, 1, X.size)
+        for mode in ("RHS", "KKT", "OCC", "OGC", "OBJ", "RHS"):
+            fn, keys = calls[mode]
+            out = fn(Xr)
+            ref = orc.eval(mode, 0.7, Xr, LE, LI, sc)
+            for k in keys:
+                if k == "val":
+                    assert abs(out["val"] - ref["val"]) <= TOL * max(abs(ref["val"]), 1.0), (name, mode, rep, "val")
+                else:
+                    assert rel_err(out[k], ref[k]) < TOL, (name, mode, rep, k, rel_err(out[k], ref[k]))
+            if mode != "KKT" and nlp.fused_info()["ok"]:
+                assert nlp.fused_segments() > 0, (name, mode, "the residual-only mode did not run on the fused kernels")

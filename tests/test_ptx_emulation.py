@@ -41,6 +41,7 @@ def test_fused_ptx_on_the_emulator_matches_the_oracle(name):
     R = info["t_hi"] - info["t_lo"]
     res = emulate_fused(nlp, X, LE, LI, sc, 0.7, [0, 1, 2, 3, R // 2, R - 1])  # every store phase (rel mod 4) and both ends
     wrote = 0
+    res.pop("stage")
     for k, (v, m) in res.items():
         if not m.any():
             continue
@@ -48,6 +49,35 @@ def test_fused_ptx_on_the_emulator_matches_the_oracle(name):
         scale = max(float(np.abs(ref[k]).max()), 1e-300)
         assert float(np.abs(v[m] - ref[k][m]).max()) <= 1e-12 * scale, (name, k)
     assert wrote >= 6 * info["slots_per_segment"]
+
+
+@pytest.mark.parametrize("mode,name", [(4, "RHS"), (5, "OGC"), (6, "OCC"), (7, "OBJ")])
+@pytest.mark.parametrize("case", ["lowthrust_LGL5", "vanderpol_LGL5", "lowthrust_LGL7_highest_order_spline"])
+def test_residual_only_fused_ptx_matches_the_oracle(case, mode, name):
+    """The fused kernels of the line-search evaluations (evalRHS / OGC / OCC / OBJ): what a thread writes -- constraint
+    values, gradient entries of its rows -- against the oracle in that mode; no matrix entry may be written."""
+    ph = CASES[case]()
+    nlp = ph.transcribe()
+    X = ph.makeSolverInput()
+    LE, LI, sc = problem_inputs(nlp)
+    info = nlp.fused_info()
+    ptx = nlp.fused_residual_ptx(mode)
+    assert ptx is not None and ("ab_fused_m%d_0" % mode) in ptx
+    assert nlp.assemble_ptx(ptx)["cubin_bytes"] > 0
+    ref = oracle.Oracle.from_problem(nlp).eval(name, 0.7, X, LE, LI, sc)
+    R = info["t_hi"] - info["t_lo"]
+    res = emulate_fused(nlp, X, LE, LI, sc, 0.7, [0, 1, 2, 3, R // 2, R - 1], residual_mode=mode)
+    res.pop("stage")
+    assert not res["KKT"][1].any()
+    expect = {"RHS": ("FXE", "FXI", "AGX", "PGX"), "OGC": ("FXE", "FXI", "PGX"), "OCC": ("FXE", "FXI"), "OBJ": ()}[name]
+    for k, (v, m) in res.items():
+        if k == "KKT":
+            continue
+        assert m.any() == (k in expect and ref[k].size > 0 and (k != "PGX" or np.abs(ref[k]).max() > 0) or (k in expect and m.any())), (case, name, k)
+        if m.any():
+            assert k in expect, (case, name, k, "an array this mode does not produce was written")
+            scale = max(float(np.abs(ref[k]).max()), 1e-300)
+            assert float(np.abs(v[m] - ref[k][m]).max()) <= 1e-12 * scale, (case, name, k)
 
 
 @pytest.mark.skipif(shutil.which("ptxas") is None or shutil.which("cuobjdump") is None, reason="needs the CUDA toolkit's ptxas and cuobjdump")

@@ -168,27 +168,52 @@ void Problem::analyze() {
 
   auto conoff = [&](const FuncRec& fn) { return fn.role == 1 ? eqoffset : (fn.role == 2 ? iqoffset : 0); };
   // solver-owned entries in the reference's storage order (NonLinearProgram.cpp:198-265)
+  // A windowed problem (Problem::window) keeps the whole problem's dimensions and the numbering of the solver's
+  // coefficients, but creates matrix entries only in the rows its applications touch: everything here then costs in
+  // proportion to the window, not to the phase (a 1.6 M-segment phase has 1.3e8 solver-owned entries).
+  std::vector<unsigned char> keep_v, keep_e, keep_i;
+  if (win.on) {
+    keep_v.assign((size_t) std::max(PV, 1), 0);
+    keep_e.assign((size_t) std::max(EC, 1), 0);
+    keep_i.assign((size_t) std::max(IC, 1), 0);
+    for (const FuncRec& fn: funcs) {
+      for (int v: fn.vindex) keep_v[(size_t) v] = 1;
+      if (fn.role != 0)
+        for (int c: fn.cindex) (fn.role == 1 ? keep_e : keep_i)[(size_t) c] = 1;
+    }
+  }
+  auto keep_var = [&](int i) { return !win.on || keep_v[(size_t) i]; };
+  auto keep_eq = [&](int i) { return !win.on || keep_e[(size_t) i]; };
+  auto keep_iq = [&](int i) { return !win.on || keep_i[(size_t) i]; };
+  // cb(row, col, kept): entries that are not kept still count in the numbering of the solver's coefficients
   auto for_each_solver = [&](auto&& cb) {
-    for (int i = 0; i < SV; i++) cb(PV + SV + EC + i, PV + i);  // slack Jacobian ones
-    for (int i = 0; i < PV; i++) cb(i, i);                      // primal diagonal
-    for (int i = 0; i < SV; i++) cb(PV + i, PV + i);            // slack diagonal
-    for (int i = 0; i < EC; i++) cb(PV + SV + i, PV + SV + i);  // equality pivots
-    for (int i = 0; i < IC; i++) cb(PV + SV + EC + i, PV + SV + EC + i);
+    for (int i = 0; i < SV; i++) cb(PV + SV + EC + i, PV + i, keep_iq(i));  // slack Jacobian ones
+    for (int i = 0; i < PV; i++) cb(i, i, keep_var(i));                      // primal diagonal
+    for (int i = 0; i < SV; i++) cb(PV + i, PV + i, keep_iq(i));            // slack diagonal
+    for (int i = 0; i < EC; i++) cb(PV + SV + i, PV + SV + i, keep_eq(i));  // equality pivots
+    for (int i = 0; i < IC; i++) cb(PV + SV + EC + i, PV + SV + EC + i, keep_iq(i));
   };
 
   // pass 1: count per CSR row (upper triangle: row = min, col = max)
   std::vector<long long> rowstart((size_t) kktdim + 1, 0);
   auto count_cb = [&](int r, int c) { rowstart[(size_t) std::min(r, c) + 1]++; };
   for (int fi: order) for_each_triplet(funcs[fi], conoff(funcs[fi]), count_cb);
-  for_each_solver(count_cb);
+  long long n_solver_kept = 0;
+  for_each_solver([&](int r, int c, bool kept) {
+    if (!kept) return;
+    count_cb(r, c);
+    n_solver_kept++;
+  });
   for (int i = 0; i < kktdim; i++) rowstart[(size_t) i + 1] += rowstart[i];
   // pass 2: bucket the columns
-  std::vector<int> colbuf((size_t) T);
+  std::vector<int> colbuf((size_t) (n_user + n_solver_kept));
   {
     std::vector<long long> pos(rowstart.begin(), rowstart.end() - 1);
     auto fill_cb = [&](int r, int c) { colbuf[(size_t) pos[std::min(r, c)]++] = std::max(r, c); };
     for (int fi: order) for_each_triplet(funcs[fi], conoff(funcs[fi]), fill_cb);
-    for_each_solver(fill_cb);
+    for_each_solver([&](int r, int c, bool kept) {
+      if (kept) fill_cb(r, c);
+    });
   }
   // pass 3: sort + unique per row (parallel over rows)
   std::vector<int> rowcnt(kktdim, 0);
@@ -230,7 +255,10 @@ void Problem::analyze() {
       kktloc[(size_t) k++] = (int) (std::lower_bound(b, e, cc) - indices.data());
     };
     for (int fi: order) for_each_triplet(funcs[fi], conoff(funcs[fi]), loc_cb);
-    for_each_solver(loc_cb);
+    for_each_solver([&](int r, int c, bool kept) {
+      if (kept) loc_cb(r, c);
+      else kktloc[(size_t) k++] = -1;  // no entry in this window's pattern
+    });
   }
 
   // pass 5: classify slots.  A slot written by exactly one user triplet and no solver entry is stored
@@ -238,6 +266,7 @@ void Problem::analyze() {
   const int nnz_i = (int) nnz_ll;
   std::vector<unsigned char> nsrc((size_t) nnz_i, 0);  // saturating count
   for (long long k = 0; k < T; k++) {
+    if (kktloc[(size_t) k] < 0) continue;
     unsigned char& c = nsrc[(size_t) kktloc[(size_t) k]];
     if (k >= n_user)
       c = 2;
@@ -260,9 +289,11 @@ void Problem::analyze() {
   }
   stage_solver = stage_pos;
   for (long long k = 0; k < n_solver; k++) {
-    tgt_of_src.push_back(kktloc[(size_t) (n_user + k)]);
-    stage_of_src.push_back((int) stage_pos);
-    stage_pos++;
+    if (kktloc[(size_t) (n_user + k)] >= 0) {
+      tgt_of_src.push_back(kktloc[(size_t) (n_user + k)]);
+      stage_of_src.push_back((int) stage_pos);
+    }
+    stage_pos++;  // the coefficient keeps its slot whether or not this window has an entry for it
   }
   {
     std::vector<char> keep((size_t) nnz_i);

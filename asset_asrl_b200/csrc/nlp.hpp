@@ -69,7 +69,8 @@ struct Problem {
   bool analyzed = false;
 
   void analyze();
-  long long nnz() const { return (long long) indices.size(); }
+  long long nnz_kept = -1;  // set when the pattern arrays have been released (Plan::release_host_analysis)
+  long long nnz() const { return nnz_kept >= 0 ? nnz_kept : (long long) indices.size(); }
 
   // ---- window of a single-phase problem (rank-local analysis, SURVEY.md section 8e / NonLinearProgram.cpp:267-344) ----
   // A rank that evaluates mesh segments [seg_lo, seg_hi) of one long phase needs the structure of those segments and of a

@@ -344,6 +344,28 @@ void Plan::window_filter(GatherList (*fl)[2], GatherList (*flE)[2], std::vector<
   }
 }
 
+void Plan::release_host_analysis() {
+  prob.nnz_kept = prob.nnz();
+  auto drop = [](auto& v) {
+    typename std::remove_reference<decltype(v)>::type().swap(v);
+  };
+  drop(prob.indices);
+  drop(prob.kktloc);
+  drop(prob.kkt_dest);
+  drop(prob.f_dest);
+  for (GatherList* g: {prob.g_kkt, prob.g_pgx, prob.g_agx, prob.g_fxe, prob.g_fxi, prob.g_val})
+    for (int w = 0; w < 2; w++) {
+      drop(g[w].ptr);
+      drop(g[w].src);
+      drop(g[w].target);
+    }
+  for (FuncRec& fr: prob.funcs) {
+    drop(fr.vindex);
+    drop(fr.cindex);
+    drop(fr.appconst);
+  }
+}
+
 int Plan::build(int dev, int rank_, int world_) {
   if (!prob.analyzed) prob.analyze();
   device = dev;
@@ -849,6 +871,7 @@ int Plan::build(int dev, int rank_, int world_) {
       return (int) cudaErrorMemoryAllocation;
     }
     finalize_out_ranges();
+    release_windowed = true;
   } else if (world > 1) {
     d_cutbuf = dalloc<double>((size_t) std::max<long long>(std::max(cut_count, cutF_count), 1));
     if (!d_cutbuf) {
@@ -871,6 +894,17 @@ int Plan::build(int dev, int rank_, int world_) {
       last_error = "out of device memory for the gather scratch";
       return (int) cudaErrorMemoryAllocation;
     }
+  }
+  if (release_windowed && !getenv("ASSET_B200_KEEP_HOST_ANALYSIS")) {
+    // assemble the fused kernels now (a piece that needs more shared memory than a block has re-cuts the rows, which
+    // reads the analysis), then let the analysis go
+    const int fr = ensure_fused(0);
+    if (fr < 0) return -fr;
+    if (fr == 0) {
+      last_error = "a windowed plan needs the fused kernels: " + jit_log;
+      return (int) cudaErrorInvalidValue;
+    }
+    release_host_analysis();
   }
   AB_CUDA(cudaDeviceSynchronize());
   return 0;

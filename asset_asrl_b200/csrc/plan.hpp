@@ -139,6 +139,11 @@ struct Plan {
   // windowed plans (Problem::window): this rank's share of one long phase, analysed locally
   bool windowed = false;
   long long win_f_b = 0, win_f_e = 0;  // fused threads of the owned segments, relative to t_lo
+  // Windowed plans: once everything is uploaded and the fused kernels are assembled, the plan's copy of the analysis
+  // (pattern, triplet locations, destination maps, gather lists, index maps: ~20 KB per segment) is released -- eight
+  // ranks of a 1.6 M-segment phase share one host.
+  void release_host_analysis();
+  bool release_windowed = false;
   void window_filter(GatherList (*fl)[2], GatherList (*flE)[2], std::vector<int>* cut_t, int true_world);
   int eval(int mode, double obj_scale);
   // eval() = enqueue() on the plan's streams, or -- from the second evaluation of a mode on, when every kernel it needs

@@ -265,7 +265,16 @@ def run_b200(a):
     windows = world > 1 and a.shard == "windows"
     requested_segments = a.segments
     if windows:
-        # one phase of world x segments; every rank transcribes it, keeps its own segments plus a halo and analyses those
+        # one phase of world x segments; every rank transcribes it, keeps its own segments plus a halo and analyses those.
+        # All ranks of a node share its host memory: about 70 KB per segment at the peak of the analysis and plan build.
+        try:
+            import psutil
+            fit = int(0.6 * psutil.virtual_memory().available / (70e3 * world)) // 25000 * 25000
+        except ImportError:
+            fit = a.segments
+        t = torch.tensor([min(fit, a.segments)], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)  # every rank must build the same phase
+        a.segments = max(25000, int(t.item()))
         ph = W.make_phase(a.ode, a.mode, a.segments * world, extras=not a.no_extras, seed=12345, control_mode=a.control_mode)
         nlp = ph.transcribe_window(rank, world)
         d = nlp.dims()

@@ -23,14 +23,16 @@ class WindowCheck:
     def __init__(self, nlp, windows, pattern=None, skip_vars=(), own_apps=None):
         """``skip_vars``: variables whose rows are not compared (a windowed problem's far variables: every rank adds to
         them).  ``own_apps(f) -> (lo, hi)``: applications of function f whose constraint rows this rank holds (a windowed
-        problem keeps applications of its neighbours too; their rows live on the neighbour)."""
+        problem keeps applications of its neighbours too; their rows live on the neighbour).
+
+        The sub-problem is *compacted*: the variables and the equality / inequality rows its applications touch are
+        renumbered 0, 1, 2, ... in ascending order (a monotone map keeps every row's column order, so CSR rows still
+        compare entry by entry), which makes the oracle's cost follow the windows, not the size of the phase."""
         d = nlp.dims()
         self.windows = [(int(a), int(b)) for a, b in windows]
-        self.orc = Oracle(d["nvars"], d["neq"], d["niq"])
         lo = np.array([w[0] for w in self.windows], dtype=np.int64)
         hi = np.array([w[1] for w in self.windows], dtype=np.int64)
-        rows = {1: [], 2: []}
-        self.applications = 0
+        picked = []
         for f in range(d["nfuncs"]):
             fi = nlp.function_info(f)
             V, Cc = nlp.function_indices(f)
@@ -39,36 +41,71 @@ class WindowCheck:
                 hit |= ((V >= a) & (V < b)).any(axis=1)
             if not hit.any():
                 continue
+            mine = hit.copy()
+            if own_apps is not None:
+                lo_a, hi_a = own_apps(f)
+                mine[:lo_a] = False
+                mine[hi_a:] = False
             ac = nlp.function_appconst(f)
-            self.orc.add_function(fi["role"], nlp.tape_describe(fi["tape"]), fi["linear"], V[hit], Cc[hit] if fi["role"] else None,
-                                  ac[hit] if ac.size else None)
-            self.applications += int(hit.sum())
+            picked.append((fi, nlp.tape_describe(fi["tape"]), V[hit].astype(np.int64), Cc[hit].astype(np.int64) if fi["role"] else None,
+                           ac[hit] if ac.size else None, Cc[mine].astype(np.int64) if fi["role"] else None))
+        # monotone renumbering of what the sub-problem touches
+        self.vmap = np.unique(np.concatenate([p[2].ravel() for p in picked] + [np.zeros(0, dtype=np.int64)]))
+        cm = {1: [np.zeros(0, dtype=np.int64)], 2: [np.zeros(0, dtype=np.int64)]}
+        for fi, _, _, C_, _, _ in picked:
+            if fi["role"]:
+                cm[fi["role"]].append(C_.ravel())
+        self.emap, self.imap = np.unique(np.concatenate(cm[1])), np.unique(np.concatenate(cm[2]))
+        self.dims_full = (d["nvars"], d["neq"], d["niq"])
+        nv, ne, ni = int(self.vmap.size), int(self.emap.size), int(self.imap.size)
+        self.orc = Oracle(nv, ne, ni)
+        rows = {1: [], 2: []}
+        self.applications = 0
+        for fi, desc, V, C_, ac, Cm in picked:
+            Vc = np.searchsorted(self.vmap, V).astype(np.int32)
+            Cc = None
+            if fi["role"]:
+                Cc = np.searchsorted(self.emap if fi["role"] == 1 else self.imap, C_).astype(np.int32)
+            self.orc.add_function(fi["role"], desc, fi["linear"], Vc, Cc, ac)
+            self.applications += int(V.shape[0])
             if fi["role"] and fi["unique_constraints"]:
-                mine = hit.copy()
-                if own_apps is not None:
-                    lo_a, hi_a = own_apps(f)
-                    mine[:lo_a] = False
-                    mine[hi_a:] = False
-                rows[fi["role"]].append(Cc[mine].ravel().astype(np.int64))
+                rows[fi["role"]].append(Cm.ravel())
         self.orc.analyze()
         vrows = np.concatenate([np.arange(a, b, dtype=np.int64) for a, b in self.windows])
         if len(skip_vars):
             vrows = vrows[~np.isin(vrows, np.asarray(list(skip_vars), dtype=np.int64))]
         empty = np.zeros(0, dtype=np.int64)
-        # the product's CSR rows of the window variables against the sub-problem's: same columns, bit for bit
+        # the product's CSR rows of the window variables against the sub-problem's: same columns (after the renumbering)
         ip, ix = pattern if pattern is not None else nlp.pattern()
         sp, sx, _ = self.orc.pattern()
+        PV, EC, IC = d["nvars"], d["neq"], d["niq"]
+        SV = IC
+
+        def compact_cols(cols):  # whole-problem KKT column -> sub-problem column (-1: not in the sub-problem)
+            cols = np.asarray(cols, dtype=np.int64)
+            out = np.full(cols.shape, -1, dtype=np.int64)
+            for lo_c, hi_c, mp, base in ((0, PV, self.vmap, 0), (PV, PV + SV, self.imap, nv), (PV + SV, PV + SV + EC, self.emap, nv + ni),
+                                         (PV + SV + EC, PV + SV + EC + IC, self.imap, nv + ni + ne)):
+                sel = (cols >= lo_c) & (cols < hi_c)
+                if sel.any():
+                    loc = cols[sel] - lo_c
+                    pos = np.searchsorted(mp, loc)
+                    ok = (pos < mp.size) & (mp[np.minimum(pos, max(mp.size - 1, 0))] == loc) if mp.size else np.zeros(loc.shape, dtype=bool)
+                    res = np.where(ok, pos + base, -1)
+                    out[sel] = res
+            return out
         kk, ks = [], []
-        for r in vrows:
-            a0, a1, b0, b1 = int(ip[r]), int(ip[r + 1]), int(sp[r]), int(sp[r + 1])
-            if a1 - a0 != b1 - b0 or not np.array_equal(ix[a0:a1], sx[b0:b1]):
+        vr_c = np.searchsorted(self.vmap, vrows)
+        for r, rc in zip(vrows, vr_c):
+            a0, a1, b0, b1 = int(ip[r]), int(ip[r + 1]), int(sp[rc]), int(sp[rc + 1])
+            if a1 - a0 != b1 - b0 or not np.array_equal(compact_cols(ix[a0:a1]), sx[b0:b1]):
                 raise AssertionError(f"CSR row {r} of the product and of the oracle window differ in pattern")
             kk.append(np.arange(a0, a1, dtype=np.int64))
             ks.append(np.arange(b0, b1, dtype=np.int64))
         self.index = {"KKT": np.concatenate(kk) if kk else empty, "AGX": vrows, "PGX": vrows,
                       "FXE": np.concatenate(rows[1]) if rows[1] else empty, "FXI": np.concatenate(rows[2]) if rows[2] else empty}
-        self._ref_index = dict(self.index)
-        self._ref_index["KKT"] = np.concatenate(ks) if ks else empty
+        self._ref_index = {"KKT": np.concatenate(ks) if ks else empty, "AGX": vr_c, "PGX": vr_c,
+                           "FXE": np.searchsorted(self.emap, self.index["FXE"]), "FXI": np.searchsorted(self.imap, self.index["FXI"])}
 
     def extract(self, out):
         """The looked-at elements of full-length host arrays."""
@@ -76,7 +113,18 @@ class WindowCheck:
 
     def compare(self, slices, obj_scale, X, LE, LI, solver_coeffs=None, threads=0):
         """Worst relative difference per array (relative to the max-norm of the array's window elements)."""
-        ref = self.orc.eval("KKT", obj_scale, X, LE, LI, solver_coeffs, threads=threads or hardware_threads())
+        PV, EC, IC = self.dims_full
+        SV = IC
+        Xc = np.asarray(X, dtype=np.float64)[self.vmap]
+        LEc = np.asarray(LE, dtype=np.float64)[self.emap] if self.emap.size else np.zeros(0)
+        LIc = np.asarray(LI, dtype=np.float64)[self.imap] if self.imap.size else np.zeros(0)
+        sc = None
+        if solver_coeffs is not None:
+            # NonLinearProgram.cpp:198-265 order: slack ones, primal diagonal, slack diagonal, equality pivots, inequality pivots
+            s = np.asarray(solver_coeffs, dtype=np.float64)
+            sc = np.concatenate([s[self.imap], s[SV + self.vmap], s[SV + PV + self.imap], s[SV + PV + SV + self.emap],
+                                 s[SV + PV + SV + EC + self.imap]])
+        ref = self.orc.eval("KKT", obj_scale, Xc, LEc, LIc, sc, threads=threads or hardware_threads())
         worst = {}
         for k, got in slices.items():
             want = ref[k][self._ref_index[k]]

@@ -44,3 +44,36 @@ def test_owned_rows_have_the_whole_problems_pattern(ode, mode, nseg, world):
         assert fi["ok"] == 1, fi["why"]
     for f, cnt in enumerate(owned_apps):
         assert np.all(cnt == 1), (f, "every application is owned by exactly one rank")
+
+
+def test_bench_parity_windows_on_a_windowed_problem():
+    """bench.py's per-rank parity leg (oracle windows on a rank-local problem), with the whole-problem oracle's values laid
+    out in the rank's own CSR pattern standing in for the device output."""
+    import oracle
+    from oracle.windows import WindowCheck
+    from helpers import problem_inputs
+    nseg, world, vs = 600, 3, 20
+    ph = W.make_phase("lowthrust", "LGL5", nseg)
+    whole = ph.transcribe()
+    X = ph.makeSolverInput()
+    LE, LI, sc = problem_inputs(whole)
+    ref = oracle.Oracle.from_problem(whole).eval("KKT", 0.7, X, LE, LI, sc)
+    gip, gix = whole.pattern()
+    for r in range(world):
+        nlp = ph.transcribe_window(r, world)
+        lip, lix = nlp.pattern()
+        lo, hi = nseg * r // world, nseg * (r + 1) // world
+        far = set(int(v) for v in nlp.window_far_vars())
+        kkt = np.zeros(nlp.dims()["nnz"])
+        for v in range(lo * vs, hi * vs):
+            if v in far:
+                continue
+            kkt[lip[v]:lip[v + 1]] = ref["KKT"][gip[v]:gip[v + 1]]
+        out = {"KKT": kkt, "AGX": ref["AGX"], "PGX": ref["PGX"], "FXE": ref["FXE"], "FXI": ref["FXI"]}
+        windows = [(lo * vs, min(lo + 64, hi) * vs), (max((lo + hi) // 2 - 32, lo) * vs, min((lo + hi) // 2 + 32, hi) * vs),
+                   (max(hi - 64, lo) * vs, hi * vs)]
+        wc = WindowCheck(nlp, windows, skip_vars=nlp.window_far_vars(),
+                         own_apps=lambda f: (nlp.window_info(f)["own_lo"], nlp.window_info(f)["own_hi"]))
+        worst = wc.compare(wc.extract(out), 0.7, X, LE, LI, sc)
+        for k in ("KKT", "AGX", "PGX", "FXE", "FXI"):
+            assert worst[k] < 1e-13, (r, k, worst)

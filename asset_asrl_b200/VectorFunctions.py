@@ -14,7 +14,8 @@ from ._lib import lib
 # ab::VKind (csrc/expr.hpp)
 (VK_ARGS, VK_SEGMENT, VK_ELEMENTS, VK_CONSTANT, VK_STACK, VK_SUM, VK_DIFF, VK_SCALED, VK_ROWSCALED, VK_ADDVEC,
  VK_VECMINUS, VK_UNARY, VK_NORM, VK_NORMALIZED, VK_DOT, VK_CROSS, VK_CWISEPROD, VK_CWISEQUOT, VK_VSPROD, VK_VSDIV,
- VK_CWISESUM, VK_ATAN2, VK_NESTED, VK_IFELSE, VK_COMPARE, VK_BOOL, VK_IOSCALED, VK_APPCONST, VK_MATVEC) = range(29)
+ VK_CWISESUM, VK_ATAN2, VK_NESTED, VK_IFELSE, VK_COMPARE, VK_BOOL, VK_IOSCALED, VK_APPCONST, VK_MATVEC, VK_QUATPROD,
+ VK_INTERP1D, VK_INTERP2D) = range(32)
 
 # ab::Op (csrc/tape.h)
 OPS = ["CONST", "INPUT", "LAMBDA", "APPCONST", "ADD", "SUB", "MUL", "DIV", "NEG", "ADDC", "MULC", "SQUARE", "INV", "SQRT",
@@ -387,6 +388,34 @@ class VectorFunction:
             raise ValueError("cross: both operands must have 3 outputs")
         return self._new(VK_CROSS, 3, [self, o])
 
+    def quatProduct(self, o):
+        """Hamilton product of two quaternions stored vector-first (FunctionQuatProduct, VectorProducts.h:28-30,229-236)."""
+        o = self._other(o)
+        if o.orows != 4 or self.orows != 4:
+            raise ValueError("quatProduct: both operands must have 4 outputs")
+        return self._new(VK_QUATPROD, 4, [self, o])
+
+    def padded_lower(self, n):
+        """The outputs followed by n zeros (PaddedOutput, Padded.h:24-60; type-level linear when the function is)."""
+        return self.padded(0, n)
+
+    def padded_upper(self, n):
+        return self.padded(n, 0)
+
+    def padded(self, upper, lower):
+        upper, lower = int(upper), int(lower)
+        if upper < 0 or lower < 0:
+            raise ValueError("padded: negative padding")
+        parts = []
+        if upper:
+            parts.append(self._new(VK_CONSTANT, upper, [], d=np.zeros(upper), raw=1))
+        parts.append(self)
+        if lower:
+            parts.append(self._new(VK_CONSTANT, lower, [], d=np.zeros(lower), raw=1))
+        if len(parts) == 1:
+            return self
+        return self._new(VK_STACK, self.orows + upper + lower, parts)
+
     def cwiseProduct(self, o):
         o = self._other(o)
         if o.orows != self.orows:
@@ -562,6 +591,24 @@ def cross(a, b):
     if isinstance(a, VectorFunction):
         return a.cross(b)
     return -(b.cross(a))
+
+
+def quatProduct(a, b):
+    """vf.quatProduct(q1, q2) (FreeFunctionsBuild.cpp:371-378)."""
+    if isinstance(a, VectorFunction):
+        return a.quatProduct(b)
+    return b._other(a).quatProduct(b)
+
+
+def quatRotate(q, v):
+    """vf.quatRotate(q, v): the vector part of q (x) (v, 0) (x) q^-1 for a unit quaternion q stored vector-first
+    (QuatRotation::Definition, FreeFunctionsBuild.cpp:310-321)."""
+    q = _as_fun(q)
+    v = v if isinstance(v, VectorFunction) else q._other(v)
+    if q.orows != 4 or v.orows != 3:
+        raise ValueError("quatRotate: needs a quaternion and a 3-vector")
+    qinv = stack(q.head(3) * (-1.0), q.coeff(3))
+    return q.quatProduct(v.padded_lower(1)).quatProduct(qinv).head(3)
 
 
 def cwiseProduct(a, b):

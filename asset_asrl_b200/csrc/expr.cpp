@@ -263,6 +263,15 @@ std::vector<int> lower_impl(const Graph& g, int root, const std::vector<int>& in
       out.push_back(dag.sub(dag.mul(a[2], b[0]), dag.mul(a[0], b[2])));
       out.push_back(dag.sub(dag.mul(a[0], b[1]), dag.mul(a[1], b[0])));
     } break;
+    case VK_QUATPROD: {  // FunctionQuatProduct (VectorProducts.h:28-30), term order of quatprodimpl (:229-236)
+      auto a = L(0), b = L(1);
+      if (a.size() != 4 || b.size() != 4) throw std::invalid_argument("lower: quaternion product needs two 4-vectors");
+      auto m = [&](int i, int j) { return dag.mul(a[i], b[j]); };
+      out.push_back(dag.sub(dag.add(dag.add(m(0, 3), m(3, 0)), m(1, 2)), m(2, 1)));
+      out.push_back(dag.sub(dag.add(dag.add(m(1, 3), m(3, 1)), m(2, 0)), m(0, 2)));
+      out.push_back(dag.sub(dag.add(dag.add(m(2, 3), m(3, 2)), m(0, 1)), m(1, 0)));
+      out.push_back(dag.sub(dag.sub(dag.sub(m(3, 3), m(0, 0)), m(1, 1)), m(2, 2)));
+    } break;
     case VK_CWISEPROD: {
       auto a = L(0), b = L(1);
       for (size_t i = 0; i < a.size(); i++) out.push_back(dag.mul(a[i], b[i]));
@@ -576,7 +585,7 @@ static const char* kind_name(int k) {
   static const char* names[] = {"args",     "segment", "elements",  "constant",  "stack",    "sum",     "diff",   "scaled",
                                 "rowscaled", "addvec",  "vecminus",  "unary",     "norm",     "normalized", "dot", "cross",
                                 "cwiseprod", "cwisequot", "vsprod",  "vsdiv",     "cwisesum", "atan2",   "nested", "ifelse",
-                                "compare",  "bool",    "ioscaled",  "appconst",  "matvec"};
+                                "compare",  "bool",    "ioscaled",  "appconst",  "matvec",   "quatprod", "interp1d", "interp2d"};
   return names[k];
 }
 

@@ -48,6 +48,9 @@ enum VKind : int {
   VK_IOSCALED,      // out_scale .* ch0(in_scale .* x)    d = [in_scales(ir) , out_scales(orows)]
   VK_APPCONST,      // per-application constant vector of size orows, ip = {first index}
   VK_MATVEC,        // matrix(d, orows x ch.orows, row-major) * ch0
+  VK_QUATPROD,      // Hamilton product ch0 (x) ch1 of two quaternions stored vector-first (x, y, z, w)
+  VK_INTERP1D,      // InterpTable1D(ch0 = t): ip = {n, vlen, kind (0 cubic, 1 linear), even}, d = [ts(n), vs(vlen x n), dvs(vlen x n)]
+  VK_INTERP2D,      // InterpTable2D(ch0 = (x, y)): ip = {nx, ny, kind, xeven, yeven}, d = [xs, ys, z, dz/dx, dz/dy, d2z/dxdy (ny x nx each)]
 };
 
 struct VNode {

@@ -60,7 +60,12 @@ enum {
   AB_VK_VSPROD = 18,     /* vector child0 * scalar child1 */
   AB_VK_VSDIV = 19, AB_VK_CWISESUM = 20, AB_VK_ATAN2 = 21,
   AB_VK_NESTED = 22,     /* child0(child1(x)) */
-  AB_VK_IFELSE = 23, AB_VK_COMPARE = 24, AB_VK_BOOL = 25, AB_VK_IOSCALED = 26, AB_VK_APPCONST = 27, AB_VK_MATVEC = 28
+  AB_VK_IFELSE = 23, AB_VK_COMPARE = 24, AB_VK_BOOL = 25, AB_VK_IOSCALED = 26, AB_VK_APPCONST = 27, AB_VK_MATVEC = 28,
+  AB_VK_QUATPROD = 29,   /* Hamilton product child0 (x) child1, quaternions stored (x, y, z, w) (VectorProducts.h:28-30,229-236) */
+  AB_VK_INTERP1D = 30,   /* InterpTable1D at child0 = t (InterpTable1D.h:9-483): iparams = {n, vlen, kind (0 cubic, 1 linear), even},
+                            dparams = [ts (n), vs (vlen x n, row-major), dvs/dt (vlen x n; cubic only)] */
+  AB_VK_INTERP2D = 31    /* InterpTable2D at child0 = (x, y) (InterpTable2D.h): iparams = {nx, ny, kind, xeven, yeven},
+                            dparams = [xs (nx), ys (ny), z, dz/dx, dz/dy, d2z/dxdy (ny x nx each, row-major; cubic: all four)] */
 };
 /* PhaseRegionFlags and TranscriptionModes of the reference (src/OptimalControl/OptimalControlFlags.h) */
 enum { AB_REGION_FRONT = 1, AB_REGION_BACK = 2, AB_REGION_FRONTANDBACK = 3, AB_REGION_BACKANDFRONT = 4, AB_REGION_PATH = 5,

@@ -92,12 +92,12 @@ static Vec atv(const Mat& A, const double* l) {
 enum Kind {
   K_ARGS, K_SEGMENT, K_ELEMENTS, K_CONSTANT, K_STACK, K_SUM, K_DIFF, K_SCALED, K_ROWSCALED, K_ADDVEC, K_VECMINUS,
   K_UNARY, K_NORM, K_NORMALIZED, K_DOT, K_CROSS, K_CWISEPROD, K_CWISEQUOT, K_VSPROD, K_VSDIV, K_CWISESUM, K_ATAN2,
-  K_NESTED, K_IFELSE, K_COMPARE, K_BOOL, K_IOSCALED, K_APPCONST, K_MATVEC, K_COUNT
+  K_NESTED, K_IFELSE, K_COMPARE, K_BOOL, K_IOSCALED, K_APPCONST, K_MATVEC, K_QUATPROD, K_INTERP1D, K_INTERP2D, K_COUNT
 };
 static const char* kKindNames[K_COUNT] = {"args", "segment", "elements", "constant", "stack", "sum", "diff", "scaled",
                                           "rowscaled", "addvec", "vecminus", "unary", "norm", "normalized", "dot", "cross",
                                           "cwiseprod", "cwisequot", "vsprod", "vsdiv", "cwisesum", "atan2", "nested", "ifelse",
-                                          "compare", "bool", "ioscaled", "appconst", "matvec"};
+                                          "compare", "bool", "ioscaled", "appconst", "matvec", "quatprod", "interp1d", "interp2d"};
 
 // unary opcodes: numeric values of ab::Op in asset_asrl_b200/csrc/tape.h (the describe() string carries them)
 enum UOp { U_NEG = 8, U_SQUARE = 11, U_INV, U_SQRT, U_EXP, U_LOG, U_SIN, U_COS, U_TAN, U_ASIN, U_ACOS, U_ATAN, U_SINH, U_COSH,
@@ -346,6 +346,27 @@ void Eval::outer(const Node& n, const Vec& Y, const std::vector<int>& off, doubl
           (*Hp)(3 + k, j) += l[i];
           (*Hp)(k, 3 + j) -= l[i];
           (*Hp)(3 + j, k) -= l[i];
+        }
+      }
+    } break;
+    case K_QUATPROD: {  // VectorProducts.h:28-30 (FunctionQuatProduct), :229-236 (quatprodimpl), :238-262 (fillquatprodmatrix)
+      // out_o = sum of sg * a_i * b_j over the bilinear terms below (quaternions stored x, y, z, w)
+      static const int T[16][4] = {{0, 0, 3, 1}, {0, 3, 0, 1}, {0, 1, 2, 1}, {0, 2, 1, -1}, {1, 1, 3, 1}, {1, 3, 1, 1}, {1, 2, 0, 1}, {1, 0, 2, -1},
+                                   {2, 2, 3, 1}, {2, 3, 2, 1}, {2, 0, 1, 1}, {2, 1, 0, -1}, {3, 3, 3, 1}, {3, 0, 0, -1}, {3, 1, 1, -1}, {3, 2, 2, -1}};
+      const double* a = &Y[0];
+      const double* b = &Y[4];
+      for (int o = 0; o < 4; o++) fx[o] = 0.0;
+      for (const auto& t: T) {
+        const int o = t[0], i = t[1], j = t[2];
+        const double sg = t[3];
+        fx[o] += sg * a[i] * b[j];
+        if (Jp) {
+          (*Jp)(o, i) += sg * b[j];
+          (*Jp)(o, 4 + j) += sg * a[i];
+        }
+        if (Hp) {
+          (*Hp)(i, 4 + j) += sg * l[o];
+          (*Hp)(4 + j, i) += sg * l[o];
         }
       }
     } break;

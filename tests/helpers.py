@@ -51,6 +51,10 @@ def expression_zoo():
     z.append(("ioscaled", vf.ioscaled(x3.normalized_power3(), [2.0, 0.5, 3.0], [0.1, 10.0, -2.0]), pos(3)))
     z.append(("cwise_sum_elements", (vf.sin(x6).sum()) * x6[[0, 3, 5]].norm(), pos(6)))
     z.append(("two_body", vf.stack([x6.tail3(), x6.head3().normalized_power3() * (-1.0)]), pos(6)))
+    x8, x7 = A(8), A(7)
+    z.append(("quat_product", vf.quatProduct(x8.head(4), vf.sin(x8.tail(4))), sym(8)))
+    z.append(("quat_kinematics", vf.quatProduct(x7.head(4), x7.tail3().padded_lower(1)) / 2.0, sym(7)))  # OptimalDocking.py:96
+    z.append(("quat_rotate", vf.quatRotate(x7.head(4).normalized(), x7.tail3()), pos(7)))
     return z
 
 

@@ -92,3 +92,24 @@ def test_threads_agree():
         b = orc.eval("KKT", 1.0, X, LE, LI, threads=t)
         for k in ("KKT", "FXE", "FXI", "PGX", "AGX"):
             assert rel_err(b[k], a[k]) < 1e-13
+
+
+def test_quaternion_product_known_answers():
+    """FunctionQuatProduct / QuatRotation (VectorProducts.h:229-236, FreeFunctionsBuild.cpp:310-321) against the unit
+    quaternion identities (i j = k, j k = i, k i = j, i i = -1; vector-first storage) and scipy's rotations."""
+    from scipy.spatial.transform import Rotation
+    qq = vf.quatProduct(vf.Arguments(8).head(4), vf.Arguments(8).tail(4))
+    i, j, k, one = np.eye(4)
+    for a, b, want in ((i, j, k), (j, k, i), (k, i, j), (i, i, -one), (j, i, -k), (one, k, k)):
+        fx, _, _, _ = oracle.computeall("expr " + qq.describe(), np.concatenate([a, b]), np.zeros(4))
+        assert np.array_equal(fx, want)
+    rng = np.random.default_rng(5)
+    rot = vf.quatRotate(vf.Arguments(7).head(4), vf.Arguments(7).tail3())
+    for _ in range(4):
+        q1, q2 = (q / np.linalg.norm(q) for q in rng.normal(size=(2, 4)))
+        v = rng.normal(size=3)
+        fx, _, _, _ = oracle.computeall("expr " + qq.describe(), np.concatenate([q1, q2]), np.zeros(4))
+        want = (Rotation.from_quat(q1) * Rotation.from_quat(q2)).as_quat()
+        assert min(np.abs(fx - want).max(), np.abs(fx + want).max()) < 1e-14
+        fx, _, _, _ = oracle.computeall("expr " + rot.describe(), np.concatenate([q1, v]), np.zeros(3))
+        assert np.abs(fx - Rotation.from_quat(q1).apply(v)).max() < 1e-14

@@ -149,6 +149,14 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_program_code(self.h, f, mode, code.ctypes.data_as(C.c_void_p), _lib.dptr(consts)))
         return st, code, consts
 
+    def program_tables(self, f, mode=4):
+        """The interpolation-table pool the program of function ``f`` reads (empty for a function without tables)."""
+        n = _lib.check(lib.ab_problem_program_tables(self.h, f, mode, None, 0))
+        out = np.zeros(n)
+        if n:
+            _lib.check(lib.ab_problem_program_tables(self.h, f, mode, _lib.dptr(out), n))
+        return out
+
     def fused_info(self, min_threads=32):
         """Host-side description of the owner-writes fused interior (no GPU needed)."""
         out = (C.c_longlong * 12)()

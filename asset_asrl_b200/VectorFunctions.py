@@ -20,7 +20,7 @@ from ._lib import lib
 # ab::Op (csrc/tape.h)
 OPS = ["CONST", "INPUT", "LAMBDA", "APPCONST", "ADD", "SUB", "MUL", "DIV", "NEG", "ADDC", "MULC", "SQUARE", "INV", "SQRT",
        "EXP", "LOG", "SIN", "COS", "TAN", "ASIN", "ACOS", "ATAN", "SINH", "COSH", "TANH", "ASINH", "ACOSH", "ATANH", "ABS",
-       "SIGN", "POWC", "ATAN2", "LT", "LE", "SELECT", "FMA", "OUT_F", "OUT_G"]
+       "SIGN", "POWC", "ATAN2", "LT", "LE", "SELECT", "FMA", "OUT_F", "OUT_G", "TABIDX", "TABLOAD"]
 OP = {n: i for i, n in enumerate(OPS)}
 
 
@@ -648,6 +648,193 @@ def ioscaled(f, in_scales, out_scales):
     if i.size != f.ir or o.size != f.orows:
         raise ValueError("ioscaled: scale sizes do not match")
     return f._new(VK_IOSCALED, f.orows, [f], d=np.concatenate([i, o]))
+
+
+def _stencil_derivs(cs, V, even):
+    """d V / d c along the last axis by five-point stencils fitted to the actual spacing: central where two neighbours
+    exist on both sides, one-sided at the ends (InterpTable1D::calc_derivs, InterpTable1D.h:133-178; an evenly spaced
+    axis reuses its first central stencil, :151-153)."""
+    n = cs.size
+    out = np.zeros_like(V, dtype=np.float64)
+    rhs = np.array([0.0, 1.0, 0.0, 0.0, 0.0])
+    coeffs, hitcent = None, False
+    for i in range(n):
+        recalc = True
+        if i + 2 <= n - 1 and i - 2 >= 0:
+            if even and hitcent:
+                recalc = False
+            hitcent = True
+            start = i - 2
+        elif i < n - 1 - i:
+            start = 0
+        else:
+            start = n - 5
+        step = np.abs(cs[i + (1 if i < n - 1 else -1)] - cs[i])
+        if recalc:
+            tau = (cs[start:start + 5] - cs[i]) / step
+            coeffs = np.linalg.solve(np.vander(tau, 5, increasing=True).T, rhs)
+        out[..., i] = V[..., start:start + 5] @ (coeffs / step)
+    return out
+
+
+def _is_even(cs):
+    return not (np.abs(cs - np.linspace(cs[0], cs[-1], cs.size)).max() > np.abs(cs[-1] - cs[0]) * 1.0e-12)
+
+
+def _kind(kind):
+    if kind in ("cubic", "Cubic"):
+        return 0
+    if kind in ("linear", "Linear"):
+        return 1
+    raise ValueError("Unrecognized interpolation type")
+
+
+def _ascending(cs, what):
+    if cs.size < 5:
+        raise ValueError(f"{what} coordinates must be larger than 4")
+    if np.any(np.diff(cs) < 0):
+        raise ValueError(f"{what} Coordinates must be in ascending order")
+
+
+class InterpTable1D:
+    """vf.InterpTable1D(ts, Vs, axis=0, kind='cubic') (InterpTable1D.h:9-131): piecewise cubic-Hermite (slopes from
+    five-point stencils) or linear interpolation of vector data over a scalar coordinate.  ``tab(f)`` with a scalar
+    function ``f`` gives the interpolant as a function evaluated on the device; ``tab(number)`` evaluates on the host."""
+
+    def __init__(self, ts, Vs=None, axis=0, kind="cubic", tvar=None):
+        if Vs is None or isinstance(Vs, (int, np.integer)):  # InterpTable1D(Vts, tvar=-1, kind): rows of [values..., t]
+            if isinstance(axis, str):  # InterpTable1D(Vts, tvar, kind) given positionally
+                kind = axis
+            rows = np.asarray(ts, dtype=np.float64)
+            if rows.ndim != 2 or rows.shape[0] == 0:
+                raise ValueError("Input is empty")
+            if rows.shape[1] < 2:
+                raise ValueError("Invalid sized value-time data.")
+            tv = -1 if Vs is None and tvar is None else int(tvar if tvar is not None else Vs)
+            tv = tv + rows.shape[1] if tv < 0 else tv
+            if not 0 <= tv < rows.shape[1]:
+                raise ValueError("Invalid time variable index")
+            ts, Vs, axis = rows[:, tv], np.delete(rows, tv, axis=1).T, 1
+        ts = np.asarray(ts, dtype=np.float64).ravel()
+        Vs = np.asarray(Vs, dtype=np.float64)
+        if Vs.ndim == 1:
+            Vs, axis = Vs[None, :], 1
+        if axis == 0:
+            Vs = Vs.T
+        elif axis != 1:
+            raise ValueError("Interpolation axis must be 0 or 1")
+        self.kind = _kind(kind)
+        _ascending(ts, "t")
+        if ts.size != Vs.shape[1]:
+            raise ValueError("Length of t coordinates must match length of interpolation axis")
+        self.ts, self.vs = ts, np.ascontiguousarray(Vs)
+        self.vlen, self.tsize = Vs.shape[0], ts.size
+        self.teven = _is_even(ts)
+        self.dvs_dts = _stencil_derivs(ts, self.vs, self.teven) if self.kind == 0 else None
+        self.WarnOutOfBounds, self.ThrowOutOfBounds = True, False
+
+    def _data(self):
+        parts = [self.ts, self.vs.ravel()] + ([self.dvs_dts.ravel()] if self.kind == 0 else [])
+        return np.concatenate(parts), [self.tsize, self.vlen, self.kind, int(self.teven)]
+
+    def vf(self):
+        t = Arguments(1)
+        d, ip = self._data()
+        return VectorFunction(GRAPH.node(VK_INTERP1D, 1, self.vlen, [t.node], d, ip, -1, 0), 1, self.vlen)
+
+    def sf(self):
+        if self.vlen != 1:
+            raise ValueError("InterpTable1D storing Vector data cannot be converted to Scalar Function.")
+        return ScalarFunction(self.vf().node, 1, 1)
+
+    def _telem(self, t):
+        if self.teven:
+            e = int((t - self.ts[0]) / (self.ts[1] - self.ts[0]))
+        else:
+            e = int(np.searchsorted(self.ts, t, side="right")) - 1
+        return max(min(e, self.tsize - 2), 0)
+
+    def interp_deriv2(self, t):
+        """(v, dv/dt, d2v/dt2) on the host (InterpTable1D::interp_impl, InterpTable1D.h:199-262)."""
+        t = float(t)
+        e = self._telem(t)
+        h = self.ts[e + 1] - self.ts[e]
+        u = (t - self.ts[e]) / h
+        v0, v1 = self.vs[:, e], self.vs[:, e + 1]
+        if self.kind == 1:
+            return v0 * (1 - u) + v1 * u, (v1 - v0) / h, np.zeros(self.vlen)
+        d0, d1 = self.dvs_dts[:, e], self.dvs_dts[:, e + 1]
+        u2, u3 = u * u, u * u * u
+        v = v0 * (2 * u3 - 3 * u2 + 1) + v1 * (-2 * u3 + 3 * u2) + d0 * ((u3 - 2 * u2 + u) * h) + d1 * ((u3 - u2) * h)
+        dv = v0 * ((6 * u2 - 6 * u) / h) + v1 * ((-6 * u2 + 6 * u) / h) + d0 * (3 * u2 - 4 * u + 1) + d1 * (3 * u2 - 2 * u)
+        d2v = v0 * ((12 * u - 6) / (h * h)) + v1 * ((-12 * u + 6) / (h * h)) + d0 * ((6 * u - 4) / h) + d1 * ((6 * u - 2) / h)
+        return v, dv, d2v
+
+    def interp_deriv1(self, t):
+        return self.interp_deriv2(t)[:2]
+
+    def interp(self, t):
+        if np.ndim(t) == 0:
+            return self.interp_deriv2(t)[0]
+        return np.stack([self.interp_deriv2(x)[0] for x in np.asarray(t).ravel()], axis=1)
+
+    def __call__(self, t):
+        if isinstance(t, VectorFunction):
+            if t.orows != 1:
+                raise ValueError("InterpTable1D: the coordinate must be a scalar function")
+            f = self.vf().eval(t)
+            return ScalarFunction(f.node, f.ir, 1) if self.vlen == 1 else f
+        return self.interp(t)
+
+
+class InterpTable2D:
+    """vf.InterpTable2D(xs, ys, Z, kind='cubic') (InterpTable2D.h:7-120): bicubic (Hermite patches with stencil
+    derivatives) or bilinear interpolation of Z[iy][ix] over (x, y)."""
+
+    def __init__(self, xs, ys, Z, kind="cubic"):
+        self.kind = _kind(kind)
+        xs, ys = np.asarray(xs, dtype=np.float64).ravel(), np.asarray(ys, dtype=np.float64).ravel()
+        Z = np.ascontiguousarray(np.asarray(Z, dtype=np.float64))
+        if xs.size < 5:
+            raise ValueError("X coordinates must be larger than 4")
+        if ys.size < 5:
+            raise ValueError("Y  coordinates must be larger than 4")
+        if Z.ndim != 2 or xs.size != Z.shape[1]:
+            raise ValueError("X coordinates must match cols in Z matrix")
+        if ys.size != Z.shape[0]:
+            raise ValueError("Y coordinates must match rows in Z matrix")
+        _ascending(xs, "X")
+        _ascending(ys, "Y")
+        self.xs, self.ys, self.zs = xs, ys, Z
+        self.xeven, self.yeven = _is_even(xs), _is_even(ys)
+        if self.kind == 0:  # InterpTable2D::calc_derivs (InterpTable2D.h:122-211)
+            self.dzys = _stencil_derivs(ys, Z.T, self.yeven).T
+            self.dzxs = _stencil_derivs(xs, Z, self.xeven)
+            self.dzys_dxs = _stencil_derivs(xs, self.dzys, self.xeven)
+        self.WarnOutOfBounds, self.ThrowOutOfBounds = True, False
+
+    def _data(self):
+        parts = [self.xs, self.ys, self.zs.ravel()]
+        if self.kind == 0:
+            parts += [self.dzxs.ravel(), self.dzys.ravel(), self.dzys_dxs.ravel()]
+        return np.concatenate(parts), [self.xs.size, self.ys.size, self.kind, int(self.xeven), int(self.yeven)]
+
+    def vf(self):
+        d, ip = self._data()
+        return ScalarFunction(GRAPH.node(VK_INTERP2D, 2, 1, [Arguments(2).node], d, ip, -1, 0), 2, 1)
+
+    sf = vf
+
+    def __call__(self, x, y=None):
+        if isinstance(x, VectorFunction):
+            xy = x if y is None else stack([x, y])
+            if xy.orows != 2:
+                raise ValueError("InterpTable2D: needs two scalar coordinates")
+            f = self.vf().eval(xy)
+            return ScalarFunction(f.node, f.ir, 1)
+        raise NotImplementedError("InterpTable2D on numbers: evaluate tab.vf() through the oracle or on the device")
+
+    interp = __call__
 
 
 Element = ScalarFunction

@@ -57,6 +57,7 @@ SIGNATURES = {
     "ab_problem_tape_describe": (_ll, [_vp, _i, _cp, _ll]),
     "ab_problem_program_stats": (_i, [_vp, _i, _i, _llp]),
     "ab_problem_program_code": (_i, [_vp, _i, _i, _vp, _dp]),
+    "ab_problem_program_tables": (_ll, [_vp, _i, _i, _dp, _ll]),
     "ab_problem_kernel_ptx": (_ll, [_vp, _i, _i, _i, _cp, _ll]),
     "ab_ptx_assemble": (_i, [_cp, _llp]),
     "ab_problem_tape_code": (_i, [_vp, _i, _vp]),

@@ -333,6 +333,16 @@ int ab_problem_program_code(const ab_problem* p, int fidx, int mode, void* code,
   return AB_OK;
   AB_CATCH
 }
+long long ab_problem_program_tables(const ab_problem* p, int fidx, int mode, double* out, long long cap) {
+  try {
+    Program P = program_of(p, fidx, mode);
+    const long long n = (long long) P.tables.size();
+    if (out && cap > 0) std::memcpy(out, P.tables.data(), (size_t) std::min(n, cap) * sizeof(double));
+    return n;
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
 int ab_problem_program_stats(const ab_problem* p, int fidx, int mode, long long out[8]) {
   AB_TRY
   Program P = program_of(p, fidx, mode);

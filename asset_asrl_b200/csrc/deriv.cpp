@@ -87,7 +87,9 @@ void ScalarFn::make_second_order() {
       case OP_APPCONST:
       case OP_SIGN:
       case OP_LT:
-      case OP_LE: break;
+      case OP_LE:
+      case OP_TABIDX:
+      case OP_TABLOAD: break;
       case OP_INPUT: t.emplace_back(a, one); break;
       case OP_ADD: t = tan_add(d, T[a], T[b], false); break;
       case OP_SUB: t = tan_add(d, T[a], T[b], true); break;

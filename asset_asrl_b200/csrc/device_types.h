@@ -23,6 +23,7 @@ enum FnMode : int {
 struct ProgDev {
   const uint4* code;     // 4 x 16-byte instructions per bundle
   const double* consts;  // shared constants, copied to shared memory by the block
+  const double* tables;  // interpolation-table pool read by OP_TABIDX / OP_TABLOAD (null when the program has none)
   int nconst;
   int nslots;            // lane-private 8-byte slots per thread
   int nthreads;          // block size the operand offsets were linked for

@@ -119,6 +119,53 @@ int SDag::unary(uint16_t op, int a, double imm) {
   if (op == OP_NEG) return neg(a);
   return raw(op, a, -1, -1, imm);
 }
+// ---------------------------------------------------------------------------------------------
+// interpolation-table pool
+// ---------------------------------------------------------------------------------------------
+size_t SDag::tab_add(const double* p, size_t len) {
+  for (const TabEntry& e: tabs)
+    if (e.len == len && std::memcmp(&tabpool[e.off], p, len * sizeof(double)) == 0) return e.off;
+  const size_t off = tabpool.size();
+  tabpool.insert(tabpool.end(), p, p + len);
+  tabs.push_back({off, len});
+  return off;
+}
+const SDag::TabEntry& SDag::tab_find(size_t off) const {
+  for (const TabEntry& e: tabs)
+    if (off >= e.off && off < e.off + e.len) return e;
+  throw std::logic_error("table offset outside every table");
+}
+double SDag::tab_import(const SDag& src, double imm) {
+  const size_t off = (size_t) imm;
+  const TabEntry& e = src.tab_find(off);
+  std::vector<double> copy(src.tabpool.begin() + (long) e.off, src.tabpool.begin() + (long) (e.off + e.len));  // src may be *this
+  return (double) (tab_add(copy.data(), copy.size()) + (off - e.off));
+}
+// InterpTable1D::get_telem (InterpTable1D.h:180-197) / InterpTable2D::get_xyelems (InterpTable2D.h:221-251)
+int table_interval(const double* axis, double t) {
+  const int n = (int) axis[0];
+  const double* ts = axis + 2;
+  int e;
+  if (axis[1] != 0.0) {
+    double q = (t - ts[0]) / (ts[1] - ts[0]);
+    // the device converts with cvt.rzi.s32.f64 (saturating, NaN -> 0); clamping first gives the same interval
+    if (!(q > -1.0)) q = -1.0;
+    if (q > (double) n) q = (double) n;
+    e = (int) q;
+  } else {
+    e = (int) (std::upper_bound(ts, ts + n, t) - ts) - 1;
+  }
+  return std::max(std::min(e, n - 2), 0);
+}
+int SDag::tabidx(int a, size_t axis_off) {
+  if (is_const(a)) return constant((double) table_interval(&tabpool[axis_off], cval(a)));
+  return raw(OP_TABIDX, a, -1, -1, (double) axis_off);
+}
+int SDag::tabload(int idx, size_t base_off) {
+  if (is_const(idx)) return constant(tabpool.at(base_off + (size_t) (long long) cval(idx)));
+  return raw(OP_TABLOAD, idx, -1, -1, (double) base_off);
+}
+
 int SDag::atan2(int y, int x) {
   if (is_const(y) && is_const(x)) return constant(std::atan2(cval(y), cval(x)));
   return raw(OP_ATAN2, y, x, -1, 0.0);
@@ -328,6 +375,140 @@ std::vector<int> lower_impl(const Graph& g, int root, const std::vector<int>& in
       auto a = lower_impl(g, nd.ch[0], sin, dag, ctx);
       for (size_t i = 0; i < a.size(); i++) out.push_back(dag.mulc(a[i], nd.d[nd.ir + i]));
     } break;
+    case VK_INTERP1D: {  // InterpTable1D::interp_impl (InterpTable1D.h:199-262), the interpolant as arithmetic on the local
+                         // coordinate; its first and second derivatives (:231-254) follow from differentiating the DAG
+      auto tt = L(0);
+      if (tt.size() != 1 || nd.ip.size() != 4) throw std::invalid_argument("lower: InterpTable1D takes one scalar and ip = {n, vlen, kind, even}");
+      const int n = nd.ip[0], vlen = nd.ip[1], kind = nd.ip[2];
+      const bool cubic = kind == 0;
+      if (n < 5) throw std::invalid_argument("t coordinates must be larger than 4");
+      if (vlen != nd.orows || (long long) nd.d.size() != (long long) n * (1 + vlen * (cubic ? 2 : 1)))
+        throw std::invalid_argument("lower: InterpTable1D data size does not match n, vlen and the kind");
+      for (int i = 0; i + 1 < n; i++)
+        if (nd.d[i + 1] < nd.d[i]) throw std::invalid_argument("t Coordinates must be in ascending order");
+      std::vector<double> axis(n + 2);
+      axis[0] = n;
+      axis[1] = nd.ip[3] ? 1.0 : 0.0;
+      std::copy(nd.d.begin(), nd.d.begin() + n, axis.begin() + 2);
+      const size_t aoff = dag.tab_add(axis.data(), axis.size());
+      const size_t voff = dag.tab_add(nd.d.data() + n, (size_t) n * vlen);
+      const size_t doff = cubic ? dag.tab_add(nd.d.data() + n + (size_t) n * vlen, (size_t) n * vlen) : 0;
+      const int t = tt[0];
+      const int e = dag.tabidx(t, aoff);
+      const int t0 = dag.tabload(e, aoff + 2), t1 = dag.tabload(e, aoff + 3);
+      const int step = dag.sub(t1, t0);
+      const int u = dag.div(dag.sub(t, t0), step);
+      if (cubic) {
+        const int u2 = dag.mul(u, u), u3 = dag.mul(u2, u);
+        // Hermite basis, InterpTable1D.h:222-225
+        const int p0 = dag.addc(dag.sub(dag.mulc(u3, 2.0), dag.mulc(u2, 3.0)), 1.0);
+        const int m0 = dag.mul(dag.add(dag.sub(u3, dag.mulc(u2, 2.0)), u), step);
+        const int p1 = dag.add(dag.mulc(u3, -2.0), dag.mulc(u2, 3.0));
+        const int m1 = dag.mul(dag.sub(u3, u2), step);
+        for (int k = 0; k < vlen; k++) {
+          const size_t r = (size_t) k * n;
+          const int v0 = dag.tabload(e, voff + r), v1 = dag.tabload(e, voff + r + 1);
+          const int d0 = dag.tabload(e, doff + r), d1 = dag.tabload(e, doff + r + 1);
+          out.push_back(dag.add(dag.add(dag.add(dag.mul(v0, p0), dag.mul(v1, p1)), dag.mul(d0, m0)), dag.mul(d1, m1)));
+        }
+      } else {
+        const int w = dag.addc(dag.neg(u), 1.0);
+        for (int k = 0; k < vlen; k++) {
+          const size_t r = (size_t) k * n;
+          const int v0 = dag.tabload(e, voff + r), v1 = dag.tabload(e, voff + r + 1);
+          out.push_back(dag.add(dag.mul(v0, w), dag.mul(v1, u)));
+        }
+      }
+    } break;
+    case VK_INTERP2D: {  // InterpTable2D::interp_impl (InterpTable2D.h:300-390): bicubic patch a = L Z R (get_amatrix, :253-298)
+      auto xy = L(0);
+      if (xy.size() != 2 || nd.ip.size() != 5) throw std::invalid_argument("lower: InterpTable2D takes (x, y) and ip = {nx, ny, kind, xeven, yeven}");
+      const int nx = nd.ip[0], ny = nd.ip[1], kind = nd.ip[2];
+      const bool cubic = kind == 0;
+      if (nx < 5) throw std::invalid_argument("X coordinates must be larger than 4");
+      if (ny < 5) throw std::invalid_argument("Y  coordinates must be larger than 4");
+      const size_t plane = (size_t) nx * ny;
+      if (nd.d.size() != (size_t) nx + ny + plane * (cubic ? 4 : 1))
+        throw std::invalid_argument("lower: InterpTable2D data size does not match nx, ny and the kind");
+      for (int i = 0; i + 1 < nx; i++)
+        if (nd.d[i + 1] < nd.d[i]) throw std::invalid_argument("X Coordinates must be in ascending order");
+      for (int i = 0; i + 1 < ny; i++)
+        if (nd.d[nx + i + 1] < nd.d[nx + i]) throw std::invalid_argument("Y Coordinates must be in ascending order");
+      auto axis_of = [&](const double* c, int n, int even) {
+        std::vector<double> a(n + 2);
+        a[0] = n;
+        a[1] = even ? 1.0 : 0.0;
+        std::copy(c, c + n, a.begin() + 2);
+        return dag.tab_add(a.data(), a.size());
+      };
+      const size_t xoff = axis_of(nd.d.data(), nx, nd.ip[3]), yoff = axis_of(nd.d.data() + nx, ny, nd.ip[4]);
+      size_t poff[4] = {0, 0, 0, 0};  // z, dz/dx, dz/dy, d2z/dxdy, each [ny][nx]
+      for (int q = 0; q < (cubic ? 4 : 1); q++) poff[q] = dag.tab_add(nd.d.data() + nx + ny + q * plane, plane);
+      const int x = xy[0], y = xy[1];
+      const int ex = dag.tabidx(x, xoff), ey = dag.tabidx(y, yoff);
+      const int x0 = dag.tabload(ex, xoff + 2), x1 = dag.tabload(ex, xoff + 3);
+      const int y0 = dag.tabload(ey, yoff + 2), y1 = dag.tabload(ey, yoff + 3);
+      const int xs = dag.sub(x1, x0), ys = dag.sub(y1, y0);
+      const int xf = dag.div(dag.sub(x, x0), xs), yf = dag.div(dag.sub(y, y0), ys);
+      const int cell = dag.add(dag.mulc(ey, (double) nx), ex);  // exact: indices are small integers
+      auto corner = [&](int q, int dx, int dy) { return dag.tabload(cell, poff[q] + (size_t) dy * nx + dx); };
+      if (cubic) {
+        // Z (InterpTable2D.h:291-293): rows (z, z, dz/dx, dz/dx) at x-corner (0, 1, 0, 1); columns (.., .., d/dy, d/dy) at y-corner
+        int Z[4][4];
+        const int sxy = dag.mul(xs, ys);
+        for (int r = 0; r < 4; r++)
+          for (int c = 0; c < 4; c++) {
+            const int dx = r & 1, dy = c & 1, wx = r >> 1, wy = c >> 1;
+            const int q = wx ? (wy ? 3 : 1) : (wy ? 2 : 0);
+            int v = corner(q, dx, dy);
+            if (wx && wy)
+              v = dag.mul(v, sxy);
+            else if (wx)
+              v = dag.mul(v, xs);
+            else if (wy)
+              v = dag.mul(v, ys);
+            Z[r][c] = v;
+          }
+        static const double Lm[4][4] = {{1, 0, 0, 0}, {0, 0, 1, 0}, {-3, 3, -2, -1}, {2, -2, 1, 1}};
+        static const double Rm[4][4] = {{1, 0, -3, 2}, {0, 0, 3, -2}, {0, 1, -2, 1}, {0, 0, -1, 1}};
+        int LZ[4][4], Am[4][4];
+        auto lin = [&](const double* w, const int* v, int stride) {
+          int s = -1;
+          for (int k = 0; k < 4; k++) {
+            if (w[k] == 0.0) continue;
+            const int term = dag.mulc(v[k * stride], w[k]);
+            s = s < 0 ? term : dag.add(s, term);
+          }
+          return s < 0 ? dag.constant(0.0) : s;
+        };
+        for (int r = 0; r < 4; r++)
+          for (int c = 0; c < 4; c++) LZ[r][c] = lin(Lm[r], &Z[0][c], 4);
+        for (int r = 0; r < 4; r++)
+          for (int c = 0; c < 4; c++) {
+            const double col[4] = {Rm[0][c], Rm[1][c], Rm[2][c], Rm[3][c]};
+            Am[r][c] = lin(col, &LZ[r][0], 1);
+          }
+        const int xf2 = dag.mul(xf, xf), yf2 = dag.mul(yf, yf);
+        const int xv[4] = {dag.constant(1.0), xf, xf2, dag.mul(xf2, xf)};
+        const int yv[4] = {dag.constant(1.0), yf, yf2, dag.mul(yf2, yf)};
+        int z = -1;
+        for (int r = 0; r < 4; r++) {
+          int row = -1;
+          for (int c = 0; c < 4; c++) {
+            const int term = dag.mul(Am[r][c], yv[c]);
+            row = row < 0 ? term : dag.add(row, term);
+          }
+          const int term = dag.mul(xv[r], row);
+          z = z < 0 ? term : dag.add(z, term);
+        }
+        out.push_back(z);
+      } else {  // InterpTable2D.h:363-388
+        const int z00 = corner(0, 0, 0), z10 = corner(0, 1, 0), z01 = corner(0, 0, 1), z11 = corner(0, 1, 1);
+        const int wx = dag.addc(dag.neg(xf), 1.0), wy = dag.addc(dag.neg(yf), 1.0);
+        const int lo = dag.add(dag.mul(z00, wx), dag.mul(z10, xf)), hi = dag.add(dag.mul(z01, wx), dag.mul(z11, xf));
+        out.push_back(dag.add(dag.mul(lo, wy), dag.mul(hi, yf)));
+      }
+    } break;
     case VK_MATVEC: {
       auto a = L(0);
       int cols = (int) a.size();
@@ -381,7 +562,9 @@ void ScalarFn::make_gradient() {
       case OP_APPCONST:
       case OP_SIGN:
       case OP_LT:
-      case OP_LE: break;
+      case OP_LE:
+      case OP_TABIDX:
+      case OP_TABLOAD: break;
       case OP_ADD:
         acc(a, yb);
         acc(b, yb);

@@ -109,6 +109,19 @@ struct SDag {
   };
   std::unordered_map<Key, int, KeyHash> cons;
 
+  // interpolation-table data referenced by OP_TABIDX / OP_TABLOAD nodes (offsets in `imm`); copies of a DAG carry it along
+  struct TabEntry {
+    size_t off, len;
+  };
+  std::vector<double> tabpool;
+  std::vector<TabEntry> tabs;
+  size_t tab_add(const double* p, size_t n);  // returns the offset; identical data are stored once
+  const TabEntry& tab_find(size_t off) const;  // the entry an offset falls in
+  // pool offset of a table node of `src` after its data have been copied into this DAG
+  double tab_import(const SDag& src, double imm);
+  int tabidx(int a, size_t axis_off);
+  int tabload(int idx, size_t base_off);
+
   int raw(uint16_t op, int a, int b, int c, double imm);
   bool is_const(int i) const { return n[i].op == OP_CONST; }
   double cval(int i) const { return n[i].imm; }
@@ -179,6 +192,7 @@ constexpr uint32_t PROG_CHUNK_BUNDLES = 64u;
 struct Program {
   std::vector<PInstr> code;  // 4 instructions per bundle, PK_END bundle last
   std::vector<double> consts;
+  std::vector<double> tables;  // the function's interpolation-table pool (SDag::tabpool); empty for most programs
   int nslots = 0;
   int nin = 0, nout = 0, nappconst = 0;
   int n_ops = 0;       // live instructions (for reporting)
@@ -219,6 +233,9 @@ struct AffineMaps {
   std::vector<int> kbase, kstride;  // per triplet: kkt_dest
 };
 LinkedProgram link_program(const Program& P, unsigned smem_budget, const AffineMaps* am = nullptr);
+
+// interval index of t on an axis stored as [n, even, coordinates...] (host copy of what the device does for OP_TABIDX)
+int table_interval(const double* axis, double t);
 
 std::vector<int> lower(const Graph& g, int root, const std::vector<int>& in, SDag& dag);
 ScalarFn lower_function(const Graph& g, int root);

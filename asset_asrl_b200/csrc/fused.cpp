@@ -250,6 +250,8 @@ struct DagCopy {
         case OP_NEG: map[i] = d.neg(m(nd.a)); break;
         case OP_ADDC: map[i] = d.addc(m(nd.a), nd.imm); break;
         case OP_MULC: map[i] = d.mulc(m(nd.a), nd.imm); break;
+        case OP_TABIDX:
+        case OP_TABLOAD: map[i] = d.raw(nd.op, m(nd.a), -1, -1, d.tab_import(s, nd.imm)); break;  // table data move with the node
         default: map[i] = d.raw(nd.op, m(nd.a), m(nd.b), m(nd.c), nd.imm); break;
       }
     }

@@ -44,8 +44,31 @@ __device__ __forceinline__ void put(const EvalIO& io, const int* __restrict__ de
     io.stage[~d] = v;
 }
 
-__device__ __forceinline__ double special_op(unsigned op, double a, double b, double c, double imm) {
+// interval of an axis stored as [n, evenly spaced, coordinates...] that holds t (InterpTable1D::get_telem,
+// /root/reference/src/VectorFunctions/CommonFunctions/InterpTable1D.h:180-197); same arithmetic as the specialised kernels
+__device__ __forceinline__ double table_interval_dev(const double* __restrict__ axis, double t) {
+  const int n = (int) __ldg(axis);
+  const double* __restrict__ ts = axis + 2;
+  int e;
+  if (__ldg(axis + 1) != 0.0) {
+    const double t0 = __ldg(ts);
+    e = __double2int_rz(__ddiv_rn(__dsub_rn(t, t0), __dsub_rn(__ldg(ts + 1), t0)));
+  } else {
+    // number of coordinates <= t, by descending powers of two
+    int pos = 0;
+    for (int step = 1 << (31 - __clz(n)); step > 0; step >>= 1) {
+      const int cand = pos + step;
+      if (cand <= n && __ldg(ts + cand - 1) <= t) pos = cand;
+    }
+    e = pos - 1;
+  }
+  return (double) max(min(e, n - 2), 0);
+}
+
+__device__ __forceinline__ double special_op(unsigned op, double a, double b, double c, double imm, const double* __restrict__ tab) {
   switch (op) {
+    case OP_TABIDX: return table_interval_dev(tab + (long long) imm, a);
+    case OP_TABLOAD: return __ldg(tab + (long long) imm + __double2int_rz(a));
     case OP_DIV: return a / b;
     case OP_INV: return 1.0 / a;
     case OP_SQRT: return sqrt(a);
@@ -199,7 +222,7 @@ __global__ void __launch_bounds__(256) k_eval_prog(const FnDev f, const EvalIO i
           const double b = ld_opnd(smem, i0.z, tid8);
           const double c3 = ld_opnd(smem, i1.y, tid8);
           const double imm = lds(smem, (i0.w >> 8) * 8u);
-          *reinterpret_cast<double*>(smem + op_addr(i0.x & 0x00FFFFFFu, tid8)) = special_op(op, a, b, c3, imm);
+          *reinterpret_cast<double*>(smem + op_addr(i0.x & 0x00FFFFFFu, tid8)) = special_op(op, a, b, c3, imm, P.tables);
         }
       }
     }

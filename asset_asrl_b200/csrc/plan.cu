@@ -438,6 +438,7 @@ int Plan::build(int dev, int rank_, int world_) {
     const AffineMaps am = function_affine(prob, fi);
     try {
       ScalarFn work = *t.fn;
+      const double* d_tables = nullptr;  // one copy of the function's interpolation tables for all its modes
       for (int mode = 0; mode < 5; mode++) {
         if (fr.role == ROLE_OBJ && (mode == FM_JAC || mode == FM_JAC_GRAD)) continue;
         ProgramSpec sp;
@@ -455,6 +456,14 @@ int Plan::build(int dev, int rank_, int world_) {
         if (!pd[mode].code || !pd[mode].consts) {
           last_error = "out of device memory for the program of " + fr.name;
           return (int) cudaErrorMemoryAllocation;
+        }
+        if (!P.tables.empty()) {
+          if (!d_tables) d_tables = dupload(P.tables);
+          if (!d_tables) {
+            last_error = "out of device memory for the interpolation tables of " + fr.name;
+            return (int) cudaErrorMemoryAllocation;
+          }
+          pd[mode].tables = d_tables;
         }
         pd[mode].nconst = (int) P.consts.size();
         pd[mode].nslots = L.nslots;

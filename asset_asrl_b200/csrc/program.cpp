@@ -373,6 +373,13 @@ Program emit_program_outs(ScalarFn& f, const std::vector<ProgOut>& outs) {
   P.nslots = std::max(nslots, 1);
   P.nappconst = maxapp + 1;
   if (nslots >= (1 << 21)) throw std::length_error("emit_program: too many slots");
+  if (P.n_special) {  // interpolation-table data travel with the program that reads them
+    for (const MOp& m: B.ops)
+      if (m.kind == PK_SPECIAL && (m.sop == OP_TABIDX || m.sop == OP_TABLOAD)) {
+        P.tables = dag.tabpool;
+        break;
+      }
+  }
   return P;
 }
 

@@ -52,6 +52,12 @@ enum Op : uint16_t {
   OP_FMA,    // v = a * b + c          (c index is stored in the imm bits)
   OP_OUT_F,  // f[dst] = value(a), J[dst][dir] = tangent(a)
   OP_OUT_G,  // g[dst] = value(a), H[dst][dir] = tangent(a)
+  // Interpolation tables (InterpTable1D.h / InterpTable2D.h of the reference).  The table data of a function sit in one
+  // pool of doubles (SDag::tabpool); `imm` is an offset into it.  Both have zero derivative: an interpolant is
+  // differentiated through its local coordinate, not through the choice of the interval.
+  OP_TABIDX,   // v = index of the interval of axis `imm` that holds a: pool[imm] = n, pool[imm+1] = evenly spaced ? 1 : 0,
+               //     pool[imm+2 ..] = n ascending coordinates; InterpTable1D::get_telem (InterpTable1D.h:180-197)
+  OP_TABLOAD,  // v = pool[imm + (int) a]
   OP_COUNT
 };
 

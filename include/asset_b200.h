@@ -119,6 +119,10 @@ long long ab_problem_tape_describe(const ab_problem* p, int t, char* buf, long l
 int ab_problem_program_stats(const ab_problem* p, int f, int mode, long long out[8]);
 /* Copies the (unlinked) program: 4 * bundles 16-byte instructions (asset_asrl_b200/csrc/expr.hpp: PInstr) and the constants. */
 int ab_problem_program_code(const ab_problem* p, int f, int mode, void* code, double* consts);
+/* The interpolation-table pool the program of function `f` reads (InterpTable1D / InterpTable2D data,
+ * /root/reference/src/VectorFunctions/CommonFunctions/InterpTable1D.h:18-29, InterpTable2D.h:14-36): copies up to `cap`
+ * doubles, returns the pool's length (0 for a function without tables) or a negative status. */
+long long ab_problem_program_tables(const ab_problem* p, int f, int mode, double* out, long long cap);
 /* PTX text of the specialised kernel the plan would assemble for function `f` in `mode` (asset_asrl_b200/csrc/jit.hpp):
  * `indexed` = 0 the affine variant run over the bulk of the mesh, 1 the indexed variant run over the mesh ends;
  * returns the full length, 0 if the function has no affine application range, or a negative status.

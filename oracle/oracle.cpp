@@ -184,6 +184,64 @@ static void unary_eval(int op, double imm, double x, double& f, double& d1, doub
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// interpolation tables: InterpTable1D.h:9-262, InterpTable2D.h:7-390 restated (own stencil derivatives, own interval
+// search, the reference's closed-form first and second derivatives of the interpolants)
+// ------------------------------------------------------------------------------------------------
+// weights of the five-point stencil for d/dc at c[i] over samples c[start .. start+5): solves sum_k w_k tau_k^r = [r == 1]
+static void stencil5(const double* c, int n, int i, int& start, double w[5]) {
+  if (i + 2 <= n - 1 && i - 2 >= 0)
+    start = i - 2;
+  else if (i < n - 1 - i)
+    start = 0;
+  else
+    start = n - 5;
+  const double step = std::fabs(c[i + (i < n - 1 ? 1 : -1)] - c[i]);
+  long double A[5][6];
+  for (int k = 0; k < 5; k++) {
+    const long double tau = ((long double) c[start + k] - c[i]) / step;
+    long double pw = 1;
+    for (int r = 0; r < 5; r++) {
+      A[r][k] = pw;
+      pw *= tau;
+    }
+  }
+  for (int r = 0; r < 5; r++) A[r][5] = (r == 1);
+  for (int col = 0; col < 5; col++) {  // Gauss-Jordan with partial pivoting
+    int piv = col;
+    for (int r = col + 1; r < 5; r++)
+      if (fabsl(A[r][col]) > fabsl(A[piv][col])) piv = r;
+    for (int k = 0; k < 6; k++) std::swap(A[col][k], A[piv][k]);
+    for (int r = 0; r < 5; r++) {
+      if (r == col) continue;
+      const long double f = A[r][col] / A[col][col];
+      for (int k = col; k < 6; k++) A[r][k] -= f * A[col][k];
+    }
+  }
+  for (int k = 0; k < 5; k++) w[k] = (double) (A[k][5] / A[k][k] / step);
+}
+// derivative along a strided axis: out[j*stride] = d/dc of v[j*stride], j < n
+static void stencil_axis(const double* c, int n, const double* v, double* out, size_t stride) {
+  for (int i = 0; i < n; i++) {
+    int start;
+    double w[5];
+    stencil5(c, n, i, start, w);
+    double s = 0;
+    for (int k = 0; k < 5; k++) s += w[k] * v[(size_t) (start + k) * stride];
+    out[(size_t) i * stride] = s;
+  }
+}
+static int interval_of(const double* c, int n, bool even, double t) {
+  int e;
+  if (even) {
+    const double q = (t - c[0]) / (c[1] - c[0]);
+    e = q < 0 ? 0 : (q > n ? n : (int) q);
+  } else {
+    e = (int) (std::upper_bound(c, c + n, t) - c) - 1;
+  }
+  return std::max(std::min(e, n - 2), 0);
+}
+
 struct Eval {
   const double* appc = nullptr;
   // fx = f(x); if J: J (orows x ir) assigned; if H: H (ir x ir) += Hessian of l.f
@@ -368,6 +426,104 @@ void Eval::outer(const Node& n, const Vec& Y, const std::vector<int>& off, doubl
           (*Hp)(i, 4 + j) += sg * l[o];
           (*Hp)(4 + j, i) += sg * l[o];
         }
+      }
+    } break;
+    case K_INTERP1D: {  // InterpFunction1D (InterpTable1D.h:322-400) over interp_impl (:199-262)
+      const int nt = n.ip[0], vlen = n.ip[1];
+      const bool cubic = n.ip[2] == 0, even = n.ip[3] != 0;
+      const double* ts = n.d.data();
+      const double* vs = ts + nt;  // [vlen][nt]
+      const double t = Y[0];
+      const int e = interval_of(ts, nt, even, t);
+      const double h = ts[e + 1] - ts[e], u = (t - ts[e]) / h;
+      Vec dv;
+      if (cubic) {  // slopes recomputed here (calc_derivs, :133-178), not taken from the description
+        dv.resize((size_t) vlen * nt);
+        for (int k = 0; k < vlen; k++) stencil_axis(ts, nt, vs + (size_t) k * nt, &dv[(size_t) k * nt], 1);
+      }
+      double h2 = 0;
+      for (int k = 0; k < vlen; k++) {
+        const double v0 = vs[(size_t) k * nt + e], v1 = vs[(size_t) k * nt + e + 1];
+        double f, d1, d2;
+        if (cubic) {
+          const double s0 = dv[(size_t) k * nt + e], s1 = dv[(size_t) k * nt + e + 1], u2 = u * u, u3 = u2 * u;
+          f = v0 * (2 * u3 - 3 * u2 + 1) + v1 * (-2 * u3 + 3 * u2) + s0 * ((u3 - 2 * u2 + u) * h) + s1 * ((u3 - u2) * h);
+          d1 = v0 * ((6 * u2 - 6 * u) / h) + v1 * ((-6 * u2 + 6 * u) / h) + s0 * (3 * u2 - 4 * u + 1) + s1 * (3 * u2 - 2 * u);
+          d2 = v0 * ((12 * u - 6) / (h * h)) + v1 * ((-12 * u + 6) / (h * h)) + s0 * ((6 * u - 4) / h) + s1 * ((6 * u - 2) / h);
+        } else {
+          f = v0 * (1 - u) + v1 * u;
+          d1 = (v1 - v0) / h;
+          d2 = 0;
+        }
+        fx[k] = f;
+        if (Jp) (*Jp)(k, 0) = d1;
+        if (Hp) h2 += l[k] * d2;
+      }
+      if (Hp) (*Hp)(0, 0) += h2;
+    } break;
+    case K_INTERP2D: {  // InterpFunction2D (InterpTable2D.h:428-485) over interp_impl (:300-390)
+      const int nx = n.ip[0], ny = n.ip[1];
+      const bool cubic = n.ip[2] == 0;
+      const double* xs = n.d.data();
+      const double* ys = xs + nx;
+      const double* zs = ys + ny;  // [ny][nx]
+      const double x = Y[0], y = Y[1];
+      const int ex = interval_of(xs, nx, n.ip[3] != 0, x), ey = interval_of(ys, ny, n.ip[4] != 0, y);
+      const double hx = xs[ex + 1] - xs[ex], hy = ys[ey + 1] - ys[ey];
+      const double xf = (x - xs[ex]) / hx, yf = (y - ys[ey]) / hy;
+      auto at = [&](const double* p, int dx, int dy) { return p[(size_t) (ey + dy) * nx + ex + dx]; };
+      double z, zx, zy, zxx, zxy, zyy;
+      if (cubic) {
+        const size_t plane = (size_t) nx * ny;
+        Vec dzx(plane), dzy(plane), dzxy(plane);  // calc_derivs (:122-211)
+        for (int c = 0; c < nx; c++) stencil_axis(ys, ny, zs + c, &dzy[c], nx);
+        for (int r = 0; r < ny; r++) {
+          stencil_axis(xs, nx, zs + (size_t) r * nx, &dzx[(size_t) r * nx], 1);
+          stencil_axis(xs, nx, &dzy[(size_t) r * nx], &dzxy[(size_t) r * nx], 1);
+        }
+        // Hermite patch in tensor form: sum over corners of value / x-slope / y-slope / twist times 1-D basis products;
+        // the same polynomial as xvec^T (L Z R) yvec of get_amatrix (:253-298)
+        auto basis = [](double s, double hh, double B[4], double D1[4], double D2[4]) {
+          const double s2 = s * s, s3 = s2 * s;  // value at 0, value at 1, slope at 0, slope at 1 (slopes scaled by the step)
+          B[0] = 2 * s3 - 3 * s2 + 1, B[1] = -2 * s3 + 3 * s2, B[2] = (s3 - 2 * s2 + s) * hh, B[3] = (s3 - s2) * hh;
+          D1[0] = (6 * s2 - 6 * s) / hh, D1[1] = -D1[0], D1[2] = 3 * s2 - 4 * s + 1, D1[3] = 3 * s2 - 2 * s;
+          D2[0] = (12 * s - 6) / (hh * hh), D2[1] = -D2[0], D2[2] = (6 * s - 4) / hh, D2[3] = (6 * s - 2) / hh;
+        };
+        double Bx[4], Dx[4], DDx[4], By[4], Dy[4], DDy[4];
+        basis(xf, hx, Bx, Dx, DDx);
+        basis(yf, hy, By, Dy, DDy);
+        z = zx = zy = zxx = zxy = zyy = 0;
+        for (int a = 0; a < 4; a++)
+          for (int b = 0; b < 4; b++) {
+            const int dx = a & 1, dy = b & 1;
+            const double* src = (a >> 1) ? ((b >> 1) ? dzxy.data() : dzx.data()) : ((b >> 1) ? dzy.data() : zs);
+            const double c = at(src, dx, dy);
+            z += c * Bx[a] * By[b];
+            zx += c * Dx[a] * By[b];
+            zy += c * Bx[a] * Dy[b];
+            zxx += c * DDx[a] * By[b];
+            zxy += c * Dx[a] * Dy[b];
+            zyy += c * Bx[a] * DDy[b];
+          }
+      } else {  // :363-388
+        const double z00 = at(zs, 0, 0), z10 = at(zs, 1, 0), z01 = at(zs, 0, 1), z11 = at(zs, 1, 1);
+        const double lo = z00 * (1 - xf) + z10 * xf, hi = z01 * (1 - xf) + z11 * xf;
+        z = lo * (1 - yf) + hi * yf;
+        zx = ((z10 - z00) * (1 - yf) + (z11 - z01) * yf) / hx;
+        zy = (hi - lo) / hy;
+        zxx = zyy = 0;
+        zxy = ((z11 - z01) - (z10 - z00)) / (hx * hy);
+      }
+      fx[0] = z;
+      if (Jp) {
+        (*Jp)(0, 0) = zx;
+        (*Jp)(0, 1) = zy;
+      }
+      if (Hp) {
+        (*Hp)(0, 0) += l[0] * zxx;
+        (*Hp)(0, 1) += l[0] * zxy;
+        (*Hp)(1, 0) += l[0] * zxy;
+        (*Hp)(1, 1) += l[0] * zyy;
       }
     } break;
     case K_CWISEPROD: {  // CwiseProduct.h

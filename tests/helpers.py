@@ -58,6 +58,69 @@ def expression_zoo():
     return z
 
 
+def interp_tables():
+    """Interpolation tables over smooth data: evenly and unevenly spaced axes, scalar and vector values, both kinds."""
+    te = np.linspace(-1.0, 2.0, 13)
+    tu = np.array([-1.0, -0.7, -0.55, -0.1, 0.0, 0.3, 0.35, 0.9, 1.4, 1.5, 2.0])
+    sc = lambda t: np.sin(1.3 * t) + 0.2 * t * t  # noqa: E731
+    vec = lambda t: np.stack([np.cos(t), np.exp(-0.5 * t), t ** 3 - t])  # noqa: E731
+    xs_e, ys_e = np.linspace(0.0, 1.8, 10), np.linspace(-1.0, 3.0, 9)
+    xs_u = np.array([0.0, 0.2, 0.4, 0.6, 0.8, 1.0, 1.2, 1.4, 1.6, 1.8]) ** 1.5
+    ys_u = np.array([-0.5, 0.0, 5.0, 10.0, 15.0, 20.0, 25.0, 30.0, 40.0, 50.0, 70.0]) / 20.0
+    surf = lambda x, y: np.sin(x[None, :] + 0.3 * y[:, None]) * (1.0 + 0.1 * y[:, None] ** 2) + x[None, :] ** 2  # noqa: E731
+    T = {}
+    for knd in ("cubic", "linear"):
+        T[f"1d_even_scalar_{knd}"] = vf.InterpTable1D(te, sc(te), kind=knd)
+        T[f"1d_uneven_scalar_{knd}"] = vf.InterpTable1D(tu, sc(tu), kind=knd)
+        T[f"1d_even_vector_{knd}"] = vf.InterpTable1D(te, vec(te), axis=1, kind=knd)
+        T[f"1d_uneven_vector_rows_{knd}"] = vf.InterpTable1D(np.concatenate([vec(tu).T, tu[:, None]], axis=1), kind=knd)
+        T[f"2d_even_{knd}"] = vf.InterpTable2D(xs_e, ys_e, surf(xs_e, ys_e), kind=knd)
+        T[f"2d_uneven_{knd}"] = vf.InterpTable2D(xs_u, ys_u, surf(xs_u, ys_u), kind=knd)
+        T[f"2d_mixed_{knd}"] = vf.InterpTable2D(xs_e, ys_u, surf(xs_e, ys_u), kind=knd)
+    return T
+
+
+def interp_zoo():
+    """Expression zoo entries over the tables (kept apart from expression_zoo so that the GPU tests of the table ops
+    live in a file of their own, tests/test_zz_gpu_tables.py)."""
+    A = vf.Arguments
+    x3 = A(3)
+    z = []
+    for nm, tab in interp_tables().items():
+        if nm.startswith("1d"):
+            lo, hi = tab.ts[0], tab.ts[-1]
+            f = tab(x3[0] * x3[1] + x3[2])  # coordinate = a nonlinear function of the inputs: chain rule through the table
+            if tab.vlen == 1:
+                f = vf.stack([f * x3[1], vf.sin(f)])
+
+            def gen(rng, lo=lo, hi=hi):
+                while True:
+                    x = rng.uniform(-1.2, 1.2, 3)
+                    if lo + 0.01 < x[0] * x[1] + x[2] < hi - 0.01:
+                        return x
+        else:
+            xl, xh, yl, yh = tab.xs[0], tab.xs[-1], tab.ys[0], tab.ys[-1]
+            f = tab(x3[0] * x3[2], x3[1] + x3[2]) * x3[0]
+
+            def gen(rng, xl=xl, xh=xh, yl=yl, yh=yh):
+                while True:
+                    x = np.array([rng.uniform(0.3, 1.5), rng.uniform(yl, yh), rng.uniform(0.0, 1.2)])
+                    if xl + 0.01 < x[0] * x[2] < xh - 0.01 and yl + 0.01 < x[1] + x[2] < yh - 0.01:
+                        return x
+        z.append(("interp_" + nm, f, gen))
+    return z
+
+
+def table_phase_zoo():
+    """Phases whose ODE reads interpolation tables (kept apart from phase_zoo for the same reason as interp_zoo)."""
+    return {
+        "minclimb_LGL5_highest_order_spline": lambda: W.make_phase("minclimb", "LGL5", 9, control_mode="HighestOrderSpline"),
+        "minclimb_LGL3": lambda: W.make_phase("minclimb", "LGL3", 8),
+        "minclimb_LGL7_block_constant": lambda: W.make_phase("minclimb", "LGL7", 5, control_mode="BlockConstant"),
+        "minclimb_Trapezoidal": lambda: W.make_phase("minclimb", "Trapezoidal", 10),
+    }
+
+
 def vdp_param_ode():
     """VanDerPol with mu as an ODE parameter (PV = 1)."""
     args = oc.ODEArguments(2, 1, 1)

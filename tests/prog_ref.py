@@ -15,8 +15,22 @@ PO_F, PO_J, PO_G, PO_H = range(4)
 _NAME = {v: k for k, v in OP.items()}
 
 
-def _special(op, a, b, c, imm):
+def _interval(axis, t):
+    """OP_TABIDX (csrc/tape.h): axis = [n, evenly spaced, coordinates...]."""
+    n, ts = int(axis[0]), axis[2:2 + int(axis[0])]
+    if axis[1] != 0.0:
+        e = int(np.trunc(np.clip((t - ts[0]) / (ts[1] - ts[0]), -1.0, float(n))))
+    else:
+        e = int(np.searchsorted(ts, t, side="right")) - 1
+    return float(max(min(e, n - 2), 0))
+
+
+def _special(op, a, b, c, imm, tables=None):
     n = _NAME[op]
+    if n == "TABIDX":
+        return _interval(tables[int(imm):], a)
+    if n == "TABLOAD":
+        return float(tables[int(imm) + int(a)])
     with np.errstate(all="ignore"):
         return {
             "DIV": lambda: a / b, "INV": lambda: 1.0 / a, "SQRT": lambda: math.sqrt(a), "EXP": lambda: math.exp(a),
@@ -30,7 +44,7 @@ def _special(op, a, b, c, imm):
         }[n]()
 
 
-def run_program(stats, code, consts, x, lam, appconst=()):
+def run_program(stats, code, consts, x, lam, appconst=(), tables=None):
     """Returns (F dict k->v, G dict i->v, T dict triplet_offset->v) of one application."""
     slots = np.zeros(stats["slots"] + 1)
 
@@ -62,7 +76,7 @@ def run_program(stats, code, consts, x, lam, appconst=()):
                 (F if ok == PO_F else G if ok == PO_G else T)[idx] = v
         elif kind == PK_SPECIAL:
             w = int(ins[0]["c"])
-            r = _special(w & 0xFF, val(ins[0]["a"]), val(ins[0]["b"]), val(ins[1]["a"]), consts[w >> 8])
+            r = _special(w & 0xFF, val(ins[0]["a"]), val(ins[0]["b"]), val(ins[1]["a"]), consts[w >> 8], tables)
             slots[(int(ins[0]["d"]) & 0x00FFFFFF) >> 3] = r
         else:
             raise ValueError(f"bad bundle kind {kind}")

@@ -28,6 +28,13 @@ class Kernel:
     """Parsed kernel: address groups and the instruction list of the body."""
 
     def __init__(self, ptx):
+        # interpolation tables: module-scope data the table ops address (jit.cpp: finish())
+        m = re.search(r"\.global \.align 16 \.b64 ab_tab\[(\d+)\] = \{([^}]*)\}", ptx)
+        self.table = None
+        if m:
+            words = [int(w, 16) for w in m.group(2).replace("\n", " ").split(",")]
+            assert len(words) == int(m.group(1))
+            self.table = np.array(words, dtype="<u8").view("<f8")
         body = ptx[ptx.index(".visible .entry"):]
         self.lines = [ln.strip() for ln in body.split("\n")]
         self.groups = {}  # %rgN -> (param index, byte stride per rel, byte offset)
@@ -137,6 +144,8 @@ class Kernel:
             elif op in ("ld.shared.f64", "ld.volatile.shared.f64"):
                 d, a = [t.strip() for t in rest.split(",", 1)]
                 R[d] = shared[saddr(a.strip())]
+            elif op == "{" and ".reg" in rest:  # a table op: a self-contained block with its own registers
+                self._block(rest, R, val)
             elif op == "{":  # call of a transcendental helper
                 fn = re.search(r"call\.uni \(po\), (\w+)", rest).group(1)
                 args = re.findall(r"st\.param\.f64 \[pi\d\], ([^;]+);", rest)
@@ -149,6 +158,69 @@ class Kernel:
                 continue  # prologue / address set-up, handled through the groups table
             else:
                 raise NotImplementedError("ptx_emu: " + ln)
+
+
+def _block(self, text, R, val):
+    """OP_TABIDX / OP_TABLOAD as jit.cpp emits them: integer index arithmetic and loads from the module's table."""
+    L, P = {}, {}
+
+    def get(tok):
+        tok = tok.strip()
+        if tok in L:
+            return L[tok]
+        if re.fullmatch(r"-?\d+", tok):
+            return int(tok)
+        return val(tok)
+
+    def put(tok, v):
+        if tok in L:
+            L[tok] = v
+        else:
+            R[tok] = v
+
+    for st in text.strip().rstrip("}").split(";"):
+        st = st.strip()
+        if not st:
+            continue
+        op, _, rest = st.partition(" ")
+        a = [t.strip() for t in rest.split(",")]
+        if op == ".reg":
+            L[rest.split()[-1]] = 0
+        elif op == "mov.u64":
+            assert a[1] == "ab_tab"
+            L[a[0]] = 0  # byte offset into the table
+        elif op == "mov.s32":
+            L[a[0]] = get(a[1])
+        elif op == "cvt.rzi.s32.f64":
+            x = get(a[1])
+            L[a[0]] = 0 if x != x else int(max(min(x, 2147483647.0), -2147483648.0))
+        elif op == "mad.wide.s32":
+            L[a[0]] = get(a[1]) * get(a[2]) + get(a[3])
+        elif op == "ld.global.nc.f64":
+            m = re.fullmatch(r"\[(%\w+)\+(-?\d+)\]", a[1])
+            addr = L[m.group(1)] + int(m.group(2))
+            assert addr % 8 == 0 and 0 <= addr // 8 < self.table.size, "table access out of range"
+            put(a[0], float(self.table[addr // 8]))
+        elif op in ("add.s32", "sub.s32", "min.s32", "max.s32"):
+            x, y = get(a[1]), get(a[2])
+            L[a[0]] = {"add.s32": x + y, "sub.s32": x - y, "min.s32": min(x, y), "max.s32": max(x, y)}[op]
+        elif op == "setp.le.s32":
+            P[a[0]] = get(a[1]) <= get(a[2])
+        elif op == "setp.le.and.f64":
+            P[a[0]] = (get(a[1]) <= get(a[2])) and P[a[3]]
+        elif op == "selp.s32":
+            L[a[0]] = get(a[1]) if P[a[3]] else get(a[2])
+        elif op == "sub.rn.f64":
+            put(a[0], get(a[1]) - get(a[2]))
+        elif op == "div.rn.f64":
+            put(a[0], get(a[1]) / get(a[2]))
+        elif op == "cvt.rn.f64.s32":
+            put(a[0], float(get(a[1])))
+        else:
+            raise NotImplementedError("ptx_emu block: " + st)
+
+
+Kernel._block = _block
 
 
 def _cmp(op, rest, R, preds, val):

@@ -15,9 +15,9 @@ def tape_block_eval(nlp):
 
     def ev(f, fi, x, lam, appc):
         if f not in progs:
-            progs[f] = nlp.program(f, 4)
-        st, code, consts = progs[f]
-        F, G, T = run_program(st, code, consts, x, lam, appc)
+            progs[f] = nlp.program(f, 4) + (nlp.program_tables(f, 4),)
+        st, code, consts, tables = progs[f]
+        F, G, T = run_program(st, code, consts, x, lam, appc, tables=tables)
         fx, jx, gx, hx = dense_blocks(fi, F, G, T)
         if fi["role"] == 0:  # objectives scatter no Jacobian triplets: recover the gradient row from G (= lam * df/dx)
             jx = (gx / lam[0]).reshape(1, -1) if lam[0] != 0 else jx

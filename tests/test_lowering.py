@@ -8,16 +8,17 @@ import numpy as np
 import pytest
 
 import oracle
-from helpers import expression_zoo, phase_zoo, problem_inputs, rel_err, TOL
+from helpers import expression_zoo, interp_zoo, phase_zoo, table_phase_zoo, problem_inputs, rel_err, TOL
 from ref_assembly import assemble
 from prog_ref import run_program, dense_blocks
 from asset_asrl_b200.Solvers import NonLinearProgram
 
 GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "collocation_functions.json")))
 ZOO = phase_zoo()
+ZOO.update(table_phase_zoo())
 
 
-@pytest.mark.parametrize("name,fun,gen", expression_zoo(), ids=[z[0] for z in expression_zoo()])
+@pytest.mark.parametrize("name,fun,gen", expression_zoo() + interp_zoo(), ids=[z[0] for z in expression_zoo() + interp_zoo()])
 def test_tape_matches_oracle(name, fun, gen):
     rng = np.random.default_rng(5)
     ir, orr = fun.IRows(), fun.ORows()
@@ -27,9 +28,10 @@ def test_tape_matches_oracle(name, fun, gen):
     fi = nlp.function_info(0)
     for mode in (4, 3, 1, 0):
         st, code, consts = nlp.program(0, mode)
+        tables = nlp.program_tables(0, mode)
         for _ in range(3):
             x, lam = gen(rng), rng.uniform(-1, 1, orr)
-            f, J, g, H = dense_blocks(fi, *run_program(st, code, consts, x, lam))
+            f, J, g, H = dense_blocks(fi, *run_program(st, code, consts, x, lam, tables=tables))
             fx, jx, gx, hx = oracle.computeall("expr " + fun.describe(), x, lam)
             assert rel_err(f, fx) < TOL
             if mode >= 3:

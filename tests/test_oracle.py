@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 import oracle
-from helpers import expression_zoo, rel_err, vf, oc, TOL
+from helpers import expression_zoo, interp_zoo, rel_err, vf, oc, TOL
 from asset_asrl_b200 import workloads as W
 
 GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "collocation_functions.json")))
@@ -42,7 +42,7 @@ def fd_check(desc, x, lam, appc=None, jtol=1e-6, htol=1e-5):
     assert np.abs(hx - hx.T).max() <= 1e-12 * max(np.abs(hx).max(), 1.0)
 
 
-@pytest.mark.parametrize("name,fun,gen", expression_zoo(), ids=[z[0] for z in expression_zoo()])
+@pytest.mark.parametrize("name,fun,gen", expression_zoo() + interp_zoo(), ids=[z[0] for z in expression_zoo() + interp_zoo()])
 def test_expression_derivatives(name, fun, gen):
     rng = np.random.default_rng(11)
     for _ in range(3):
@@ -113,3 +113,80 @@ def test_quaternion_product_known_answers():
         assert min(np.abs(fx - want).max(), np.abs(fx + want).max()) < 1e-14
         fx, _, _, _ = oracle.computeall("expr " + rot.describe(), np.concatenate([q1, v]), np.zeros(3))
         assert np.abs(fx - Rotation.from_quat(q1).apply(v)).max() < 1e-14
+
+
+def _eval(fun, x, lam):
+    return oracle.computeall("expr " + fun.describe(), np.asarray(x, dtype=np.float64), np.asarray(lam, dtype=np.float64))
+
+
+@pytest.mark.parametrize("spacing", ["even", "uneven"])
+def test_interp_table_1d_known_answers(spacing):
+    """InterpTable1D (InterpTable1D.h:133-262): the five-point slopes are exact for polynomials up to degree four and a
+    cubic Hermite segment reproduces a cubic, so data sampled from a cubic come back exactly, with both derivatives;
+    general data agree with scipy's CubicHermiteSpline given the same slopes, linear tables with np.interp; the central
+    stencil on an even axis is the textbook (1, -8, 0, 8, -1) / 12h."""
+    from scipy.interpolate import CubicHermiteSpline
+    ts = np.linspace(-1.0, 2.0, 13) if spacing == "even" else np.array([-1.0, -0.7, -0.55, -0.1, 0.0, 0.3, 0.35, 0.9, 1.4, 1.5, 2.0])
+    p = np.polynomial.Polynomial([0.3, -1.1, 0.7, 0.45])
+    tab = vf.InterpTable1D(ts, p(ts), kind="cubic")
+    assert tab.teven == (spacing == "even")
+    f = tab.vf()
+    for t in np.random.default_rng(2).uniform(ts[0], ts[-1], 12):
+        fx, jx, _, hx = _eval(f, [t], [1.0])
+        assert abs(fx[0] - p(t)) < 2e-14 and abs(jx[0, 0] - p.deriv()(t)) < 2e-13 and abs(hx[0, 0] - p.deriv(2)(t)) < 3e-12
+        v, dv, d2v = tab.interp_deriv2(t)  # the host evaluation of the front end against the oracle
+        assert abs(v[0] - fx[0]) < 1e-14 and abs(dv[0] - jx[0, 0]) < 1e-13 and abs(d2v[0] - hx[0, 0]) < 1e-12
+    g = np.sin(1.3 * ts) + 0.2 * ts * ts
+    tab = vf.InterpTable1D(ts, g, kind="cubic")
+    if spacing == "even":
+        h = ts[1] - ts[0]
+        want = (g[:-4] - 8 * g[1:-3] + 8 * g[3:-1] - g[4:]) / (12 * h)
+        assert np.abs(tab.dvs_dts[0, 2:-2] - want).max() < 1e-13
+    ref = CubicHermiteSpline(ts, g, tab.dvs_dts[0])
+    lin = vf.InterpTable1D(ts, g, kind="linear")
+    for t in np.random.default_rng(3).uniform(ts[0], ts[-1], 12):
+        fx, jx, _, hx = _eval(tab.vf(), [t], [1.0])
+        assert abs(fx[0] - ref(t)) < 1e-14 and abs(jx[0, 0] - ref.derivative()(t)) < 1e-13 and abs(hx[0, 0] - ref.derivative(2)(t)) < 1e-11
+        fx, jx, _, hx = _eval(lin.vf(), [t], [1.0])
+        assert abs(fx[0] - np.interp(t, ts, g)) < 1e-14 and hx[0, 0] == 0.0
+    # outside the table the end segments extrapolate (get_telem clamps, :193-196)
+    fx, _, _, _ = _eval(lin.vf(), [ts[-1] + 0.25], [1.0])
+    assert abs(fx[0] - (g[-1] + 0.25 * (g[-1] - g[-2]) / (ts[-1] - ts[-2]))) < 1e-14
+
+
+@pytest.mark.parametrize("spacing", ["even", "uneven"])
+def test_interp_table_2d_known_answers(spacing):
+    """InterpTable2D (InterpTable2D.h:122-390): data sampled from a polynomial of degree three in x and in y come back
+    exactly with gradient and Hessian; general data agree with two passes of scipy's CubicHermiteSpline over the same
+    node derivatives (a bicubic Hermite patch is the tensor product of the one-dimensional ones); the linear kind is
+    bilinear interpolation."""
+    from scipy.interpolate import CubicHermiteSpline
+    if spacing == "even":
+        xs, ys = np.linspace(0.0, 1.8, 10), np.linspace(-1.0, 3.0, 9)
+    else:
+        xs = np.array([0.0, 0.2, 0.4, 0.6, 0.8, 1.0, 1.2, 1.4, 1.6, 1.8]) ** 1.5
+        ys = np.array([-0.5, 0.0, 5.0, 10.0, 15.0, 20.0, 25.0, 30.0, 40.0, 50.0, 70.0]) / 20.0
+    px, py = np.polynomial.Polynomial([0.2, 1.0, -0.6, 0.3]), np.polynomial.Polynomial([-0.4, 0.5, 0.25, -0.1])
+    tab = vf.InterpTable2D(xs, ys, py(ys)[:, None] * px(xs)[None, :], kind="cubic")
+    assert tab.xeven == (spacing == "even") and tab.yeven == (spacing == "even")
+    rng = np.random.default_rng(4)
+    for _ in range(10):
+        x, y = rng.uniform(xs[0], xs[-1]), rng.uniform(ys[0], ys[-1])
+        fx, jx, _, hx = _eval(tab.vf(), [x, y], [1.0])
+        assert abs(fx[0] - px(x) * py(y)) < 1e-13
+        assert np.abs(jx[0] - [px.deriv()(x) * py(y), px(x) * py.deriv()(y)]).max() < 1e-12
+        want = np.array([[px.deriv(2)(x) * py(y), px.deriv()(x) * py.deriv()(y)], [px.deriv()(x) * py.deriv()(y), px(x) * py.deriv(2)(y)]])
+        assert np.abs(hx - want).max() < 1e-10
+    Z = np.sin(xs[None, :] + 0.3 * ys[:, None]) * (1.0 + 0.1 * ys[:, None] ** 2) + xs[None, :] ** 2
+    tab = vf.InterpTable2D(xs, ys, Z, kind="cubic")
+    lin = vf.InterpTable2D(xs, ys, Z, kind="linear")
+    for _ in range(10):
+        x, y = rng.uniform(xs[0], xs[-1]), rng.uniform(ys[0], ys[-1])
+        # along x at every y node: value and y-slope; then along y
+        vals = np.array([CubicHermiteSpline(xs, Z[j], tab.dzxs[j])(x) for j in range(ys.size)])
+        slopes = np.array([CubicHermiteSpline(xs, tab.dzys[j], tab.dzys_dxs[j])(x) for j in range(ys.size)])
+        fx, _, _, _ = _eval(tab.vf(), [x, y], [1.0])
+        assert abs(fx[0] - CubicHermiteSpline(ys, vals, slopes)(y)) < 1e-13
+        fx, _, _, _ = _eval(lin.vf(), [x, y], [1.0])
+        row = np.array([np.interp(x, xs, Z[j]) for j in range(ys.size)])
+        assert abs(fx[0] - np.interp(y, ys, row)) < 1e-14

@@ -26,6 +26,9 @@ CASES = {
     "vanderpol_LGL5": lambda: W.make_phase("vanderpol", "LGL5", 60),
     "hypersens_LGL5": lambda: W.make_phase("hypersens", "LGL5", 60),
     "brachistochrone_LGL3": lambda: W.make_phase("brachistochrone", "LGL3", 60),
+    # interpolation tables inside the ODE: table ops and their module-scope data in the fused kernels
+    "minclimb_LGL5_highest_order_spline": lambda: W.make_phase("minclimb", "LGL5", 60, control_mode="HighestOrderSpline"),
+    "minclimb_LGL3": lambda: W.make_phase("minclimb", "LGL3", 60),
 }
 
 

@@ -346,6 +346,22 @@ class NonLinearProgram:
             res[nm] = [(int(out[2 * k]), int(out[2 * k + 1])) for k in range(n)]
         return res
 
+    def input_ranges(self):
+        """{"X" | "LE" | "LI": [(lo, hi), ...]}: what the functions of this problem read of the iterate -- everything for an
+        ordinary problem, the rank's segments + halo + far variables for a windowed one (ab_problem_input_ranges; the plan
+        keeps its own copy, ab_plan_input_ranges, which ``eval_host_sharded(sliced=True)`` uploads)."""
+        res = {}
+        for w, nm in enumerate(("X", "LE", "LI")):
+            if self.plan:
+                call = lambda out, cap: lib.ab_plan_input_ranges(self.plan, w, out, cap)  # noqa: E731
+            else:
+                call = lambda out, cap: lib.ab_problem_input_ranges(self.h, w, out, cap)  # noqa: E731
+            n = _lib.check(call(None, 0))
+            out = (C.c_longlong * max(2 * n, 2))()
+            _lib.check(call(out, n))
+            res[nm] = [(int(out[2 * k]), int(out[2 * k + 1])) for k in range(n)]
+        return res
+
     def cut_pack(self):
         _lib.check0(lib.ab_plan_cut_pack(self.plan))
 
@@ -453,11 +469,11 @@ class NonLinearProgram:
         _lib.check0(lib.ab_plan_eval_host(self.plan, mode, float(ObjScale), g(X), g(LE), g(LI), g(val), g(PGX), g(AGX),
                                           g(FXE), g(FXI), g(KKT)))
 
-    def eval_host_sharded(self, mode, ObjScale, X, LE, LI, val, PGX, AGX, FXE, FXI, KKT, compact=False):
-        """eval_host for a sharded plan: H2D of the (replicated) iterate, evaluation, cut-set all-reduce, D2H of this
-        rank's output ranges only."""
+    def eval_host_sharded(self, mode, ObjScale, X, LE, LI, val, PGX, AGX, FXE, FXI, KKT, compact=False, sliced=False):
+        """eval_host for a sharded plan: H2D of the iterate (the whole of it, or with ``sliced`` only the ranges this
+        rank's functions read, see input_ranges), evaluation, cut-set all-reduce, D2H of this rank's output ranges only."""
         g = _lib.dptr
-        _lib.check0(lib.ab_plan_set_inputs(self.plan, g(X), g(LE), g(LI)))
+        _lib.check0((lib.ab_plan_set_inputs_sliced if sliced else lib.ab_plan_set_inputs)(self.plan, g(X), g(LE), g(LI)))
         self.eval_device(mode, ObjScale)
         if compact:  # the arrays hold this rank's output ranges back to back (see output_ranges)
             _lib.check0(lib.ab_plan_get_outputs_packed(self.plan, g(KKT), g(PGX), g(AGX), g(FXE), g(FXI), g(val)))

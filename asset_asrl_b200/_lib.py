@@ -97,6 +97,9 @@ SIGNATURES = {
     "ab_problem_gather_sizes": (_i, [_vp, _i, _i, _llp]),
     "ab_problem_gather": (_i, [_vp, _i, _i, _llp, _ip, _ip]),
     "ab_plan_set_inputs": (_i, [_vp, _dp, _dp, _dp]),
+    "ab_plan_set_inputs_sliced": (_i, [_vp, _dp, _dp, _dp]),
+    "ab_plan_input_ranges": (_ll, [_vp, _i, _llp, _ll]),
+    "ab_problem_input_ranges": (_ll, [_vp, _i, _llp, _ll]),
     "ab_plan_set_solver_coeffs": (_i, [_vp, _dp]),
     "ab_plan_eval": (_i, [_vp, _i, _d]),
     "ab_plan_sync": (_i, [_vp]),

@@ -222,6 +222,19 @@ int ab_problem_window_far_vars(const ab_problem* p, int* out, int cap) {
   return (int) v.size();
 }
 
+long long ab_problem_input_ranges(const ab_problem* p, int which, long long* out, long long cap) {
+  try {
+    const auto r = p->p.input_ranges(which);
+    for (size_t k = 0; k < r.size() && (long long) k < cap; k++) {
+      out[2 * k] = r[k].first;
+      out[2 * k + 1] = r[k].second;
+    }
+    return (long long) r.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
+
 int ab_problem_analyze(ab_problem* p) {
   AB_TRY
   p->p.analyze();
@@ -791,6 +804,28 @@ int ab_plan_set_inputs(ab_plan* plan, const double* X, const double* LE, const d
   if (X) PLAN_CUDA(cudaMemcpyAsync(P.d_X, X, sizeof(double) * P.prob.nvars, cudaMemcpyHostToDevice, P.stream));
   if (LE && P.prob.neq) PLAN_CUDA(cudaMemcpyAsync(P.d_LE, LE, sizeof(double) * P.prob.neq, cudaMemcpyHostToDevice, P.stream));
   if (LI && P.prob.niq) PLAN_CUDA(cudaMemcpyAsync(P.d_LI, LI, sizeof(double) * P.prob.niq, cudaMemcpyHostToDevice, P.stream));
+  return AB_OK;
+}
+long long ab_plan_input_ranges(const ab_plan* plan, int which, long long* out, long long cap) {
+  if (which < 0 || which > 2) return fail(AB_ERR_INVALID, "which must be 0 (X), 1 (LE) or 2 (LI)");
+  const auto& r = plan->plan.in_ranges[which];
+  for (size_t k = 0; k < r.size() && (long long) k < cap; k++) {
+    out[2 * k] = r[k].first;
+    out[2 * k + 1] = r[k].second;
+  }
+  return (long long) r.size();
+}
+int ab_plan_set_inputs_sliced(ab_plan* plan, const double* X, const double* LE, const double* LI) {
+  Plan& P = plan->plan;
+  PLAN_CUDA(cudaSetDevice(P.device));
+  const double* host[3] = {X, LE, LI};
+  double* dev[3] = {P.d_X, P.d_LE, P.d_LI};
+  for (int w = 0; w < 3; w++) {
+    if (!host[w]) continue;
+    for (const auto& r: P.in_ranges[w])
+      PLAN_CUDA(cudaMemcpyAsync(dev[w] + r.first, host[w] + r.first, sizeof(double) * (size_t) (r.second - r.first), cudaMemcpyHostToDevice,
+                                P.stream));
+  }
   return AB_OK;
 }
 int ab_plan_set_solver_coeffs(ab_plan* plan, const double* c) {

@@ -477,4 +477,38 @@ RankPartition make_partition(const Problem& prob, int rank, int world) {
   return P;
 }
 
+std::vector<std::pair<long long, long long>> Problem::input_ranges(int which, long long gap) const {
+  if (which < 0 || which > 2) throw std::invalid_argument("input_ranges: which must be 0 (X), 1 (LE) or 2 (LI)");
+  const long long n = which == 0 ? nvars : which == 1 ? neq : niq;
+  std::vector<std::pair<long long, long long>> out;
+  if (n <= 0) return out;
+  if (!win.on) {
+    out.emplace_back(0, n);
+    return out;
+  }
+  std::vector<unsigned char> used((size_t) n, 0);
+  for (const FuncRec& fr: funcs) {
+    if (which == 0) {
+      for (int v: fr.vindex) used.at((size_t) v) = 1;
+    } else if (fr.role == which) {
+      for (int c: fr.cindex) used.at((size_t) c) = 1;
+    }
+  }
+  long long i = 0;
+  while (i < n) {
+    if (!used[(size_t) i]) {
+      i++;
+      continue;
+    }
+    long long hi = i + 1, last = i;  // grow while the next used element is within `gap`
+    while (hi < n && hi - last <= gap) {
+      if (used[(size_t) hi]) last = hi;
+      hi++;
+    }
+    out.emplace_back(i, last + 1);
+    i = last + 1;
+  }
+  return out;
+}
+
 }  // namespace ab

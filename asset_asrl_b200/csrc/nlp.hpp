@@ -109,6 +109,12 @@ struct Problem {
   // Restricts the function list to the window (before analyze()); throws if the kept or owned applications of a function
   // are not one contiguous range.
   void window(long long mesh_vars, int seg_vars, long long nseg, long long seg_lo, long long seg_hi, int halo);
+
+  // Index ranges [lo, hi) of X (which = 0), LE (1) or LI (2) that the problem's functions read: what a rank has to receive
+  // of the iterate each step.  The whole array for an ordinary problem; for a windowed problem the variables / multiplier
+  // rows of the kept applications (own segments + halo + far variables), runs closer than `gap` elements joined into one
+  // copy.  Ascending, disjoint.
+  std::vector<std::pair<long long, long long>> input_ranges(int which, long long gap = 512) const;
 };
 
 constexpr int LARGE_FANIN = 96;

@@ -904,6 +904,7 @@ int Plan::build(int dev, int rank_, int world_) {
       return (int) cudaErrorMemoryAllocation;
     }
   }
+  for (int w = 0; w < 3; w++) in_ranges[w] = prob.input_ranges(w);
   if (release_windowed && !getenv("ASSET_B200_KEEP_HOST_ANALYSIS")) {
     // assemble the fused kernels now (a piece that needs more shared memory than a block has re-cuts the rows, which
     // reads the analysis), then let the analysis go

@@ -138,6 +138,9 @@ struct Plan {
   int cut_unpack();  // after the all-reduce: the owner keeps the sum, other contributors clear their partial
   // windowed plans (Problem::window): this rank's share of one long phase, analysed locally
   bool windowed = false;
+  // what this plan's kernels read of X / LE / LI (Problem::input_ranges, taken before the analysis is released): a rank of
+  // a windowed plan receives these ranges of the iterate each step, not the whole iterate
+  std::vector<std::pair<long long, long long>> in_ranges[3];
   long long win_f_b = 0, win_f_e = 0;  // fused threads of the owned segments, relative to t_lo
   // Windowed plans: once everything is uploaded and the fused kernels are assembled, the plan's copy of the analysis
   // (pattern, triplet locations, destination maps, gather lists, index maps: ~20 KB per segment) is released -- eight

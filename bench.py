@@ -45,6 +45,8 @@ def parse_args():
                          "leg, the roofline bytes and e2e are evalKKT's and are skipped for the others)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--full-upload", action="store_true",
+                    help="windows sharding: upload the whole iterate on every rank each step instead of the rank's slice")
     ap.add_argument("--no-parity", action="store_true", help="skip the (untimed) oracle-window comparison before the timed region")
     ap.add_argument("--shard", default="windows", choices=["windows", "one-phase", "phases"],
                     help="N > 1: one phase of N x segments split across the ranks -- 'windows' (default): every rank analyses "
@@ -430,10 +432,44 @@ def run_b200(a):
             return torch.empty(max(nel, 1), dtype=torch.float64).pin_memory().numpy()[:nel]
         hX, hLE, hLI = pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"])
         hX[:], hLE[:], hLI[:] = X, LE, LI
+        h2d = 8 * (d["nvars"] + d["neq"] + d["niq"])
+        upload_note = "pinned host X/LE/LI in (replicated)"
         if sharded:  # compact pinned buffers holding this rank's output ranges only
             rg = nlp.output_ranges()
             out = [pinned(max(sum(hi - lo for (lo, hi) in rg[k]), 1)) for k in ("val", "PGX", "AGX", "FXE", "FXI", "KKT")]
             host_call = lambda *args: nlp.eval_host_sharded(*args, compact=True)  # noqa: E731
+            if windows and not a.full_upload:
+                # A rank of a windowed plan needs its own segments' slice of the iterate (+ halo, + far variables), not
+                # the phase's: upload only the ranges its functions read.  Checked here before it is timed: the device
+                # copy of the iterate is poisoned with NaN, then a sliced evaluation must reproduce the outputs of a
+                # full-upload evaluation bit for bit; otherwise the run falls back to the full upload and says so.
+                ok = 0
+                try:
+                    host_call(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
+                    nlp.sync()
+                    want = [o.copy() for o in out]
+                    for nm in ("X", "LE", "LI"):
+                        t = nlp.device_tensor(nm)
+                        if t.numel():
+                            t.fill_(float("nan"))
+                    torch.cuda.synchronize()
+                    nlp.eval_host_sharded(EVAL_KKT, 1.0, hX, hLE, hLI, *out, compact=True, sliced=True)
+                    nlp.sync()
+                    ok = int(all(np.array_equal(w_, o_) for w_, o_ in zip(want, out)))
+                except Exception as e:  # noqa: BLE001 - any failure of the new path means: use the old one
+                    upload_note = f"sliced upload failed ({type(e).__name__}: {e}); " + upload_note
+                flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                if int(flag.item()) == 1:
+                    host_call = lambda *args: nlp.eval_host_sharded(*args, compact=True, sliced=True)  # noqa: E731
+                    ir_ = nlp.input_ranges()
+                    h2d = 8 * sum(hi - lo for rr in ir_.values() for (lo, hi) in rr)
+                    upload_note = ("pinned host X/LE/LI, of which only the ranges this rank's functions read are copied "
+                                   f"({sum(len(rr) for rr in ir_.values())} copies; checked against a full upload with the device iterate poisoned)")
+                elif ok == 1:
+                    upload_note = "sliced upload disagreed with the full upload on another rank; " + upload_note
+                elif "failed" not in upload_note:
+                    upload_note = "sliced upload did not reproduce the full upload's outputs; " + upload_note
         else:
             out = [pinned(1), pinned(d["nvars"]), pinned(d["nvars"]), pinned(d["neq"]), pinned(d["niq"]), pinned(d["nnz"])]
             host_call = nlp.eval_host
@@ -454,9 +490,9 @@ def run_b200(a):
         note = "ab_plan_eval_host: pinned host X/LE/LI in, val/PGX/AGX/FXE/FXI/KKT values out"
         if sharded:
             d2h = 8 * sum(hi - lo for rr in nlp.output_ranges().values() for (lo, hi) in rr)
-            note = ("per rank: pinned host X/LE/LI in (replicated), evaluation of the rank's share, NCCL cut-set reduce, "
+            note = ("per rank: " + upload_note + ", evaluation of the rank's share, NCCL cut-set reduce, "
                     "the rank's output ranges out; bytes are rank 0's")
-        e2e = {"value": world * a.segments / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * (d["nvars"] + d["neq"] + d["niq"]),
+        e2e = {"value": world * a.segments / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3, "steps": ksteps, "note": note}
 
     cpu = None

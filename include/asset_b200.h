@@ -216,6 +216,16 @@ int ab_partition_cut(const ab_partition* q, int array, int* target, int* owner, 
 int ab_problem_gather_sizes(const ab_problem* p, int array, int level, long long out[3] /* targets, sources, stage size */);
 int ab_problem_gather(const ab_problem* p, int array, int level, long long* ptr, int* src, int* target);
 int ab_plan_set_inputs(ab_plan* plan, const double* X, const double* LE, const double* LI); /* host -> device */
+/* The index ranges [lo, hi) of X (which = 0), LE (1), LI (2) the problem's functions read, as pairs in out[0 .. 2*cap);
+ * returns the number of ranges.  The whole array for an ordinary problem; for a windowed problem (ab_problem_window) the
+ * rank's own segments, its halo and the far variables.  The reference hands every thread the whole iterate
+ * (/root/reference/src/Solvers/NonLinearProgram.cpp:473-537); a rank with its own memory needs only this slice of it.
+ * ab_plan_input_ranges: the same for a plan (kept after a windowed plan has released its host analysis). */
+long long ab_problem_input_ranges(const ab_problem* p, int which, long long* out, long long cap);
+long long ab_plan_input_ranges(const ab_plan* plan, int which, long long* out, long long cap);
+/* ab_plan_set_inputs that copies only those ranges of the (full-length) host arrays: the per-step host -> device traffic of
+ * a rank follows its share of the phase, not the phase. */
+int ab_plan_set_inputs_sliced(ab_plan* plan, const double* X, const double* LE, const double* LI);
 int ab_plan_set_solver_coeffs(ab_plan* plan, const double* coeffs /* n_solver_entries */);
 int ab_plan_eval(ab_plan* plan, int mode, double obj_scale); /* asynchronous on the plan's stream */
 int ab_plan_sync(ab_plan* plan);

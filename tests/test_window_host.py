@@ -77,3 +77,38 @@ def test_bench_parity_windows_on_a_windowed_problem():
         worst = wc.compare(wc.extract(out), 0.7, X, LE, LI, sc)
         for k in ("KKT", "AGX", "PGX", "FXE", "FXI"):
             assert worst[k] < 1e-13, (r, k, worst)
+
+
+@pytest.mark.parametrize("ode,mode,nseg,world", [("lowthrust", "LGL5", 4000, 8), ("vanderpol", "LGL3", 3000, 3)])
+def test_input_ranges_cover_what_a_rank_reads_and_follow_its_share(ode, mode, nseg, world):
+    """ab_problem_input_ranges: the slice of X / LE / LI a rank has to receive each step (sliced upload of
+    eval_host_sharded).  Everything for the whole problem; for a window every index a kept application reads lies in a
+    range, ranges are ascending and disjoint, and their total is the rank's share plus halo -- not the phase."""
+    ph = W.make_phase(ode, mode, nseg)
+    whole = ph.transcribe()
+    d = whole.dims()
+    full = {"X": d["nvars"], "LE": d["neq"], "LI": d["niq"]}
+    assert whole.input_ranges() == {k: ([(0, n)] if n else []) for k, n in full.items()}
+    for r in range(world):
+        nlp = ph.transcribe_window(r, world)
+        rg = nlp.input_ranges()
+        used = {"X": set(), "LE": set(), "LI": set()}
+        for f in range(nlp.dims()["nfuncs"]):
+            fi = nlp.function_info(f)
+            V, Cc = nlp.function_indices(f)
+            used["X"].update(int(v) for v in np.unique(V))
+            if fi["role"]:
+                used["LE" if fi["role"] == 1 else "LI"].update(int(c) for c in np.unique(Cc))
+        for k, ranges in rg.items():
+            for (a0, a1), (b0, b1) in zip(ranges[:-1], ranges[1:]):
+                assert a0 < a1 <= b0 < b1
+            cover = np.zeros(full[k] + 1, dtype=bool)
+            for lo, hi in ranges:
+                assert 0 <= lo < hi <= full[k]
+                cover[lo:hi] = True
+            idx = np.fromiter(used[k], dtype=np.int64, count=len(used[k]))
+            assert cover[idx].all(), (r, k, "an index a kept application reads is not uploaded")
+            total = int(cover.sum())
+            if full[k]:
+                assert total <= 1.25 * full[k] / world + 40 * full[k] / nseg, (r, k, total, full[k])
+                assert len(ranges) <= 8, (r, k, ranges)

@@ -15,7 +15,7 @@ from ._lib import lib
 (VK_ARGS, VK_SEGMENT, VK_ELEMENTS, VK_CONSTANT, VK_STACK, VK_SUM, VK_DIFF, VK_SCALED, VK_ROWSCALED, VK_ADDVEC,
  VK_VECMINUS, VK_UNARY, VK_NORM, VK_NORMALIZED, VK_DOT, VK_CROSS, VK_CWISEPROD, VK_CWISEQUOT, VK_VSPROD, VK_VSDIV,
  VK_CWISESUM, VK_ATAN2, VK_NESTED, VK_IFELSE, VK_COMPARE, VK_BOOL, VK_IOSCALED, VK_APPCONST, VK_MATVEC, VK_QUATPROD,
- VK_INTERP1D, VK_INTERP2D) = range(32)
+ VK_INTERP1D, VK_INTERP2D, VK_MATPROD, VK_MATINV, VK_INTERPND) = range(35)
 
 # ab::Op (csrc/tape.h)
 OPS = ["CONST", "INPUT", "LAMBDA", "APPCONST", "ADD", "SUB", "MUL", "DIV", "NEG", "ADDC", "MULC", "SQUARE", "INV", "SQRT",
@@ -635,11 +635,103 @@ def ifelse(cond, a, b):
     return cond._new(VK_IFELSE, a.orows, [cond, a, b])
 
 
+class _MatrixView:
+    """A vector function read as a matrix (MatrixFunctionView, CommonFunctions/MatrixFunction.h:9-19): ``ColMatrix`` stores
+    its columns one after another, ``RowMatrix`` its rows.  Python surface of MatrixFunctionBuild.cpp:17-215."""
+    rowmajor = 0
+
+    def __init__(self, f, rows=None, cols=None):
+        if isinstance(f, (list, tuple)):  # a list of column (row) functions
+            if len(f) == 0:
+                raise ValueError("List must contain at least one function.")
+            parts = [_as_fun(q) for q in f]
+            for q in parts:
+                if q.orows != parts[0].orows:
+                    raise ValueError(("Row" if self.rowmajor else "Column") + " Functions must have same output size")
+            n_other, n_list = parts[0].orows, len(parts)
+            rows, cols = (n_list, n_other) if self.rowmajor else (n_other, n_list)
+            f = stack(parts)
+        f = _as_fun(f)
+        if rows is None or cols is None or int(rows) * int(cols) != f.orows:
+            raise ValueError("matrix view: rows * cols must equal the function's output size")
+        self.f, self.MatrixRows, self.MatrixCols = f, int(rows), int(cols)
+
+    def vf(self):
+        return self.f
+
+    def IRows(self):
+        return self.f.ir
+
+    def transpose(self):
+        other = ColMatrix if self.rowmajor else RowMatrix
+        return other(self.f, self.MatrixCols, self.MatrixRows)
+
+    def inverse(self):
+        if self.MatrixRows != self.MatrixCols:
+            raise ValueError("Matrix must be square to be invertible")
+        n = self.MatrixRows
+        inv = self.f._new(VK_MATINV, n * n, [self.f], ip=[n, self.rowmajor])
+        return type(self)(inv, n, n)
+
+    def _prod(self, o):
+        if self.MatrixCols != o.MatrixRows:
+            raise ValueError("Invalid matrix product. Number of columns in matrix 1 does not match number of rows in matrix 2.")
+        r, k, c = self.MatrixRows, self.MatrixCols, o.MatrixCols
+        return self.f._new(VK_MATPROD, r * c, [self.f, o.f], ip=[r, k, c, self.rowmajor, o.rowmajor])
+
+    def __mul__(self, o):
+        if isinstance(o, _MatrixView):
+            return ColMatrix(self._prod(o), self.MatrixRows, o.MatrixCols)  # products come back column-major
+        if isinstance(o, VectorFunction):
+            return self._prod(ColMatrix(o, o.orows, 1))  # a vector
+        if _is_num(o):
+            return type(self)(self.f * float(o), self.MatrixRows, self.MatrixCols)
+        v = _vec(o)  # constant vector
+        return self * self.f._new(VK_CONSTANT, v.size, [], d=v, raw=1)
+
+    def __rmul__(self, o):
+        if _is_num(o):
+            return self * o
+        return NotImplemented
+
+    def __add__(self, o):
+        if isinstance(o, _MatrixView):
+            if (o.MatrixRows, o.MatrixCols) != (self.MatrixRows, self.MatrixCols):
+                raise ValueError("Matrices must have the same dimensions to be added.")
+            if o.rowmajor != self.rowmajor:
+                raise TypeError("matrices of different storage order cannot be added")
+            return type(self)(self.f + o.f, self.MatrixRows, self.MatrixCols)
+        m = np.asarray(o, dtype=np.float64)
+        if m.shape != (self.MatrixRows, self.MatrixCols):
+            raise ValueError("Matrices must have the same dimensions to be added.")
+        return type(self)(self.f + (m.ravel() if self.rowmajor else m.T.ravel()), self.MatrixRows, self.MatrixCols)
+
+    __radd__ = __add__
+    __array_ufunc__ = None
+
+
+class ColMatrix(_MatrixView):
+    rowmajor = 0
+
+
+class RowMatrix(_MatrixView):
+    rowmajor = 1
+
+
 def matmul(M, f):
+    """vf.matmul (MatrixFunctionBuild.cpp:218-271): matrix function x matrix function / vector function / constant vector,
+    or a constant matrix x vector function (MatrixScaled)."""
+    if isinstance(M, _MatrixView):
+        return M * f
     M = np.asarray(M, dtype=np.float64)
     if M.ndim != 2 or M.shape[1] != f.orows:
         raise ValueError("matmul: shape mismatch")
     return f._new(VK_MATVEC, M.shape[0], [f], d=M.ravel())
+
+
+def ParsedInput(f, varlocs, irr):
+    """ParsedInput(f, varlocs, irr) (CommonFunctions/ParsedInput.h:6-27): f applied to the listed elements of a larger input."""
+    return _as_fun(f).eval(int(irr), [int(v) for v in varlocs])
 
 
 def ioscaled(f, in_scales, out_scales):
@@ -835,6 +927,66 @@ class InterpTable2D:
         raise NotImplementedError("InterpTable2D on numbers: evaluate tab.vf() through the oracle or on the device")
 
     interp = __call__
+
+
+class _InterpTableND:
+    """InterpTable3D / InterpTable4D (CommonFunctions/InterpTable3D.h:9-390, InterpTable4D.h): tri- / quadri-cubic Hermite
+    patches through the values and every mixed first derivative at the cell corners (derivatives by the same five-point
+    stencils as the lower-dimensional tables), or multilinear interpolation.  ``fs[i, j, k(, l)]`` is the value at
+    ``(xs[i], ys[j], zs[k](, ws[l]))``."""
+    D = 0
+
+    def __init__(self, *args, kind="cubic", cache=False):
+        args = list(args)
+        if len(args) > self.D + 1 and isinstance(args[self.D + 1], str):
+            kind = args[self.D + 1]
+        axes, fs = [np.asarray(a, dtype=np.float64).ravel() for a in args[:self.D]], np.asarray(args[self.D], dtype=np.float64)
+        self.kind = _kind(kind)
+        names = "XYZW"
+        for d, c in enumerate(axes):
+            _ascending(c, names[d])
+        if fs.shape != tuple(c.size for c in axes):
+            raise ValueError("coordinates must match the dimensions of the value tensor")
+        self.axes, self.fs = axes, np.ascontiguousarray(fs)
+        self.even = [_is_even(c) for c in axes]
+        self.arrays = [self.fs]
+        if self.kind == 0:
+            self.arrays = [None] * (1 << self.D)
+            self.arrays[0] = self.fs
+            for b in range(1, 1 << self.D):
+                d = b.bit_length() - 1  # differentiate the array without the highest bit along that axis
+                src = np.moveaxis(self.arrays[b & ~(1 << d)], d, -1)
+                self.arrays[b] = np.ascontiguousarray(np.moveaxis(_stencil_derivs(axes[d], src, self.even[d]), -1, d))
+        self.WarnOutOfBounds, self.ThrowOutOfBounds = True, False
+
+    def vf(self):
+        d = np.concatenate(self.axes + [a.ravel() for a in self.arrays])
+        ip = [self.D, self.kind] + [c.size for c in self.axes] + [int(e) for e in self.even]
+        return ScalarFunction(GRAPH.node(VK_INTERPND, self.D, 1, [Arguments(self.D).node], d, ip, -1, 0), self.D, 1)
+
+    sf = vf
+
+    def __call__(self, *xs):
+        if len(xs) == 1 and isinstance(xs[0], VectorFunction):
+            x = xs[0]
+        elif all(isinstance(x, VectorFunction) for x in xs):
+            x = stack(list(xs))
+        else:
+            raise NotImplementedError("InterpTableND on numbers: evaluate tab.vf() through the oracle or on the device")
+        if x.orows != self.D:
+            raise ValueError(f"InterpTable{self.D}D: needs {self.D} scalar coordinates")
+        f = self.vf().eval(x)
+        return ScalarFunction(f.node, f.ir, 1)
+
+    interp = __call__
+
+
+class InterpTable3D(_InterpTableND):
+    D = 3
+
+
+class InterpTable4D(_InterpTableND):
+    D = 4
 
 
 Element = ScalarFunction

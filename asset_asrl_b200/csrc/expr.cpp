@@ -1,6 +1,7 @@
 #include "expr.hpp"
 
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstring>
 #include <sstream>
@@ -509,6 +510,177 @@ std::vector<int> lower_impl(const Graph& g, int root, const std::vector<int>& in
         out.push_back(dag.add(dag.mul(lo, wy), dag.mul(hi, yf)));
       }
     } break;
+    case VK_MATPROD: {  // MatrixFunctionProduct (MatrixProduct.h:19-120): Eigen maps over the two outputs, result column-major
+      auto A = L(0), B = L(1);
+      if (nd.ip.size() != 5) throw std::invalid_argument("lower: matrix product takes ip = {r, k, c, A row-major, B row-major}");
+      const int r = nd.ip[0], k = nd.ip[1], c = nd.ip[2];
+      if ((int) A.size() != r * k || (int) B.size() != k * c || nd.orows != r * c)
+        throw std::invalid_argument("Invalid matrix product. Number of columns in matrix 1 does not match number of rows in matrix 2.");
+      auto a = [&](int i, int q) { return A[(size_t) (nd.ip[3] ? i * k + q : q * r + i)]; };
+      auto b = [&](int q, int j) { return B[(size_t) (nd.ip[4] ? q * c + j : j * k + q)]; };
+      for (int j = 0; j < c; j++)
+        for (int i = 0; i < r; i++) {
+          int sum = -1;
+          for (int q = 0; q < k; q++) {
+            const int term = dag.mul(a(i, q), b(q, j));
+            sum = sum < 0 ? term : dag.add(sum, term);
+          }
+          out.push_back(sum);
+        }
+    } break;
+    case VK_MATINV: {  // MatrixInverse (MatrixInverse.h:6-58); derivatives (:60-188) follow from differentiating the DAG
+      auto A = L(0);
+      if (nd.ip.size() != 2) throw std::invalid_argument("lower: matrix inverse takes ip = {n, row-major}");
+      const int n = nd.ip[0];
+      if (n < 1 || (int) A.size() != n * n) throw std::invalid_argument("Matrix must be square to be invertible");
+      const bool rowmajor = nd.ip[1] != 0;
+      std::vector<std::vector<int>> M((size_t) n, std::vector<int>((size_t) n)), R = M;
+      for (int i = 0; i < n; i++)
+        for (int j = 0; j < n; j++) M[i][j] = A[(size_t) (rowmajor ? i * n + j : j * n + i)];
+      if (n == 1) {
+        R[0][0] = dag.unary(OP_INV, M[0][0]);
+      } else if (n == 2) {  // adjugate over determinant, as Eigen does for fixed sizes up to four
+        const int idet = dag.unary(OP_INV, dag.sub(dag.mul(M[0][0], M[1][1]), dag.mul(M[0][1], M[1][0])));
+        R[0][0] = dag.mul(M[1][1], idet);
+        R[0][1] = dag.neg(dag.mul(M[0][1], idet));
+        R[1][0] = dag.neg(dag.mul(M[1][0], idet));
+        R[1][1] = dag.mul(M[0][0], idet);
+      } else if (n == 3) {
+        auto cof = [&](int i, int j) {  // cofactor of element (i, j)
+          const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+          return dag.sub(dag.mul(M[i1][j1], M[i2][j2]), dag.mul(M[i1][j2], M[i2][j1]));
+        };
+        int C[3][3];
+        for (int i = 0; i < 3; i++)
+          for (int j = 0; j < 3; j++) C[i][j] = cof(i, j);
+        const int det = dag.add(dag.add(dag.mul(M[0][0], C[0][0]), dag.mul(M[0][1], C[0][1])), dag.mul(M[0][2], C[0][2]));
+        const int idet = dag.unary(OP_INV, det);
+        for (int i = 0; i < 3; i++)
+          for (int j = 0; j < 3; j++) R[i][j] = dag.mul(C[j][i], idet);
+      } else {
+        // Gauss-Jordan on [M | I] with partial pivoting done by selects: before column j is eliminated, row j is exchanged
+        // with every later row whose entry in that column is larger in magnitude (straight-line code; the comparisons
+        // have zero derivative, so the derivatives are those of the inverse wherever the pivot order is locally constant)
+        std::vector<std::vector<int>> W((size_t) n, std::vector<int>((size_t) 2 * n));
+        for (int i = 0; i < n; i++)
+          for (int j = 0; j < 2 * n; j++) W[i][j] = j < n ? M[i][j] : dag.constant(j - n == i ? 1.0 : 0.0);
+        for (int j = 0; j < n; j++) {
+          for (int i = j + 1; i < n; i++) {
+            const int swap = dag.cmp(OP_LT, dag.unary(OP_ABS, W[j][j]), dag.unary(OP_ABS, W[i][j]));
+            for (int q = 0; q < 2 * n; q++) {
+              const int top = dag.select(swap, W[i][q], W[j][q]), bot = dag.select(swap, W[j][q], W[i][q]);
+              W[j][q] = top;
+              W[i][q] = bot;
+            }
+          }
+          const int ip = dag.unary(OP_INV, W[j][j]);
+          for (int q = 0; q < 2 * n; q++) W[j][q] = q == j ? dag.constant(1.0) : dag.mul(W[j][q], ip);
+          for (int i = 0; i < n; i++) {
+            if (i == j) continue;
+            const int f = W[i][j];
+            for (int q = 0; q < 2 * n; q++) W[i][q] = q == j ? dag.constant(0.0) : dag.sub(W[i][q], dag.mul(f, W[j][q]));
+          }
+        }
+        for (int i = 0; i < n; i++)
+          for (int j = 0; j < n; j++) R[i][j] = W[i][n + j];
+      }
+      out.resize((size_t) n * n);
+      for (int i = 0; i < n; i++)
+        for (int j = 0; j < n; j++) out[(size_t) (rowmajor ? i * n + j : j * n + i)] = R[i][j];
+    } break;
+    case VK_INTERPND: {  // InterpTable3D / InterpTable4D (InterpTable3D.h:395-560, InterpTable4D.h): the tricubic / quadricubic
+                         // Hermite patch through values and all mixed first derivatives at the cell corners, as a tensor product
+      auto xs = L(0);
+      if (nd.ip.size() < 2) throw std::invalid_argument("lower: InterpTableND takes ip = {D, kind, n_0.., even_0..}");
+      const int D = nd.ip[0];
+      const bool cubic = nd.ip[1] == 0;
+      if (D < 1 || D > 4 || (int) xs.size() != D || (int) nd.ip.size() != 2 + 2 * D)
+        throw std::invalid_argument("lower: InterpTableND dimension / coordinate count mismatch");
+      std::vector<int> n((size_t) D);
+      size_t cells = 1, naxis = 0;
+      for (int d = 0; d < D; d++) {
+        n[d] = nd.ip[2 + d];
+        if (n[d] < 5) throw std::invalid_argument("coordinates must be larger than 4");
+        cells *= (size_t) n[d];
+        naxis += (size_t) n[d];
+      }
+      const int narr = cubic ? 1 << D : 1;
+      if (nd.d.size() != naxis + cells * narr) throw std::invalid_argument("lower: InterpTableND data size does not match its shape");
+      std::vector<size_t> stride((size_t) D);
+      for (int d = D - 1, s = 1; d >= 0; d--) {
+        stride[d] = (size_t) s;
+        s *= n[d];
+      }
+      std::vector<size_t> aoff((size_t) D), arr((size_t) narr);
+      size_t pos = 0;
+      for (int d = 0; d < D; d++) {
+        for (int i = 0; i + 1 < n[d]; i++)
+          if (nd.d[pos + i + 1] < nd.d[pos + i]) throw std::invalid_argument("coordinates must be in ascending order");
+        std::vector<double> axis((size_t) n[d] + 2);
+        axis[0] = n[d];
+        axis[1] = nd.ip[2 + D + d] ? 1.0 : 0.0;
+        std::copy(nd.d.begin() + (long) pos, nd.d.begin() + (long) pos + n[d], axis.begin() + 2);
+        aoff[d] = dag.tab_add(axis.data(), axis.size());
+        pos += (size_t) n[d];
+      }
+      for (int b = 0; b < narr; b++) arr[b] = dag.tab_add(nd.d.data() + pos + (size_t) b * cells, cells);
+      // per axis: interval, local coordinate, the four Hermite weights (value at 0 / 1, slope at 0 / 1 times the step)
+      int cell = -1;
+      std::vector<std::array<int, 4>> Bw((size_t) D);
+      for (int d = 0; d < D; d++) {
+        const int e = dag.tabidx(xs[d], aoff[d]);
+        const int c0 = dag.tabload(e, aoff[d] + 2), c1 = dag.tabload(e, aoff[d] + 3);
+        const int step = dag.sub(c1, c0);
+        const int u = dag.div(dag.sub(xs[d], c0), step);
+        if (cubic) {
+          const int u2 = dag.mul(u, u), u3 = dag.mul(u2, u);
+          Bw[d] = {dag.addc(dag.sub(dag.mulc(u3, 2.0), dag.mulc(u2, 3.0)), 1.0), dag.add(dag.mulc(u3, -2.0), dag.mulc(u2, 3.0)),
+                   dag.mul(dag.add(dag.sub(u3, dag.mulc(u2, 2.0)), u), step), dag.mul(dag.sub(u3, u2), step)};
+        } else {
+          Bw[d] = {dag.addc(dag.neg(u), 1.0), u, -1, -1};
+        }
+        const int term = dag.mulc(e, (double) stride[d]);
+        cell = cell < 0 ? term : dag.add(cell, term);
+      }
+      // V[flags][corner] -> contract one axis at a time, the last axis first
+      const int per = cubic ? 2 : 1;  // flag values per axis
+      std::vector<int> V;             // index: sum over axes of ((flag_d * 2 + corner_d) * 4^d)  (only used combinations filled)
+      auto key = [&](const std::vector<int>& fc, int upto) {  // fc[d] = flag_d * 2 + corner_d for d < upto
+        int k = 0;
+        for (int d = upto - 1; d >= 0; d--) k = k * 4 + fc[d];
+        return k;
+      };
+      V.assign((size_t) 1 << (2 * D), -1);
+      std::vector<int> fc((size_t) D, 0);
+      for (int fb = 0; fb < (cubic ? 1 << D : 1); fb++)
+        for (int cb = 0; cb < 1 << D; cb++) {
+          size_t off = 0;
+          for (int d = 0; d < D; d++) {
+            fc[d] = ((fb >> d & 1) << 1) | (cb >> d & 1);
+            off += (size_t) (cb >> d & 1) * stride[d];
+          }
+          V[(size_t) key(fc, D)] = dag.tabload(cell, arr[cubic ? fb : 0] + off);
+        }
+      for (int d = D - 1; d >= 0; d--) {  // after this pass V is indexed by the combinations of axes 0 .. d-1
+        std::vector<int> Wn((size_t) 1 << (2 * d), -1);
+        for (int k = 0; k < 1 << (2 * d); k++) {
+          bool used = true;  // skip combinations with a slope flag in the linear kind
+          for (int q = 0, kk = k; q < d; q++, kk >>= 2)
+            if ((kk & 3) >> 1 >= per) used = false;
+          if (!used) continue;
+          int sum = -1;
+          for (int w = 0; w < 2 * per; w++) {
+            const int v = V[(size_t) (k + (w << (2 * d)))];
+            if (v < 0) continue;
+            const int term = dag.mul(v, Bw[d][w]);
+            sum = sum < 0 ? term : dag.add(sum, term);
+          }
+          Wn[(size_t) k] = sum;
+        }
+        V.swap(Wn);
+      }
+      out.push_back(V[0]);
+    } break;
     case VK_MATVEC: {
       auto a = L(0);
       int cols = (int) a.size();
@@ -768,7 +940,8 @@ static const char* kind_name(int k) {
   static const char* names[] = {"args",     "segment", "elements",  "constant",  "stack",    "sum",     "diff",   "scaled",
                                 "rowscaled", "addvec",  "vecminus",  "unary",     "norm",     "normalized", "dot", "cross",
                                 "cwiseprod", "cwisequot", "vsprod",  "vsdiv",     "cwisesum", "atan2",   "nested", "ifelse",
-                                "compare",  "bool",    "ioscaled",  "appconst",  "matvec",   "quatprod", "interp1d", "interp2d"};
+                                "compare",  "bool",    "ioscaled",  "appconst",  "matvec",   "quatprod", "interp1d", "interp2d",
+                                "matprod",  "matinv",  "interpnd"};
   return names[k];
 }
 

@@ -51,6 +51,11 @@ enum VKind : int {
   VK_QUATPROD,      // Hamilton product ch0 (x) ch1 of two quaternions stored vector-first (x, y, z, w)
   VK_INTERP1D,      // InterpTable1D(ch0 = t): ip = {n, vlen, kind (0 cubic, 1 linear), even}, d = [ts(n), vs(vlen x n), dvs(vlen x n)]
   VK_INTERP2D,      // InterpTable2D(ch0 = (x, y)): ip = {nx, ny, kind, xeven, yeven}, d = [xs, ys, z, dz/dx, dz/dy, d2z/dxdy (ny x nx each)]
+  VK_MATPROD,       // matrix product A(ch0) * B(ch1): ip = {r, k, c, A row-major?, B row-major?}; output r x c column-major
+  VK_MATINV,        // inverse of the n x n matrix ch0: ip = {n, row-major?}; output in the same storage order
+  VK_INTERPND,      // InterpTable3D / 4D (ch0 = the D coordinates): ip = {D, kind, n_0.., even_0..}, d = [axis_0 .. axis_{D-1},
+                    //   2^D arrays (cubic; array b holds the derivative along every axis whose bit is set in b) or one (linear),
+                    //   each of shape (n_0, ..., n_{D-1}) in C order]
 };
 
 struct VNode {

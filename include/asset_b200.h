@@ -64,8 +64,14 @@ enum {
   AB_VK_QUATPROD = 29,   /* Hamilton product child0 (x) child1, quaternions stored (x, y, z, w) (VectorProducts.h:28-30,229-236) */
   AB_VK_INTERP1D = 30,   /* InterpTable1D at child0 = t (InterpTable1D.h:9-483): iparams = {n, vlen, kind (0 cubic, 1 linear), even},
                             dparams = [ts (n), vs (vlen x n, row-major), dvs/dt (vlen x n; cubic only)] */
-  AB_VK_INTERP2D = 31    /* InterpTable2D at child0 = (x, y) (InterpTable2D.h): iparams = {nx, ny, kind, xeven, yeven},
+  AB_VK_INTERP2D = 31,   /* InterpTable2D at child0 = (x, y) (InterpTable2D.h): iparams = {nx, ny, kind, xeven, yeven},
                             dparams = [xs (nx), ys (ny), z, dz/dx, dz/dy, d2z/dxdy (ny x nx each, row-major; cubic: all four)] */
+  AB_VK_MATPROD = 32,    /* matrix product child0 (r x k) * child1 (k x c), iparams = {r, k, c, child0 row-major, child1 row-major};
+                            result column-major (MatrixFunctionProduct, CommonFunctions/MatrixProduct.h:19-120) */
+  AB_VK_MATINV = 33,     /* inverse of the n x n matrix child0, iparams = {n, row-major} (CommonFunctions/MatrixInverse.h:6-58) */
+  AB_VK_INTERPND = 34    /* InterpTable3D / InterpTable4D at child0 = the D coordinates (CommonFunctions/InterpTable3D.h:395-560,
+                            InterpTable4D.h): iparams = {D, kind, n_0.., even_0..}, dparams = [axes, then 2^D arrays (cubic: array b
+                            = derivative along the axes whose bit is set in b) or one (linear), shape (n_0..n_{D-1}), C order] */
 };
 /* PhaseRegionFlags and TranscriptionModes of the reference (src/OptimalControl/OptimalControlFlags.h) */
 enum { AB_REGION_FRONT = 1, AB_REGION_BACK = 2, AB_REGION_FRONTANDBACK = 3, AB_REGION_BACKANDFRONT = 4, AB_REGION_PATH = 5,

@@ -92,12 +92,12 @@ static Vec atv(const Mat& A, const double* l) {
 enum Kind {
   K_ARGS, K_SEGMENT, K_ELEMENTS, K_CONSTANT, K_STACK, K_SUM, K_DIFF, K_SCALED, K_ROWSCALED, K_ADDVEC, K_VECMINUS,
   K_UNARY, K_NORM, K_NORMALIZED, K_DOT, K_CROSS, K_CWISEPROD, K_CWISEQUOT, K_VSPROD, K_VSDIV, K_CWISESUM, K_ATAN2,
-  K_NESTED, K_IFELSE, K_COMPARE, K_BOOL, K_IOSCALED, K_APPCONST, K_MATVEC, K_QUATPROD, K_INTERP1D, K_INTERP2D, K_COUNT
+  K_NESTED, K_IFELSE, K_COMPARE, K_BOOL, K_IOSCALED, K_APPCONST, K_MATVEC, K_QUATPROD, K_INTERP1D, K_INTERP2D, K_MATPROD, K_MATINV, K_INTERPND, K_COUNT
 };
 static const char* kKindNames[K_COUNT] = {"args", "segment", "elements", "constant", "stack", "sum", "diff", "scaled",
                                           "rowscaled", "addvec", "vecminus", "unary", "norm", "normalized", "dot", "cross",
                                           "cwiseprod", "cwisequot", "vsprod", "vsdiv", "cwisesum", "atan2", "nested", "ifelse",
-                                          "compare", "bool", "ioscaled", "appconst", "matvec", "quatprod", "interp1d", "interp2d"};
+                                          "compare", "bool", "ioscaled", "appconst", "matvec", "quatprod", "interp1d", "interp2d", "matprod", "matinv", "interpnd"};
 
 // unary opcodes: numeric values of ab::Op in asset_asrl_b200/csrc/tape.h (the describe() string carries them)
 enum UOp { U_NEG = 8, U_SQUARE = 11, U_INV, U_SQRT, U_EXP, U_LOG, U_SIN, U_COS, U_TAN, U_ASIN, U_ACOS, U_ATAN, U_SINH, U_COSH,
@@ -524,6 +524,158 @@ void Eval::outer(const Node& n, const Vec& Y, const std::vector<int>& off, doubl
         (*Hp)(0, 1) += l[0] * zxy;
         (*Hp)(1, 0) += l[0] * zxy;
         (*Hp)(1, 1) += l[0] * zyy;
+      }
+    } break;
+    case K_MATPROD: {  // MatrixFunctionProduct (MatrixProduct.h:19-442): C = A B over the children's outputs read as matrices
+      const int r = n.ip[0], kk = n.ip[1], c = n.ip[2];
+      const bool arow = n.ip[3] != 0, brow = n.ip[4] != 0;
+      const int nb = off[1];  // B's outputs follow A's in Y
+      for (int j = 0; j < c; j++)
+        for (int i = 0; i < r; i++) {
+          const int o = j * r + i;  // column-major result
+          fx[o] = 0.0;
+          for (int q = 0; q < kk; q++) {
+            const int ia = arow ? i * kk + q : q * r + i, ib = nb + (brow ? q * c + j : j * kk + q);
+            fx[o] += Y[ia] * Y[ib];
+            if (Jp) {
+              (*Jp)(o, ia) += Y[ib];
+              (*Jp)(o, ib) += Y[ia];
+            }
+            if (Hp) {
+              (*Hp)(ia, ib) += l[o];
+              (*Hp)(ib, ia) += l[o];
+            }
+          }
+        }
+    } break;
+    case K_MATINV: {  // MatrixInverse (MatrixInverse.h:6-188): d(A^-1) = -A^-1 dA A^-1, second derivative by the product rule
+      const int m = n.ip[0];
+      const bool rowm = n.ip[1] != 0;
+      auto at = [&](int i, int j) { return rowm ? i * m + j : j * m + i; };
+      Mat A(m, 2 * m);
+      for (int i = 0; i < m; i++) {
+        for (int j = 0; j < m; j++) A(i, j) = Y[at(i, j)];
+        A(i, m + i) = 1.0;
+      }
+      for (int col = 0; col < m; col++) {  // Gauss-Jordan, partial pivoting
+        int piv = col;
+        for (int i = col + 1; i < m; i++)
+          if (std::fabs(A(i, col)) > std::fabs(A(piv, col))) piv = i;
+        for (int q = 0; q < 2 * m; q++) std::swap(A(col, q), A(piv, q));
+        const double ip = 1.0 / A(col, col);
+        for (int q = 0; q < 2 * m; q++) A(col, q) *= ip;
+        for (int i = 0; i < m; i++) {
+          if (i == col) continue;
+          const double f = A(i, col);
+          if (f != 0.0)
+            for (int q = 0; q < 2 * m; q++) A(i, q) -= f * A(col, q);
+        }
+      }
+      auto inv = [&](int i, int j) { return A(i, m + j); };
+      for (int i = 0; i < m; i++)
+        for (int j = 0; j < m; j++) fx[at(i, j)] = inv(i, j);
+      if (Jp || Hp)
+        for (int a = 0; a < m; a++)
+          for (int b = 0; b < m; b++)      // input element A(a, b)
+            for (int p = 0; p < m; p++)
+              for (int q = 0; q < m; q++) {  // output element Ainv(p, q)
+                if (Jp) (*Jp)(at(p, q), at(a, b)) = -inv(p, a) * inv(b, q);
+                if (Hp)
+                  for (int c2 = 0; c2 < m; c2++)
+                    for (int d2 = 0; d2 < m; d2++)
+                      (*Hp)(at(a, b), at(c2, d2)) += l[at(p, q)] * (inv(p, a) * inv(b, c2) * inv(d2, q) + inv(p, c2) * inv(d2, a) * inv(b, q));
+              }
+    } break;
+    case K_INTERPND: {  // InterpTable3D / 4D (InterpTable3D.h:122-560, InterpTable4D.h): Hermite patch over the cell, tensor form
+      const int D = n.ip[0];
+      const bool cubic = n.ip[1] == 0;
+      int nn[4], e[4];
+      size_t stride[4], cells = 1;
+      const double* ax[4];
+      const double* p = n.d.data();
+      for (int d = 0; d < D; d++) {
+        nn[d] = n.ip[2 + d];
+        ax[d] = p;
+        p += nn[d];
+        cells *= (size_t) nn[d];
+      }
+      for (int d = D - 1, sacc = 1; d >= 0; d--) {
+        stride[d] = (size_t) sacc;
+        sacc *= nn[d];
+      }
+      const double* vals = p;
+      // mixed derivative arrays recomputed here by successive stencils (calc_derivs), lowest set axis last
+      std::vector<Vec> arr((size_t) (cubic ? 1 << D : 1));
+      arr[0].assign(vals, vals + cells);
+      if (cubic)
+        for (int b = 1; b < (1 << D); b++) {
+          int d = 0;
+          while (!((b >> d) & 1)) d++;  // differentiate arr[b without its lowest bit] along that axis
+          const Vec& src = arr[(size_t) (b & (b - 1))];
+          arr[(size_t) b].assign(cells, 0.0);
+          for (size_t base = 0; base < cells; base++) {
+            if ((base / stride[d]) % (size_t) nn[d] != 0) continue;  // first element of each line along axis d
+            stencil_axis(ax[d], nn[d], &src[base], &arr[(size_t) b][base], stride[d]);
+          }
+        }
+      double B[4][4], D1[4][4], D2[4][4];
+      size_t cell = 0;
+      for (int d = 0; d < D; d++) {
+        e[d] = interval_of(ax[d], nn[d], n.ip[2 + D + d] != 0, Y[d]);
+        const double hh = ax[d][e[d] + 1] - ax[d][e[d]], u = (Y[d] - ax[d][e[d]]) / hh;
+        cell += (size_t) e[d] * stride[d];
+        if (cubic) {
+          const double u2 = u * u, u3 = u2 * u;
+          B[d][0] = 2 * u3 - 3 * u2 + 1, B[d][1] = -2 * u3 + 3 * u2, B[d][2] = (u3 - 2 * u2 + u) * hh, B[d][3] = (u3 - u2) * hh;
+          D1[d][0] = (6 * u2 - 6 * u) / hh, D1[d][1] = -D1[d][0], D1[d][2] = 3 * u2 - 4 * u + 1, D1[d][3] = 3 * u2 - 2 * u;
+          D2[d][0] = (12 * u - 6) / (hh * hh), D2[d][1] = -D2[d][0], D2[d][2] = (6 * u - 4) / hh, D2[d][3] = (6 * u - 2) / hh;
+        } else {
+          B[d][0] = 1 - u, B[d][1] = u, B[d][2] = B[d][3] = 0;
+          D1[d][0] = -1 / hh, D1[d][1] = 1 / hh, D1[d][2] = D1[d][3] = 0;
+          D2[d][0] = D2[d][1] = D2[d][2] = D2[d][3] = 0;
+        }
+      }
+      double f = 0, g[4] = {0, 0, 0, 0}, H2[4][4] = {{0}};
+      const int per = cubic ? 4 : 2;
+      int w[4] = {0, 0, 0, 0};
+      for (;;) {  // every combination of (slope flag, corner) per axis: w[d] = flag * 2 + corner
+        int fb = 0;
+        size_t o = cell;
+        for (int d = 0; d < D; d++) {
+          fb |= (w[d] >> 1) << d;
+          o += (size_t) (w[d] & 1) * stride[d];
+        }
+        const double c = arr[(size_t) fb][o];
+        double prod = c;
+        for (int d = 0; d < D; d++) prod *= B[d][w[d]];
+        f += prod;
+        for (int a = 0; a < D; a++) {
+          double ga = c;
+          for (int d = 0; d < D; d++) ga *= (d == a ? D1[d][w[d]] : B[d][w[d]]);
+          g[a] += ga;
+          for (int b = a; b < D; b++) {
+            double hab = c;
+            for (int d = 0; d < D; d++) {
+              if (a == b)
+                hab *= (d == a ? D2[d][w[d]] : B[d][w[d]]);
+              else
+                hab *= (d == a || d == b ? D1[d][w[d]] : B[d][w[d]]);
+            }
+            H2[a][b] += hab;
+          }
+        }
+        int d = 0;
+        while (d < D && ++w[d] == per) w[d++] = 0;
+        if (d == D) break;
+      }
+      fx[0] = f;
+      for (int a = 0; a < D; a++) {
+        if (Jp) (*Jp)(0, a) = g[a];
+        if (Hp)
+          for (int b = a; b < D; b++) {
+            (*Hp)(a, b) += l[0] * H2[a][b];
+            if (b != a) (*Hp)(b, a) += l[0] * H2[a][b];
+          }
       }
     } break;
     case K_CWISEPROD: {  // CwiseProduct.h

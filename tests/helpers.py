@@ -58,6 +58,27 @@ def expression_zoo():
     return z
 
 
+def matrix_zoo():
+    """Matrix functions (MatrixFunctionBuild.cpp): views, products in every storage-order pairing, inverses of sizes 2..4
+    (the 4 x 4 one with row exchanges), ParsedInput.  Kept apart from expression_zoo like interp_zoo (GPU tests in
+    tests/test_zz_gpu_tables.py)."""
+    A = vf.Arguments
+    x4, x6, x9, x16 = A(4), A(6), A(9), A(16)
+    z = []
+    pos = lambda n: (lambda rng: rng.uniform(0.5, 1.5, n))  # noqa: E731
+    sym = lambda n: (lambda rng: rng.uniform(-0.9, 0.9, n))  # noqa: E731
+    dd = lambda n: (lambda rng: (np.eye(int(round(n ** 0.5))) * 2.5 + rng.uniform(-0.6, 0.6, (int(round(n ** 0.5)),) * 2)).ravel())  # noqa: E731
+    Mc, Mr = vf.ColMatrix(x6, 2, 3), vf.RowMatrix(vf.sin(x6), 3, 2)
+    z.append(("mat_products", vf.stack([(Mc * Mr).vf(), (Mr * Mc).vf(), (Mc.transpose() * Mr.transpose()).vf(), Mc * x6.tail3(),
+                                        vf.matmul(Mr, np.array([0.5, -2.0])), (2.0 * Mc + np.arange(6.0).reshape(2, 3)).vf()]), sym(6)))
+    z.append(("mat_inverse_2", vf.stack([vf.ColMatrix(x4, 2, 2).inverse().vf(), vf.RowMatrix(x4, 2, 2).inverse() * x4.head2()]), dd(4)))
+    z.append(("mat_inverse_3", vf.stack([vf.ColMatrix(x9, 3, 3).inverse().vf(), vf.RowMatrix(x9, 3, 3).inverse() * x9.head3()]), dd(9)))
+    z.append(("mat_inverse_4_pivoting", (vf.RowMatrix(x16, 4, 4).inverse() * vf.RowMatrix(x16, 4, 4).transpose()).vf(),
+              lambda rng: (np.eye(4)[rng.permutation(4)] * 2.0 + rng.uniform(-0.4, 0.4, (4, 4))).ravel()))
+    z.append(("parsed_input", vf.ParsedInput(A(3).normalized_power3(), [5, 0, 2], 6), pos(6)))
+    return z
+
+
 def interp_tables():
     """Interpolation tables over smooth data: evenly and unevenly spaced axes, scalar and vector values, both kinds."""
     te = np.linspace(-1.0, 2.0, 13)
@@ -77,6 +98,12 @@ def interp_tables():
         T[f"2d_even_{knd}"] = vf.InterpTable2D(xs_e, ys_e, surf(xs_e, ys_e), kind=knd)
         T[f"2d_uneven_{knd}"] = vf.InterpTable2D(xs_u, ys_u, surf(xs_u, ys_u), kind=knd)
         T[f"2d_mixed_{knd}"] = vf.InterpTable2D(xs_e, ys_u, surf(xs_e, ys_u), kind=knd)
+        g3 = np.meshgrid(xs_e[:6], ys_u[:7], te[:5], indexing="ij")
+        T[f"3d_mixed_{knd}"] = vf.InterpTable3D(xs_e[:6], ys_u[:7], te[:5], np.sin(g3[0] + 0.4 * g3[1]) * np.cos(0.7 * g3[2]) + 0.1 * g3[1] * g3[2],
+                                                kind=knd)
+        g4 = np.meshgrid(xs_u[:5], ys_e[:5], tu[:6], te[:5], indexing="ij")
+        T[f"4d_mixed_{knd}"] = vf.InterpTable4D(xs_u[:5], ys_e[:5], tu[:6], te[:5],
+                                                np.sin(g4[0] + 0.4 * g4[1]) * np.cos(0.7 * g4[2] - 0.2 * g4[3]) + 0.1 * g4[1] * g4[3], kind=knd)
     return T
 
 
@@ -98,6 +125,15 @@ def interp_zoo():
                     x = rng.uniform(-1.2, 1.2, 3)
                     if lo + 0.01 < x[0] * x[1] + x[2] < hi - 0.01:
                         return x
+        elif nm[0] in "34":
+            D = tab.D
+            xa = A(D)
+            lo = np.array([c[0] for c in tab.axes]) + 0.01
+            hi = np.array([c[-1] for c in tab.axes]) - 0.01
+            f = tab(*[xa[d] for d in range(D)]) * xa[0] + vf.sin(tab(xa))
+
+            def gen(rng, lo=lo, hi=hi):
+                return rng.uniform(lo, hi)
         else:
             xl, xh, yl, yh = tab.xs[0], tab.xs[-1], tab.ys[0], tab.ys[-1]
             f = tab(x3[0] * x3[2], x3[1] + x3[2]) * x3[0]

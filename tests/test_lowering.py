@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import oracle
-from helpers import expression_zoo, interp_zoo, phase_zoo, table_phase_zoo, problem_inputs, rel_err, TOL
+from helpers import expression_zoo, interp_zoo, matrix_zoo, phase_zoo, table_phase_zoo, problem_inputs, rel_err, TOL
 from ref_assembly import assemble
 from prog_ref import run_program, dense_blocks
 from asset_asrl_b200.Solvers import NonLinearProgram
@@ -18,7 +18,7 @@ ZOO = phase_zoo()
 ZOO.update(table_phase_zoo())
 
 
-@pytest.mark.parametrize("name,fun,gen", expression_zoo() + interp_zoo(), ids=[z[0] for z in expression_zoo() + interp_zoo()])
+@pytest.mark.parametrize("name,fun,gen", expression_zoo() + matrix_zoo() + interp_zoo(), ids=[z[0] for z in expression_zoo() + matrix_zoo() + interp_zoo()])
 def test_tape_matches_oracle(name, fun, gen):
     rng = np.random.default_rng(5)
     ir, orr = fun.IRows(), fun.ORows()

@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 import oracle
-from helpers import expression_zoo, interp_zoo, rel_err, vf, oc, TOL
+from helpers import expression_zoo, interp_zoo, matrix_zoo, rel_err, vf, oc, TOL
 from asset_asrl_b200 import workloads as W
 
 GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "collocation_functions.json")))
@@ -42,7 +42,7 @@ def fd_check(desc, x, lam, appc=None, jtol=1e-6, htol=1e-5):
     assert np.abs(hx - hx.T).max() <= 1e-12 * max(np.abs(hx).max(), 1.0)
 
 
-@pytest.mark.parametrize("name,fun,gen", expression_zoo() + interp_zoo(), ids=[z[0] for z in expression_zoo() + interp_zoo()])
+@pytest.mark.parametrize("name,fun,gen", expression_zoo() + matrix_zoo() + interp_zoo(), ids=[z[0] for z in expression_zoo() + matrix_zoo() + interp_zoo()])
 def test_expression_derivatives(name, fun, gen):
     rng = np.random.default_rng(11)
     for _ in range(3):
@@ -190,3 +190,69 @@ def test_interp_table_2d_known_answers(spacing):
         fx, _, _, _ = _eval(lin.vf(), [x, y], [1.0])
         row = np.array([np.interp(x, xs, Z[j]) for j in range(ys.size)])
         assert abs(fx[0] - np.interp(y, ys, row)) < 1e-14
+
+
+def test_matrix_functions_known_answers():
+    """Matrix views, products and inverses (MatrixFunctionBuild.cpp:17-271, MatrixProduct.h, MatrixInverse.h) against numpy,
+    in both storage orders; the inverse's Jacobian against -kron(A^-T, A^-1)."""
+    rng = np.random.default_rng(8)
+    x = vf.Arguments(12)
+    a, b = rng.normal(size=(2, 3)), rng.normal(size=(3, 2))
+    xin = np.concatenate([a.T.ravel(), b.ravel()])  # A column-major, B row-major
+    A_, B_ = vf.ColMatrix(x.head(6), 2, 3), vf.RowMatrix(x.tail(6), 3, 2)
+    fx, _, _, _ = _eval((A_ * B_).vf(), xin, np.zeros(4))
+    assert np.abs(fx.reshape(2, 2).T - a @ b).max() < 1e-14  # products come back column-major
+    fx, _, _, _ = _eval((B_ * A_).vf(), xin, np.zeros(9))
+    assert np.abs(fx.reshape(3, 3).T - b @ a).max() < 1e-14
+    fx, _, _, _ = _eval((A_.transpose() * B_.transpose()).vf(), xin, np.zeros(9))
+    assert np.abs(fx.reshape(3, 3).T - a.T @ b.T).max() < 1e-14
+    v = np.array([0.3, -1.2, 2.0])
+    fx, _, _, _ = _eval(vf.matmul(A_, v), xin, np.zeros(2))
+    assert np.abs(fx - a @ v).max() < 1e-14
+    for n in (2, 3, 4, 6):
+        m = rng.normal(size=(n, n)) + np.eye(n)[rng.permutation(n)] * 3.0  # needs row exchanges
+        xm = vf.Arguments(n * n)
+        for cls, flat, back in ((vf.ColMatrix, m.T.ravel(), lambda f: f.reshape(n, n).T), (vf.RowMatrix, m.ravel(), lambda f: f.reshape(n, n))):
+            fx, jx, _, _ = _eval(cls(xm, n, n).inverse().vf(), flat, np.zeros(n * n))
+            inv = np.linalg.inv(m)
+            assert np.abs(back(fx) - inv).max() < 1e-12 * np.abs(inv).max()
+            if cls is vf.ColMatrix:  # d vec(A^-1) / d vec(A) = -(A^-T kron A^-1) for column-major vec
+                assert np.abs(jx + np.kron(inv.T, inv)).max() < 1e-11 * np.abs(inv).max() ** 2
+
+
+@pytest.mark.parametrize("D", [3, 4])
+def test_interp_table_nd_known_answers(D):
+    """InterpTable3D / 4D: data sampled from a product of cubics come back exactly with gradient and Hessian (the
+    tri- / quadri-cubic Hermite patch reproduces them); the linear kind agrees with scipy's RegularGridInterpolator."""
+    from scipy.interpolate import RegularGridInterpolator
+    axes = [np.linspace(0.0, 1.5, 6), np.array([-1.0, -0.6, -0.1, 0.2, 0.9, 1.3, 2.0]), np.linspace(2.0, 3.0, 5),
+            np.array([0.0, 0.3, 0.5, 1.0, 1.2, 1.9])][:D]
+    polys = [np.polynomial.Polynomial(c) for c in ([0.2, 1.0, -0.6, 0.3], [-0.4, 0.5, 0.25, -0.1], [1.0, -0.3, 0.2, 0.05], [0.7, 0.1, -0.2, 0.15])][:D]
+    grid = np.meshgrid(*axes, indexing="ij")
+    data = np.ones_like(grid[0])
+    for g, p in zip(grid, polys):
+        data = data * p(g)
+    Tab = vf.InterpTable3D if D == 3 else vf.InterpTable4D
+    tab = Tab(*axes, data, kind="cubic")
+    rng = np.random.default_rng(6)
+    lo, hi = np.array([a[0] for a in axes]), np.array([a[-1] for a in axes])
+    for _ in range(8):
+        x = rng.uniform(lo, hi)
+        fx, jx, _, hx = _eval(tab.vf(), x, [1.0])
+        vals = np.array([p(v) for p, v in zip(polys, x)])
+        d1 = np.array([p.deriv()(v) for p, v in zip(polys, x)])
+        d2 = np.array([p.deriv(2)(v) for p, v in zip(polys, x)])
+        assert abs(fx[0] - vals.prod()) < 1e-12
+        for a in range(D):
+            ga = np.prod([d1[d] if d == a else vals[d] for d in range(D)])
+            assert abs(jx[0, a] - ga) < 1e-11
+            for b in range(D):
+                hab = np.prod([(d2[d] if a == b else d1[d]) if d in (a, b) else vals[d] for d in range(D)])
+                assert abs(hx[a, b] - hab) < 1e-9
+    wavy = np.sin(sum((k + 1) * 0.4 * g for k, g in enumerate(grid)))
+    lin = Tab(*axes, wavy, kind="linear")
+    ref = RegularGridInterpolator(axes, wavy, method="linear")
+    for _ in range(8):
+        x = rng.uniform(lo, hi)
+        fx, _, _, _ = _eval(lin.vf(), x, [1.0])
+        assert abs(fx[0] - ref(x[None, :])[0]) < 1e-13

@@ -91,3 +91,40 @@ def test_assembler_keeps_the_order_of_parked_value_accesses(name):
     info = nlp.fused_info()
     for p in range(int(info["pieces"])):
         assert sass_park_order.check(nlp.fused_ptx(p)) == [], (name, p)
+
+
+def _single_function_cases():
+    from helpers import interp_zoo, matrix_zoo
+    want = ("interp_1d_uneven_scalar_cubic", "interp_2d_mixed_cubic", "interp_3d_mixed_cubic", "interp_4d_mixed_cubic", "interp_4d_mixed_linear",
+            "mat_products", "mat_inverse_4_pivoting")
+    return [z for z in interp_zoo() + matrix_zoo() if z[0] in want]
+
+
+@pytest.mark.parametrize("name,fun,gen", _single_function_cases(), ids=[z[0] for z in _single_function_cases()])
+def test_fused_ptx_of_table_and_matrix_functions_matches_the_oracle(name, fun, gen):
+    """One function over many applications is a fusable problem too: its fused kernel (table ops, table data copied into the
+    fused DAG; select-based pivoting of the matrix inverse) on the emulator against the oracle."""
+    from asset_asrl_b200.Solvers import NonLinearProgram
+    rng = np.random.default_rng(31)
+    ir, orr, nappl = fun.IRows(), fun.ORows(), 200
+    nlp = NonLinearProgram(ir * nappl, orr * nappl, 0)
+    t = nlp.add_tape(fun, True)
+    nlp.add_function(1, t, False, np.arange(ir * nappl, dtype=np.int32).reshape(nappl, ir), np.arange(orr * nappl, dtype=np.int32).reshape(nappl, orr))
+    nlp.analyze()
+    info = nlp.fused_info()
+    assert info["ok"], info["why"]
+    X = np.concatenate([gen(rng) for _ in range(nappl)])
+    LE = rng.uniform(-1, 1, orr * nappl)
+    sc = np.linspace(0.5, 1.5, nlp.dims()["n_solver"])
+    ref = oracle.Oracle.from_problem(nlp).eval("KKT", 1.0, X, LE, np.zeros(0), sc)
+    R = info["t_hi"] - info["t_lo"]
+    res = emulate_fused(nlp, X, LE, np.zeros(0), sc, 1.0, [0, 1, 2, 3, R // 2, R - 1])
+    res.pop("stage")
+    wrote = 0
+    for k, (v, m) in res.items():
+        if not m.any():
+            continue
+        wrote += int(m.sum())
+        scale = max(float(np.abs(ref[k]).max()), 1e-300)
+        assert float(np.abs(v[m] - ref[k][m]).max()) <= 1e-12 * scale, (name, k)
+    assert wrote >= 6 * info["slots_per_segment"]

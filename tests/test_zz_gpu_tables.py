@@ -1,4 +1,4 @@
-"""GPU parity of the interpolation-table ops (InterpTable1D / InterpTable2D) and of the
+"""GPU parity of the interpolation-table ops (InterpTable1D .. 4D), the matrix functions and of the
 minimum-time-to-climb workload whose ODE reads them, against the CPU oracle through the C ABI.
 
 A file of its own, collected after the other GPU tests: these kernels (table ops in the interpreter, in the specialised
@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 
 import oracle
-from helpers import interp_zoo, table_phase_zoo, problem_inputs, rel_err, TOL
+from helpers import interp_zoo, matrix_zoo, table_phase_zoo, problem_inputs, rel_err, TOL
 from asset_asrl_b200 import workloads as W
 from asset_asrl_b200.Solvers import NonLinearProgram
 
@@ -28,11 +28,24 @@ def check(out, ref, keys, tag):
             assert rel_err(out[k], ref[k]) < TOL, (tag, k, rel_err(out[k], ref[k]))
 
 
-@pytest.mark.parametrize("nappl", [19, 4099], ids=["interpreter", "specialised_kernels"])
-@pytest.mark.parametrize("name,fun,gen", interp_zoo(), ids=[z[0] for z in interp_zoo()])
-def test_table_ops_on_device(name, fun, gen, nappl):
-    """Every table flavour (1-D / 2-D, cubic / linear, even / uneven axes, scalar / vector data) as an equality constraint:
-    19 applications (fewer than the smallest range that gets a specialised kernel) run through the program interpreter, 4099 through the specialised kernels (bulk + indexed ends)."""
+def _cases():
+    out = []
+    for z in interp_zoo() + matrix_zoo():
+        out.append(pytest.param(*z, "interpreter", 37, id=z[0] + "-interpreter"))
+        out.append(pytest.param(*z, "specialised_kernels", 4099, id=z[0] + "-specialised_bulk"))
+        if z[0] in ("interp_1d_uneven_scalar_cubic", "interp_2d_mixed_cubic", "interp_3d_mixed_linear", "mat_inverse_3"):
+            out.append(pytest.param(*z, "specialised_kernels", 37, id=z[0] + "-specialised_short_range"))
+    return out
+
+
+@pytest.mark.parametrize("name,fun,gen,engine,nappl", _cases())
+def test_table_ops_on_device(name, fun, gen, engine, nappl, monkeypatch):
+    """Every table flavour (1-D .. 4-D, cubic / linear, even / uneven axes, scalar / vector data) and the matrix functions
+    (products, inverses with select-based pivoting) as an equality constraint
+    through each execution engine: the program interpreter (ASSET_B200_JIT=0: table pool in global memory), the
+    specialised kernels over a short range and over 4099 applications (bulk kernel + indexed ends; table as module data)."""
+    if engine == "interpreter":
+        monkeypatch.setenv("ASSET_B200_JIT", "0")
     rng = np.random.default_rng(23)
     ir, orr = fun.IRows(), fun.ORows()
     nlp = NonLinearProgram(ir * nappl, orr * nappl, 0)
@@ -49,8 +62,7 @@ def test_table_ops_on_device(name, fun, gen, nappl):
     out = nlp.evalKKT(1.0, X, LE, np.zeros(0))
     ref = oracle.Oracle.from_problem(nlp).eval("KKT", 1.0, X, LE, np.zeros(0), sc)
     check(out, ref, ("AGX", "FXE", "KKT"), name)
-    if nappl > 1000:
-        assert nlp.specialised_launches() > 0
+    assert (nlp.specialised_launches() == 0) == (engine == "interpreter")
 
 
 @pytest.mark.parametrize("name", sorted(table_phase_zoo()))

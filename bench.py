@@ -443,24 +443,42 @@ def run_b200(a):
                 # the phase's: upload only the ranges its functions read.  Checked here before it is timed: the device
                 # copy of the iterate is poisoned with NaN, then a sliced evaluation must reproduce the outputs of a
                 # full-upload evaluation bit for bit; otherwise the run falls back to the full upload and says so.
+                # Collectives (the cut-set reduce inside an evaluation) are entered by every rank or by none: each stage's
+                # verdict is agreed on across the ranks before the next stage starts.
+                def agreed(v):
+                    flag = torch.tensor([int(v)], device="cuda", dtype=torch.int32)
+                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                    return int(flag.item()) == 1
+                from asset_asrl_b200 import _lib as _ablib
+                host_call(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
+                nlp.sync()
+                want = [o.copy() for o in out]
                 ok = 0
-                try:
-                    host_call(EVAL_KKT, 1.0, hX, hLE, hLI, *out)
-                    nlp.sync()
-                    want = [o.copy() for o in out]
+                try:  # stage 1, rank-local: poison the device iterate, upload the slices
                     for nm in ("X", "LE", "LI"):
                         t = nlp.device_tensor(nm)
                         if t.numel():
                             t.fill_(float("nan"))
                     torch.cuda.synchronize()
-                    nlp.eval_host_sharded(EVAL_KKT, 1.0, hX, hLE, hLI, *out, compact=True, sliced=True)
+                    _ablib.check0(_ablib.lib.ab_plan_set_inputs_sliced(nlp.plan, _ablib.dptr(hX), _ablib.dptr(hLE), _ablib.dptr(hLI)))
                     nlp.sync()
-                    ok = int(all(np.array_equal(w_, o_) for w_, o_ in zip(want, out)))
+                    ok = 1
                 except Exception as e:  # noqa: BLE001 - any failure of the new path means: use the old one
                     upload_note = f"sliced upload failed ({type(e).__name__}: {e}); " + upload_note
-                flag = torch.tensor([ok], device="cuda", dtype=torch.int32)
-                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-                if int(flag.item()) == 1:
+                all_ok = agreed(ok)
+                if all_ok:  # stage 2, collective: evaluate on what was uploaded, read back, compare
+                    nlp.eval_device(EVAL_KKT, 1.0)
+                    ok = 0
+                    try:
+                        _ablib.check0(_ablib.lib.ab_plan_get_outputs_packed(nlp.plan, *[_ablib.dptr(out[k]) for k in (5, 1, 2, 3, 4, 0)]))
+                        nlp.sync()
+                        ok = int(all(np.array_equal(w_, o_) for w_, o_ in zip(want, out)))
+                    except Exception as e:  # noqa: BLE001
+                        upload_note = f"sliced upload check failed ({type(e).__name__}: {e}); " + upload_note
+                    all_ok = agreed(ok)
+                del want
+                flag_all = all_ok
+                if flag_all:
                     host_call = lambda *args: nlp.eval_host_sharded(*args, compact=True, sliced=True)  # noqa: E731
                     ir_ = nlp.input_ranges()
                     h2d = 8 * sum(hi - lo for rr in ir_.values() for (lo, hi) in rr)

@@ -117,20 +117,34 @@ def cpu_eval_rate(a, steps, warmup, full_size=False):
     """Oracle (CPU port of the reference evaluation) on a bounded sample of the same workload, all host threads: once
     with the IEEE build used for parity and once built with the reference's own flags (-O2 -march=native -ffast-math,
     CMakeLists.txt:55,:86,:160); the faster of the two is the reported value."""
-    import asset_asrl_b200  # noqa: F401  (problem set-up runs through the product's host code; no GPU call is made)
-    from asset_asrl_b200 import workloads as W
     import oracle
+    from oracle import standalone
     nseg = a.segments if full_size else min(a.cpu_segments, a.segments)
-    ph = W.make_phase(a.ode, a.mode, nseg, extras=not a.no_extras, control_mode=a.control_mode)
-    nlp = ph.transcribe()
-    X = ph.makeSolverInput()
-    LE, LI = W.multipliers(nlp)
+    # The problem is built without the product where the standalone builder covers the workload (oracle/standalone.py:
+    # layout and index maps from the independent restatement oracle/indexing.py, no libasset_b200.so in this process);
+    # tests/test_standalone_oracle.py shows the two builds agree bit for bit on pattern and input.  Otherwise (block-
+    # constant control, other ODEs) the product's host code transcribes the phase; no GPU call is made either way.
+    built_by = "oracle/standalone.py (independent of the product)"
+    if a.ode in standalone.SIZES and a.control_mode != "BlockConstant":
+        funcs, X_, dims = standalone.describe(a.ode, a.mode, nseg, control_mode=a.control_mode, extras=not a.no_extras)
+
+        def make():
+            return (standalone.instantiate(funcs, dims), X_) + standalone.multipliers(dims)
+    else:
+        import asset_asrl_b200  # noqa: F401
+        from asset_asrl_b200 import workloads as W
+        ph = W.make_phase(a.ode, a.mode, nseg, extras=not a.no_extras, control_mode=a.control_mode)
+        nlp = ph.transcribe()
+        built_by = "the product's host transcription, mirrored into the oracle"
+
+        def make():
+            return (oracle.Oracle.from_problem(nlp), ph.makeSolverInput()) + tuple(W.multipliers(nlp))
     threads = max(1, min(oracle.hardware_threads(), os.cpu_count() or 1))
     rates = {}
     for variant in ("ieee", "fast"):
         try:
             oracle.use_variant(variant)
-            orc = oracle.Oracle.from_problem(nlp)
+            orc, X, LE, LI = make()
         except Exception as e:  # no compiler on the box: the IEEE copy travels prebuilt, the native one may be missing
             rates[variant] = None
             sys.stderr.write(f"bench.py: oracle variant {variant} unavailable: {e}\n")
@@ -149,7 +163,7 @@ def cpu_eval_rate(a, steps, warmup, full_size=False):
     return {"value": nseg / t, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"{nseg} segments of {workload_name(a)} per step, {steps} timed evalKKT calls, "
                       f"{threads} threads over contiguous application chunks; oracle/oracle.cpp (reference binary unbuildable here); "
-                      "value = the faster of the two builds",
+                      f"value = the faster of the two builds; problem built by {built_by}",
             "segments_per_sec_ieee_build": nseg / rates["ieee"] if rates.get("ieee") else None,
             "segments_per_sec_reference_flags_build": nseg / rates["fast"] if rates.get("fast") else None,
             "segments": nseg, "ms_per_step": t * 1e3}

@@ -292,22 +292,30 @@ __global__ void __launch_bounds__(256) k_gather_large_final(const GatherDev g, c
 // ---------------------------------------------------------------------------------------------
 // host launchers (called from plan.cu)
 // ---------------------------------------------------------------------------------------------
-static int g_num_sms = 0;
+// per device (the C ABI lets one process hold plans on several devices): SM count, and the dynamic shared memory
+// k_eval_prog has been allowed so far (cudaFuncSetAttribute is a per-device setting)
+constexpr int MAX_DEVICES = 64;
+static int g_num_sms[MAX_DEVICES] = {0};
+static unsigned g_smem_configured[MAX_DEVICES] = {0};
+static int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return (dev >= 0 && dev < MAX_DEVICES) ? dev : 0;
+}
 static int num_sms() {
-  if (!g_num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
+  const int dev = current_device();
+  if (!g_num_sms[dev]) {
+    cudaDeviceGetAttribute(&g_num_sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms[dev] <= 0) g_num_sms[dev] = 148;
   }
-  return g_num_sms;
+  return g_num_sms[dev];
 }
 
 cudaError_t launch_eval(const FnDev& f, cudaStream_t st, const EvalIO& io) {
   const long long napp = (long long) f.app_end - f.app_begin;
   if (napp <= 0) return cudaSuccess;
   const ProgDev& P = f.prog;
-  static unsigned configured = 0;
+  unsigned& configured = g_smem_configured[current_device()];
   if (P.smem_bytes > configured) {
     cudaError_t e = cudaFuncSetAttribute(k_eval_prog, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) P.smem_bytes);
     if (e != cudaSuccess) return e;

@@ -185,6 +185,16 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_fused_residual_ptx(self.h, min_threads, mode, buf, n + 1))
         return buf.value.decode()
 
+    def fused_mode_ptx(self, mode, piece=0, min_threads=32):
+        """PTX of piece ``piece`` of the fused kernels of eval mode 1 (KKTNO), 2 (SOE), 3 (AUG) -- the partial-matrix
+        evaluations, same row blocks as the evalKKT pieces -- or 4..7 (piece 0); None past the last piece."""
+        n = _lib.check(lib.ab_problem_fused_mode_ptx(self.h, min_threads, mode, piece, None, 0))
+        if n == 0:
+            return None
+        buf = C.create_string_buffer(n + 1)
+        _lib.check(lib.ab_problem_fused_mode_ptx(self.h, min_threads, mode, piece, buf, n + 1))
+        return buf.value.decode()
+
     def kernel_ptx(self, f, mode=4, indexed=False):
         """PTX of the specialised kernel for function ``f``: the affine variant (None if the function has no affine
         application range) or the indexed variant that reads explicit index maps."""

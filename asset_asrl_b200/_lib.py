@@ -77,6 +77,7 @@ SIGNATURES = {
     "ab_problem_fused_info": (_ll, [_vp, _i, _llp, _cp, _ll]),
     "ab_problem_fused_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
     "ab_problem_fused_residual_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
+    "ab_problem_fused_mode_ptx": (_ll, [_vp, _i, _i, _i, _cp, _ll]),
     "ab_plan_create": (_i, [_vp, _i, C.POINTER(_vp)]),
     "ab_plan_destroy": (None, [_vp]),
     "ab_plan_create_sharded": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),

@@ -618,6 +618,22 @@ long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, in
     return fail(AB_ERR_INVALID, e.what());
   }
 }
+long long ab_problem_fused_mode_ptx(const ab_problem* p, int min_threads, int mode, int piece, char* buf, long long cap) {
+  try {
+    if (mode < 1 || mode > 7) return fail(AB_ERR_INVALID, "modes AB_EVAL_KKTNO .. AB_EVAL_OBJ (evalKKT: ab_problem_fused_ptx)");
+    FusedPlan fp = build_fused(p->p, min_threads);
+    if (!fp.ok || piece < 0 || piece >= (int) fp.residual[mode].size()) return 0;
+    const std::string s = fused_ptx(fp, piece, nullptr, nullptr, 0, mode);
+    if (buf && cap > 0) {
+      const size_t n = std::min<size_t>(s.size(), (size_t) cap - 1);
+      std::memcpy(buf, s.data(), n);
+      buf[n] = 0;
+    }
+    return (long long) s.size();
+  } catch (const std::exception& e) {
+    return fail(AB_ERR_INVALID, e.what());
+  }
+}
 long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap) {
   try {
     FusedPlan fp = build_fused(p->p, min_threads);

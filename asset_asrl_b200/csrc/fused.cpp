@@ -347,16 +347,22 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
   };
   const long long ks = F.ks;
   std::vector<std::vector<int>> kk((size_t) ks), ag((size_t) s), pg((size_t) s);
+  // what each contribution to a matrix entry is (parallel to kk): the partial-matrix modes sum a subset
+  enum : unsigned char { T_OBJ = 1, T_HESS = 2, T_SOLVER = 4 };
+  std::vector<std::vector<unsigned char>> kk_tag((size_t) ks);
   struct Extra {
     JitOut where;
     int node;
     int kind = 0;  // far_out: 0 matrix entry, 1 gradient entry, 2 objective value
     int role = 1;
+    unsigned char tag = 0;  // kind 0: T_OBJ / T_HESS
   };
   std::vector<Extra> fx_out, far_out;
   const long long SV = prob.niq;
-  for (long long j = 0; j < s; j++)  // solver-owned primal diagonal: first slot of the row
+  for (long long j = 0; j < s; j++) {  // solver-owned primal diagonal: first slot of the row
     kk[(size_t) (F.iref[(size_t) j] - F.kbr)].push_back(input(FA_STAGE, prob.stage_solver + SV + F.vbr + j, s));
+    kk_tag[(size_t) (F.iref[(size_t) j] - F.kbr)].push_back(T_SOLVER);
+  }
 
   std::map<int, ScalarFn> work;  // per function: lowered function with first and second derivatives
   for (const InstRef& q: F.insts) {
@@ -390,23 +396,25 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       return input(FA_APPC, FP.appc_offset[q.fi] + q.a_ref * fn.nappconst + k, (long long) q.m * fn.nappconst);
     });
     auto owned_var = [&](int i) { return q.vst[i] == s && q.v0[i] >= F.vbr && q.v0[i] < F.vbr + s; };
-    auto place = [&](int e, int row_in, int node) {
+    auto place = [&](int e, int row_in, int node, bool hess) {
+      const unsigned char tag = (unsigned char) ((fn.role == 0 ? T_OBJ : 0) | (hess ? T_HESS : 0));
       if (q.lst[e] == ks && q.l0[e] >= F.kbr && q.l0[e] < F.kbr + ks) {
         kk[(size_t) (q.l0[e] - F.kbr)].push_back(node);
+        kk_tag[(size_t) (q.l0[e] - F.kbr)].push_back(tag);
       } else if (q.home && q.vst[row_in] == 0) {
         // row of a variable no segment owns (parameters, the phase's end times): as in the per-function kernels
         if (q.d0[e] >= 0)
-          far_out.push_back({{FA_KKT, q.d0[e] + dlo * q.dst[e], q.dst[e]}, node, 0, fn.role});
+          far_out.push_back({{FA_KKT, q.d0[e] + dlo * q.dst[e], q.dst[e]}, node, 0, fn.role, tag});
         else
-          far_out.push_back({{FA_STAGE, ~q.d0[e] - dlo * q.dst[e], -q.dst[e]}, node, 0, fn.role});
+          far_out.push_back({{FA_STAGE, ~q.d0[e] - dlo * q.dst[e], -q.dst[e]}, node, 0, fn.role, tag});
       }
     };
     int e = 0;
     for (int i = 0; i < ir; i++) {
       if (lay_h)
-        for (int j = i; j < ir; j++, e++) place(e, q.v0[i] <= q.v0[j] ? i : j, cp(cf.hess[(size_t) j * ir + i]));
+        for (int j = i; j < ir; j++, e++) place(e, q.v0[i] <= q.v0[j] ? i : j, cp(cf.hess[(size_t) j * ir + i]), true);
       if (lay_j)
-        for (int k = 0; k < orr; k++, e++) place(e, i, cp(cf.jac[(size_t) k * ir + i]));
+        for (int k = 0; k < orr; k++, e++) place(e, i, cp(cf.jac[(size_t) k * ir + i]), false);
       const int g = cp(cf.grads[(size_t) i]);
       if (owned_var(i)) {
         (fn.role == 0 ? pg : ag)[(size_t) (q.v0[i] - F.vbr)].push_back(g);
@@ -459,7 +467,9 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
   fused.nin = (int) FP.fin.size();
   fused.nout = (int) recs.size();
   // pieces are blocks of whole owned rows; bnd holds the np+1 row boundaries
+  std::vector<long long> final_bnd;  // the row split the evalKKT pieces ended up with
   auto build_pieces = [&](const std::vector<long long>& bnd) {
+    final_bnd = bnd;
     const int np = (int) bnd.size() - 1;
     FP.pieces.assign((size_t) np, FusedPlan::Piece());
     std::vector<std::vector<ProgOut>> outs((size_t) np);
@@ -606,6 +616,56 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
     }
   } catch (const std::exception& ex) {
     for (auto& r: FP.residual) r.clear();  // the per-function kernels evaluate these modes
+  }
+  // Partial-matrix evaluations on the same threads and the same row blocks (evalKKTNO 1: everything but the objective;
+  // evalSOE 2: constraint values and Jacobians; evalAUG 3: Jacobians, both gradients, values -- NonLinearProgram.cpp:
+  // 540-666): every owned matrix entry is written, with the sum of the contributions the mode computes (the solver's
+  // diagonal coefficient always; zero if nothing is left).
+  try {
+    const int np = (int) final_bnd.size() - 1;
+    for (int mode = 1; mode <= 3 && np >= 1; mode++) {
+      const bool want_ag = mode == 1 || mode == 3, want_pg = mode == 3, want_val = mode == 3;
+      auto allowed = [&](unsigned char tag) {
+        if (tag & T_SOLVER) return true;
+        if (mode == 1) return !(tag & T_OBJ);
+        return !(tag & T_HESS) && !(tag & T_OBJ);  // Jacobians of the constraints only
+      };
+      std::vector<Rec> mrecs;
+      for (long long o = 0; o < ks; o++) {
+        int acc = -1;
+        for (size_t k = 0; k < kk[(size_t) o].size(); k++) {
+          if (!allowed(kk_tag[(size_t) o][k])) continue;
+          acc = acc < 0 ? kk[(size_t) o][k] : D.add(acc, kk[(size_t) o][k]);
+        }
+        if (acc < 0) acc = D.constant(0.0);
+        const long long row = (std::upper_bound(F.iref.begin(), F.iref.end(), F.kbr + o) - F.iref.begin()) - 1;
+        mrecs.push_back({{FA_KKT, FP.kb + o, ks}, acc, row});
+      }
+      for (const Extra& x: fx_out) mrecs.push_back({x.where, x.node, -1});
+      if (want_ag)
+        for (long long j = 0; j < s; j++)
+          if (!ag[(size_t) j].empty()) mrecs.push_back({{FA_AGX, FP.vb + j, s}, sum(ag[(size_t) j]), j});
+      if (want_pg)
+        for (long long j = 0; j < s; j++)
+          if (!pg[(size_t) j].empty()) mrecs.push_back({{FA_PGX, FP.vb + j, s}, sum(pg[(size_t) j]), j});
+      for (const Extra& x: far_out) {
+        if (x.kind == 0 && !allowed(x.tag)) continue;
+        if (x.kind == 1 && !(x.role == 0 ? want_pg : want_ag)) continue;
+        if (x.kind == 2 && !want_val) continue;
+        mrecs.push_back({x.where, x.node, -1});
+      }
+      std::vector<FusedPlan::Piece> pcs((size_t) np);
+      std::vector<std::vector<ProgOut>> outs((size_t) np);
+      for (const Rec& r: mrecs) {
+        const int pc = r.row < 0 ? np - 1 : (int) (std::upper_bound(final_bnd.begin() + 1, final_bnd.end() - 1, r.row) - final_bnd.begin()) - 1;
+        pcs[(size_t) pc].fout.push_back(r.where);
+        outs[(size_t) pc].push_back({r.node, PO_TABLE, (uint32_t) pcs[(size_t) pc].fout.size() - 1});
+      }
+      for (int pc = 0; pc < np; pc++) pcs[(size_t) pc].prog = emit_program_outs(fused, outs[(size_t) pc]);
+      FP.residual[mode] = std::move(pcs);
+    }
+  } catch (const std::exception& ex) {
+    for (int mode = 1; mode <= 3; mode++) FP.residual[mode].clear();
   }
   FP.ok = true;
   return FP;

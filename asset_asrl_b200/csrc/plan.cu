@@ -1345,10 +1345,22 @@ int Plan::enqueue(int mode, double obj_scale) {
   bool fused_eval = false;
   // the fused kernels evaluate evalKKT and -- single-device plans -- the residual-only modes of the line search
   const bool residual_mode = mode >= EM_RHS && mode <= EM_OBJ && world == 1 && !windowed && !getenv("ASSET_B200_NO_FUSED_RESIDUAL");
-  if ((mode == EM_KKT || residual_mode) && fused.ok) {
+  // The partial-matrix evaluations (evalKKTNO / SOE / AUG) on the fused threads: opt-in (ASSET_B200_FUSED_PARTIAL=1) until
+  // they have been run on a device -- written after the round's GPU time was spent; the kernels are checked on the CPU
+  // (tests/test_ptx_emulation.py), the GPU tests are tests/test_zz3_gpu_partial_modes.py.
+  const bool partial_mode = mode >= EM_KKTNO && mode <= EM_AUG && world == 1 && !windowed && getenv("ASSET_B200_FUSED_PARTIAL") != nullptr
+                            && std::atoi(getenv("ASSET_B200_FUSED_PARTIAL")) != 0;
+  if ((mode == EM_KKT || residual_mode || partial_mode) && fused.ok) {
     const int fr = ensure_fused(mode == EM_KKT ? 0 : mode);
     if (fr < 0) return -fr;
     fused_eval = fr > 0;
+  }
+  if (fused_eval && partial_mode && gkS.dev[0].ntargets + gkS.dev[1].ntargets > 0) {
+    // the entries that hold solver coefficients alone are not in the fused evaluation's gather lists (an evalKKT leaves
+    // them alone); the zero fill above cleared them
+    AB_CUDA(launch_gather(gkS.dev[0], gkS.dev[1], d_stage, d_kkt, d_gscratch, stream));
+    launches += (gkS.dev[0].ntargets > 0) + 2 * (gkS.dev[1].ntargets > 0);
+    solver_entries_valid = true;
   }
   const std::vector<JitKernel>& fjits = mode == EM_KKT ? fused_jits : fused_res_jits[mode & 7];
   if (windowed && !fused_eval) {

@@ -45,6 +45,8 @@ def parse_args():
                          "leg, the roofline bytes and e2e are evalKKT's and are skipped for the others)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--fused-partial", action="store_true",
+                    help="--eval KKTNO / SOE / AUG on the fused threads (ASSET_B200_FUSED_PARTIAL=1; opt-in until run on a device)")
     ap.add_argument("--full-upload", action="store_true",
                     help="windows sharding: upload the whole iterate on every rank each step instead of the rank's slice")
     ap.add_argument("--no-parity", action="store_true", help="skip the (untimed) oracle-window comparison before the timed region")
@@ -273,6 +275,8 @@ def run_b200(a):
     from asset_asrl_b200 import workloads as W
     from asset_asrl_b200 import Solvers as _S
     EVAL_KKT = getattr(_S, "EVAL_" + a.eval)  # the step's entry point (evalKKT unless --eval says otherwise)
+    if a.fused_partial:
+        os.environ["ASSET_B200_FUSED_PARTIAL"] = "1"
     if a.eval != "KKT":
         a.no_parity = a.no_e2e = True
 

@@ -173,6 +173,10 @@ long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, 
 /* ... of the residual-only fused kernel of an evaluation mode (AB_EVAL_RHS, _OGC, _OCC, _OBJ: the evaluations of PSIOPT's
  * line search, src/Solvers/PSIOPT.cpp:811-978); 0 if the mode has none. */
 long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, int mode, char* buf, long long cap);
+/* ... of piece `piece` of the fused kernels of any evaluation mode but evalKKT: the partial-matrix evaluations
+ * AB_EVAL_KKTNO, _SOE, _AUG (src/Solvers/NonLinearProgram.cpp:540-666; same row blocks as the evalKKT pieces, each owned
+ * matrix entry written with the contributions the mode computes) or a residual-only mode (piece 0); 0 if there is none. */
+long long ab_problem_fused_mode_ptx(const ab_problem* p, int min_threads, int mode, int piece, char* buf, long long cap);
 /* Rank-local analysis of one long phase (replaces the whole-problem pass of NonLinearProgram::analyzeSparsity,
  * /root/reference/src/Solvers/NonLinearProgram.cpp:267-344, by a pass over the rank's own segments).  Call between the
  * transcription and ab_problem_analyze: keeps, of every function, the applications whose lowest mesh variable lies in

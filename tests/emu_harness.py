@@ -35,7 +35,18 @@ def emulate_fused(nlp, X, LE, LI, sc, obj_scale, rels, residual_mode=None):
            "PGX": np.full(d["nvars"], nan), "AGX": np.full(d["nvars"], nan)}
     arrays = {0: np.asarray(X, dtype=np.float64), 1: np.asarray(LE, dtype=np.float64), 2: out["KKT"], 3: out["FXE"], 4: stage,
               5: appc, 6: np.asarray(LI, dtype=np.float64) if d["niq"] else np.zeros(1), 7: out["FXI"], 8: out["PGX"], 9: out["AGX"]}
-    ptxs = [nlp.fused_ptx(p) for p in range(int(info["pieces"]))] if residual_mode is None else [nlp.fused_residual_ptx(residual_mode)]
+    if residual_mode is None:
+        ptxs = [nlp.fused_ptx(p) for p in range(int(info["pieces"]))]
+    elif residual_mode >= 4:
+        ptxs = [nlp.fused_residual_ptx(residual_mode)]
+    else:  # partial-matrix modes: one kernel per row block, like evalKKT
+        ptxs = []
+        while True:
+            t = nlp.fused_mode_ptx(residual_mode, len(ptxs))
+            if t is None:
+                break
+            ptxs.append(t)
+        assert len(ptxs) == int(info["pieces"])
     for ptx in ptxs:
         k = Kernel(ptx)
         for rel in rels:

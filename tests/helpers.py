@@ -61,7 +61,7 @@ def expression_zoo():
 def matrix_zoo():
     """Matrix functions (MatrixFunctionBuild.cpp): views, products in every storage-order pairing, inverses of sizes 2..4
     (the 4 x 4 one with row exchanges), ParsedInput.  Kept apart from expression_zoo like interp_zoo (GPU tests in
-    tests/test_zz_gpu_tables.py)."""
+    tests/test_zz2_gpu_tables.py)."""
     A = vf.Arguments
     x4, x6, x9, x16 = A(4), A(6), A(9), A(16)
     z = []
@@ -109,7 +109,7 @@ def interp_tables():
 
 def interp_zoo():
     """Expression zoo entries over the tables (kept apart from expression_zoo so that the GPU tests of the table ops
-    live in a file of their own, tests/test_zz_gpu_tables.py)."""
+    live in a file of their own, tests/test_zz2_gpu_tables.py)."""
     A = vf.Arguments
     x3 = A(3)
     z = []

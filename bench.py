@@ -32,7 +32,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ode", default="lowthrust", choices=["lowthrust", "vanderpol", "hypersens", "brachistochrone"])
+    ap.add_argument("--ode", default="lowthrust", choices=["lowthrust", "vanderpol", "hypersens", "brachistochrone", "minclimb"])
     ap.add_argument("--mode", default="LGL5", choices=["LGL3", "LGL5", "LGL7", "Trapezoidal"])
     ap.add_argument("--segments", type=int, default=int(os.environ.get("AB_BENCH_SEGMENTS", 200000)),
                     help="mesh segments per GPU (weak scaling: each rank owns a contiguous range of the phase)")

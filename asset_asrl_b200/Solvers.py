@@ -185,6 +185,25 @@ class NonLinearProgram:
         _lib.check(lib.ab_problem_fused_residual_ptx(self.h, min_threads, mode, buf, n + 1))
         return buf.value.decode()
 
+    def fused_layout(self, min_threads=32):
+        """{"vb", "vs", "kb", "ks", "ex_lo", "ex_hi"} of the fused interior: owned variables / CSR slots per thread and, per
+        function, the applications the fused threads evaluate."""
+        nf = self.dims()["nfuncs"]
+        out = (C.c_longlong * 4)()
+        lo, hi = np.zeros(nf, dtype=np.int32), np.zeros(nf, dtype=np.int32)
+        _lib.check(lib.ab_problem_fused_layout(self.h, min_threads, out, lo.ctypes.data_as(_lib._ip), hi.ctypes.data_as(_lib._ip)))
+        return {"vb": int(out[0]), "vs": int(out[1]), "kb": int(out[2]), "ks": int(out[3]), "ex_lo": lo, "ex_hi": hi}
+
+    def dest_maps(self, f):
+        """(kkt_dest [nappl, E], f_dest [nappl, orows], first gradient staging slot, first objective-value staging slot)."""
+        fi = self.function_info(f)
+        E = (0 if fi["linear"] else fi["ir"] * (fi["ir"] + 1) // 2) + (fi["ir"] * fi["orows"] if fi["role"] else 0)
+        kd = np.zeros((fi["nappl"], E), dtype=np.int32)
+        fd = np.zeros((fi["nappl"], fi["orows"] if fi["role"] else 0), dtype=np.int32)
+        out = (C.c_longlong * 2)()
+        _lib.check(lib.ab_problem_dest_maps(self.h, f, kd.ctypes.data_as(_lib._ip), fd.ctypes.data_as(_lib._ip), out))
+        return kd, fd, int(out[0]), int(out[1])
+
     def fused_mode_ptx(self, mode, piece=0, min_threads=32):
         """PTX of piece ``piece`` of the fused kernels of eval mode 1 (KKTNO), 2 (SOE), 3 (AUG) -- the partial-matrix
         evaluations, same row blocks as the evalKKT pieces -- or 4..7 (piece 0); None past the last piece."""

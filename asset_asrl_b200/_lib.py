@@ -78,6 +78,8 @@ SIGNATURES = {
     "ab_problem_fused_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
     "ab_problem_fused_residual_ptx": (_ll, [_vp, _i, _i, _cp, _ll]),
     "ab_problem_fused_mode_ptx": (_ll, [_vp, _i, _i, _i, _cp, _ll]),
+    "ab_problem_fused_layout": (_i, [_vp, _i, _llp, _ip, _ip]),
+    "ab_problem_dest_maps": (_i, [_vp, _i, _ip, _ip, _llp]),
     "ab_plan_create": (_i, [_vp, _i, C.POINTER(_vp)]),
     "ab_plan_destroy": (None, [_vp]),
     "ab_plan_create_sharded": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),

@@ -602,6 +602,35 @@ long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long 
   }
 }
 
+int ab_problem_fused_layout(const ab_problem* p, int min_threads, long long out[4], int* ex_lo, int* ex_hi) {
+  AB_TRY
+  FusedPlan fp = build_fused(p->p, min_threads);
+  if (!fp.ok) return fail(AB_ERR_INVALID, "no fused interior: " + fp.why);
+  out[0] = fp.vb;
+  out[1] = fp.vs;
+  out[2] = fp.kb;
+  out[3] = fp.ks;
+  for (size_t f = 0; f < p->p.funcs.size(); f++) {
+    if (ex_lo) ex_lo[f] = fp.ex_lo[f];
+    if (ex_hi) ex_hi[f] = fp.ex_hi[f];
+  }
+  return AB_OK;
+  AB_CATCH
+}
+int ab_problem_dest_maps(const ab_problem* p, int f, int* kkt_dest, int* f_dest, long long out[2]) {
+  AB_TRY
+  const Problem& P = p->p;
+  if (!P.analyzed) return fail(AB_ERR_INVALID, "ab_problem_analyze() first");
+  const FuncRec& fr = P.funcs.at((size_t) f);
+  const long long nt = (long long) fr.nappl * fr.triplets_per_app();
+  if (kkt_dest) std::copy(P.kkt_dest.begin() + P.trip_base[(size_t) f], P.kkt_dest.begin() + P.trip_base[(size_t) f] + nt, kkt_dest);
+  if (f_dest && fr.role != 0)
+    std::copy(P.f_dest.begin() + P.fdest_base[(size_t) f], P.f_dest.begin() + P.fdest_base[(size_t) f] + (long long) fr.nappl * fr.orows, f_dest);
+  out[0] = P.g_stage.at((size_t) f);
+  out[1] = P.v_stage.at((size_t) f);
+  return AB_OK;
+  AB_CATCH
+}
 long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, int mode, char* buf, long long cap) {
   try {
     if (mode < 4 || mode > 7) return fail(AB_ERR_INVALID, "residual-only modes are AB_EVAL_RHS .. AB_EVAL_OBJ");

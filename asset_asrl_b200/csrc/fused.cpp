@@ -32,7 +32,14 @@ struct Finder {
   std::vector<long long> iref;  // indptr of the owned block's rows (vs + 1 entries) at t_ref
   std::string why;
 
-  explicit Finder(const Problem& p) : P(p) {}
+  // ASSET_B200_FUSED_BLOCKED=1: accept inputs that advance by a second stride (block-constant control); opt-in until run
+  // on a device (written after the round's GPU time was spent; tests/test_fused_flow_model.py checks the whole flow on
+  // the CPU, tests/test_zz4_gpu_blocked_fused.py on the device)
+  bool satellites = false;
+
+  explicit Finder(const Problem& p) : P(p) {
+    if (const char* e = getenv("ASSET_B200_FUSED_BLOCKED")) satellites = std::atoi(e) != 0;
+  }
 
   // stride of every input of application a of function fn per application step; false at the last application
   static bool strides(const FuncRec& fn, long long a, std::vector<long long>& st) {
@@ -66,6 +73,20 @@ struct Finder {
           if (s != 0 && x != s) mixed = true;
           s = x;
         }
+      if (mixed && satellites) {
+        // Block-constant control (Blocked_ODE_Wrapper.h:8-27, PhaseIndexer.cpp:373-391): the states advance by one stride,
+        // the per-segment controls -- stored in a block of their own behind all states -- by another.  The thread owns
+        // the states' block; the controls are *satellite* variables: read with their own stride, their rows and gradient
+        // entries written like those of the variables no segment owns (directly where an entry has one source, through
+        // the staging buffer and the gather lists otherwise).
+        long long vlow = -1;
+        for (int i = 0; i < an.ir; i++)
+          if (st[i] != 0 && (vlow < 0 || an.vindex[(size_t) t_ref * an.ir + i] < vlow)) {
+            vlow = an.vindex[(size_t) t_ref * an.ir + i];
+            s = st[i];
+          }
+        mixed = false;
+      }
       if (mixed) w = "inputs of " + an.name + " advance by different strides (block-constant control)";
       if (w.empty() && s <= 0) w = an.name + " does not advance through the variables";
       if (w.empty()) {
@@ -124,11 +145,21 @@ struct Finder {
       std::vector<long long> fs;
       if (!strides(fn, q.a_ref, fs)) return fail("a boundary application touches the interior block (" + fn.name + ")");
       long long sf = 0;
-      for (long long x: fs)
-        if (x != 0) {
-          if (sf != 0 && x != sf) return fail("inputs of " + fn.name + " advance by different strides");
-          sf = x;
-        }
+      if (satellites) {
+        // the stride of the lowest advancing variable (a state) counts; check() verifies every thread afterwards
+        long long vlow = -1;
+        for (int i = 0; i < fn.ir; i++)
+          if (fs[i] != 0 && (vlow < 0 || fn.vindex[(size_t) q.a_ref * fn.ir + i] < vlow)) {
+            vlow = fn.vindex[(size_t) q.a_ref * fn.ir + i];
+            sf = fs[i];
+          }
+      } else {
+        for (long long x: fs)
+          if (x != 0) {
+            if (sf != 0 && x != sf) return fail("inputs of " + fn.name + " advance by different strides");
+            sf = x;
+          }
+      }
       if (sf <= 0 || s % sf != 0) return fail("stride of " + fn.name + " does not divide the segment stride");
       q.m = (int) (s / sf);
       if (q.a_ref + q.m >= fn.nappl) return fail("template application at the end of " + fn.name);
@@ -149,7 +180,10 @@ struct Finder {
       long long vmin = -1, vmax = -1;
       for (int i = 0; i < fn.ir; i++)
         if (q.vst[i] != 0) {
-          if (q.vst[i] != s) return fail("input of " + fn.name + " does not follow the segment stride");
+          if (q.vst[i] != s) {
+            if (!satellites) return fail("input of " + fn.name + " does not follow the segment stride");
+            continue;  // a satellite variable: no part in where the application lives
+          }
           vmin = vmin < 0 ? q.v0[i] : std::min(vmin, q.v0[i]);
           vmax = std::max(vmax, q.v0[i]);
         }
@@ -401,8 +435,9 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       if (q.lst[e] == ks && q.l0[e] >= F.kbr && q.l0[e] < F.kbr + ks) {
         kk[(size_t) (q.l0[e] - F.kbr)].push_back(node);
         kk_tag[(size_t) (q.l0[e] - F.kbr)].push_back(tag);
-      } else if (q.home && q.vst[row_in] == 0) {
-        // row of a variable no segment owns (parameters, the phase's end times): as in the per-function kernels
+      } else if (q.home && q.vst[row_in] != s) {
+        // row of a variable no segment owns (parameters, the phase's end times; with ASSET_B200_FUSED_BLOCKED the
+        // per-segment controls, whose stride differs): as in the per-function kernels
         if (q.d0[e] >= 0)
           far_out.push_back({{FA_KKT, q.d0[e] + dlo * q.dst[e], q.dst[e]}, node, 0, fn.role, tag});
         else
@@ -418,7 +453,7 @@ FusedPlan build_fused(const Problem& prob, int min_threads, int npieces) {
       const int g = cp(cf.grads[(size_t) i]);
       if (owned_var(i)) {
         (fn.role == 0 ? pg : ag)[(size_t) (q.v0[i] - F.vbr)].push_back(g);
-      } else if (q.home && q.vst[i] == 0) {
+      } else if (q.home && q.vst[i] != s) {
         far_out.push_back({{FA_STAGE, prob.g_stage[q.fi] + (q.a_ref + q.m * dlo) * ir + i, (long long) q.m * ir}, g, 1, fn.role});
       }
     }

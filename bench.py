@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--fused-partial", action="store_true",
                     help="--eval KKTNO / SOE / AUG on the fused threads (ASSET_B200_FUSED_PARTIAL=1; opt-in until run on a device)")
+    ap.add_argument("--fused-blocked", action="store_true",
+                    help="--control-mode BlockConstant on the fused threads (ASSET_B200_FUSED_BLOCKED=1; opt-in until run on a device)")
     ap.add_argument("--full-upload", action="store_true",
                     help="windows sharding: upload the whole iterate on every rank each step instead of the rank's slice")
     ap.add_argument("--no-parity", action="store_true", help="skip the (untimed) oracle-window comparison before the timed region")
@@ -277,6 +279,8 @@ def run_b200(a):
     EVAL_KKT = getattr(_S, "EVAL_" + a.eval)  # the step's entry point (evalKKT unless --eval says otherwise)
     if a.fused_partial:
         os.environ["ASSET_B200_FUSED_PARTIAL"] = "1"
+    if a.fused_blocked:
+        os.environ["ASSET_B200_FUSED_BLOCKED"] = "1"
     if a.eval != "KKT":
         a.no_parity = a.no_e2e = True
 

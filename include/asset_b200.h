@@ -168,6 +168,15 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* static_p
  * per thread, of which home, distinct loads, outputs, FMAs over all pieces, number of pieces (kernels)}; `why` receives the
  * reason when the problem has no fused interior. */
 long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long out[12], char* why, long long cap);
+/* Layout of the fused interior (introspection for tests/test_fused_flow_model.py): out = {first owned variable, variables
+ * per thread, first owned CSR slot, slots per thread}; ex_lo / ex_hi (one entry per function, may be NULL): applications
+ * [ex_lo, ex_hi) are evaluated by the fused threads and skipped by the per-function path. */
+int ab_problem_fused_layout(const ab_problem* p, int min_threads, long long out[4], int* ex_lo, int* ex_hi);
+/* Destination maps of function `f` after ab_problem_analyze (the device analogue of KKTLocations / the RHS slot starts,
+ * src/Solvers/NonLinearProgram.cpp:318-335, src/VectorFunctions/IndexingData.h:96-115): per triplet and per constraint
+ * output, >= 0 the slot of the output array written directly, < 0 the complement of a staging slot summed by the gather
+ * lists; out = {first staging slot of the gradient contributions, of the objective-value contributions (-1: none)}. */
+int ab_problem_dest_maps(const ab_problem* p, int f, int* kkt_dest, int* f_dest, long long out[2]);
 /* PTX text of one piece of the fused evaluation (0 if there is none); buf == NULL only sizes. */
 long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap);
 /* ... of the residual-only fused kernel of an evaluation mode (AB_EVAL_RHS, _OGC, _OCC, _OBJ: the evaluations of PSIOPT's

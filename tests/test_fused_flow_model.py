@@ -25,7 +25,13 @@ from ref_assembly import tape_block_eval
 from asset_asrl_b200 import workloads as W
 
 
-def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
+def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale, mode=0):
+    """mode 0: evalKKT; 1 / 2 / 3: evalKKTNO / evalSOE / evalAUG on the fused threads (ASSET_B200_FUSED_PARTIAL): the value
+    array and the staging slots below the solver coefficients start from zero (Plan::enqueue), contributions the mode
+    does not compute are never written."""
+    with_obj = mode in (0, 3)          # objective functions are evaluated (gradient and value; Hessian only in evalKKT)
+    with_hess = mode in (0, 1)
+    with_grad = mode in (0, 1, 3)
     d = nlp.dims()
     info = nlp.fused_info()
     assert info["ok"], info["why"]
@@ -34,7 +40,7 @@ def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
     k_lo, k_hi = lay["kb"], lay["kb"] + R * lay["ks"]
     v_lo, v_hi = lay["vb"], lay["vb"] + R * lay["vs"]
     # 1. the fused threads
-    res = emulate_fused(nlp, X, LE, LI, sc, obj_scale, range(R))
+    res = emulate_fused(nlp, X, LE, LI, sc, obj_scale, range(R), residual_mode=mode or None)
     stage = res.pop("stage")
     out = {k: v.copy() for k, (v, _) in res.items()}
     direct_by_fused = {k: m.copy() for k, (_, m) in res.items()}
@@ -47,6 +53,8 @@ def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
         kd, fd, g_stage, v_stage = nlp.dest_maps(f)
         appc_all = nlp.function_appconst(f)
         L = LE if fi["role"] == 1 else LI
+        if fi["role"] == 0 and not with_obj:
+            continue
         for a in range(fi["nappl"]):
             if lay["ex_lo"][f] <= a < lay["ex_hi"][f]:
                 continue
@@ -54,10 +62,13 @@ def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
             fx, J, H = ev(f, fi, X[V[a]], lam, appc_all[a] if fi["nappconst"] else ())
             e = 0
             for i in range(fi["ir"]):
-                vals = ([H[j, i] for j in range(i, fi["ir"])] if not fi["linear"] else []) + ([J[k, i] for k in range(fi["orows"])] if fi["role"] else [])
-                for v in vals:
+                hess = [] if fi["linear"] else [(H[j, i], with_hess and (fi["role"] != 0 or mode == 0)) for j in range(i, fi["ir"])]
+                jac = [(J[k, i], True) for k in range(fi["orows"])] if fi["role"] else []
+                for v, computed in hess + jac:
                     dst = int(kd[a, e])
                     e += 1
+                    if not computed:
+                        continue
                     if dst < 0:
                         stage[~dst] = v
                     elif not (k_lo <= dst < k_hi):  # a fused thread's own entry is redirected away (Plan::kdF)
@@ -68,7 +79,8 @@ def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
                         out["KKT"][dst] = v
             g = J.T @ lam
             for i in range(fi["ir"]):
-                stage[g_stage + a * fi["ir"] + i] = g[i]
+                if with_grad:
+                    stage[g_stage + a * fi["ir"] + i] = g[i]
             if fi["role"] == 0:
                 stage[v_stage + a] = fx[0] * obj_scale
             else:
@@ -82,7 +94,11 @@ def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
     # 3. the gathers: everything outside the owned rows that has a list entry
     lists, _ = nlp.gather_lists()
     val = 0.0
+    produced = {0: ("KKT", "PGX", "AGX", "FXE", "FXI", "val"), 1: ("KKT", "AGX", "FXE", "FXI"), 2: ("KKT", "FXE", "FXI"),
+                3: ("KKT", "PGX", "AGX", "FXE", "FXI", "val")}[mode]
     for name, owned in (("KKT", (k_lo, k_hi)), ("PGX", (v_lo, v_hi)), ("AGX", (v_lo, v_hi)), ("FXE", None), ("FXI", None), ("val", None)):
+        if name not in produced:
+            continue
         for ptr, src, tgt in lists[name]:
             for t in range(tgt.size):
                 if owned is not None and owned[0] <= tgt[t] < owned[1]:
@@ -101,16 +117,19 @@ def model_fused_evalkkt(nlp, X, LE, LI, sc, obj_scale):
     return out
 
 
-def check(nlp, ph, tag):
+def check(nlp, ph, tag, mode=0):
     X = ph.makeSolverInput()
     LE, LI, sc = problem_inputs(nlp)
-    got = model_fused_evalkkt(nlp, X, LE, LI, sc, 0.7)
-    ref = oracle.Oracle.from_problem(nlp).eval("KKT", 0.7, X, LE, LI, sc)
-    for k in ("KKT", "FXE", "FXI", "PGX", "AGX"):
+    got = model_fused_evalkkt(nlp, X, LE, LI, sc, 0.7, mode)
+    name = ("KKT", "KKTNO", "SOE", "AUG")[mode]
+    ref = oracle.Oracle.from_problem(nlp).eval(name, 0.7, X, LE, LI, sc)
+    arrays = {0: ("KKT", "FXE", "FXI", "PGX", "AGX"), 1: ("KKT", "FXE", "FXI", "AGX"), 2: ("KKT", "FXE", "FXI"), 3: ("KKT", "FXE", "FXI", "PGX", "AGX")}[mode]
+    for k in arrays:
         if ref[k].size:
             scale = max(float(np.abs(ref[k]).max()), 1e-300)
-            assert float(np.abs(got[k] - ref[k]).max()) <= 1e-12 * scale, (tag, k)
-    assert abs(got["val"] - ref["val"]) <= 1e-12 * max(abs(ref["val"]), 1.0), tag
+            assert float(np.abs(got[k] - ref[k]).max()) <= 1e-12 * scale, (tag, name, k)
+    if mode in (0, 3):
+        assert abs(got["val"] - ref["val"]) <= 1e-12 * max(abs(ref["val"]), 1.0), (tag, name)
 
 
 @pytest.mark.parametrize("ode,mode,nseg,control", [("lowthrust", "LGL5", 44, None), ("vanderpol", "LGL3", 48, None),
@@ -154,3 +173,12 @@ def test_block_constant_control_other_modes_direct_outputs(mode, name, monkeypat
             scale = max(float(np.abs(ref[k]).max()), 1e-300)
             assert float(np.abs(v[m] - ref[k][m]).max()) <= 1e-12 * scale, (name, k)
     assert wrote > 0
+
+
+@pytest.mark.parametrize("mode", [1, 2, 3])
+@pytest.mark.parametrize("ode,tm,nseg,control", [("lowthrust", "LGL5", 44, None), ("vanderpol", "LGL3", 48, None)])
+def test_partial_matrix_modes_through_the_fused_flow(ode, tm, nseg, control, mode):
+    """evalKKTNO / evalSOE / evalAUG with their fused kernels (ASSET_B200_FUSED_PARTIAL): zero-filled value array and staging
+    slots, the mode's fused kernels, the mode's per-function programs at the mesh ends, the same gather lists."""
+    ph = W.make_phase(ode, tm, nseg, control_mode=control)
+    check(ph.transcribe(), ph, (ode, tm), mode)

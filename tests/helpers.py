@@ -164,6 +164,40 @@ def vdp_param_ode():
     return oc.ODEBase(vf.stack([x1, (1.0 - x0 * x0) * x1 * mu - x0 + u]), 2, 1, 1)
 
 
+def regions_phase(mode="LGL5", control_mode=None, nseg=6, accumulate=True):
+    rng = np.random.default_rng(7)
+    ode = vdp_param_ode()
+    S = (W.CARDINALS[mode] - 1) * nseg + 1
+    t = np.linspace(0.0, 2.0, S)
+    T = np.stack([np.cos(t), -np.sin(t), t, 0.1 * np.sin(2 * t), np.full(S, 0.8)], axis=1)
+    T[:, [0, 1, 3]] += 0.01 * rng.uniform(-1, 1, (S, 3))
+    ph = ode.phase(mode)
+    if control_mode:
+        ph.setControlMode(control_mode)
+    ph.setStaticParams([0.3, 1.7])
+    ph.setTraj(T, nseg)
+    A = vf.Arguments
+    ph.addBoundaryValue("Front", [0, 1, 2], T[0, :3])
+    ph.addEqualCon("Back", A(3).head2().squared_norm() - A(3)[2] * 0.1, [0, 1], [0], [])
+    ph.addEqualCon("FrontandBack", A(4)[0] * A(4)[2] - A(4)[1] * A(4)[3], [0, 1])
+    ph.addEqualCon("BackandFront", A(2)[0] - A(2)[1], [2])
+    ph.addInequalCon("Path", vf.sin(A(3)[0]) * A(3)[1] - A(3)[2], [0, 3], [], [1])
+    ph.addInequalCon("InnerPath", A(2).squared_norm() - 4.0, [0, 1])
+    ph.addInequalCon("NodalPath", A(2)[0] * A(2)[1] - 1.0, [1, 3])
+    ph.addInequalCon("PairWisePath", (A(4).head2() - A(4).tail2()).squared_norm() - 9.0, [0, 1])
+    ph.addEqualCon("StaticParams", A(2)[0] * A(2)[1] - 0.51, [], [], [0, 1])
+    ph.addEqualCon("ODEParams", vf.exp(A(1)[0]) - 2.2, [], [0], [])
+    ph.addLUVarBound("Path", 3, -1.0, 1.0, 2.0)
+    ph.addLUNormBound("Path", [0, 1], 0.01, 5.0)
+    ph.addIntegralObjective(A(2).squared_norm() * A(2)[0], [1, 3])
+    if accumulate:
+        ph.addIntegralParamFunction(A(1)[0] * A(1)[0], [3], 1)
+    ph.addStateObjective("Back", A(2)[0] * A(2)[1], [0, 2])
+    ph.addDeltaTimeObjective(0.5)
+    ph.addValueObjective("Front", 1, -1.0)
+    return ph
+
+
 def phase_zoo():
     """name -> builder returning a phase; small meshes, every region flag / transcription / control mode."""
     zoo = {}
@@ -176,42 +210,10 @@ def phase_zoo():
     zoo["lowthrust_LGL5_block_constant"] = lambda: W.make_phase("lowthrust", "LGL5", 6, control_mode="BlockConstant")
     zoo["lowthrust_LGL3_no_spline_defect_only"] = lambda: W.make_phase("lowthrust", "LGL3", 5, control_mode="NoSpline", extras=False)
 
-    def regions(mode="LGL5", control_mode=None, nseg=6):
-        rng = np.random.default_rng(7)
-        ode = vdp_param_ode()
-        S = (W.CARDINALS[mode] - 1) * nseg + 1
-        t = np.linspace(0.0, 2.0, S)
-        T = np.stack([np.cos(t), -np.sin(t), t, 0.1 * np.sin(2 * t), np.full(S, 0.8)], axis=1)
-        T[:, [0, 1, 3]] += 0.01 * rng.uniform(-1, 1, (S, 3))
-        ph = ode.phase(mode)
-        if control_mode:
-            ph.setControlMode(control_mode)
-        ph.setStaticParams([0.3, 1.7])
-        ph.setTraj(T, nseg)
-        A = vf.Arguments
-        ph.addBoundaryValue("Front", [0, 1, 2], T[0, :3])
-        ph.addEqualCon("Back", A(3).head2().squared_norm() - A(3)[2] * 0.1, [0, 1], [0], [])
-        ph.addEqualCon("FrontandBack", A(4)[0] * A(4)[2] - A(4)[1] * A(4)[3], [0, 1])
-        ph.addEqualCon("BackandFront", A(2)[0] - A(2)[1], [2])
-        ph.addInequalCon("Path", vf.sin(A(3)[0]) * A(3)[1] - A(3)[2], [0, 3], [], [1])
-        ph.addInequalCon("InnerPath", A(2).squared_norm() - 4.0, [0, 1])
-        ph.addInequalCon("NodalPath", A(2)[0] * A(2)[1] - 1.0, [1, 3])
-        ph.addInequalCon("PairWisePath", (A(4).head2() - A(4).tail2()).squared_norm() - 9.0, [0, 1])
-        ph.addEqualCon("StaticParams", A(2)[0] * A(2)[1] - 0.51, [], [], [0, 1])
-        ph.addEqualCon("ODEParams", vf.exp(A(1)[0]) - 2.2, [], [0], [])
-        ph.addLUVarBound("Path", 3, -1.0, 1.0, 2.0)
-        ph.addLUNormBound("Path", [0, 1], 0.01, 5.0)
-        ph.addIntegralObjective(A(2).squared_norm() * A(2)[0], [1, 3])
-        ph.addIntegralParamFunction(A(1)[0] * A(1)[0], [3], 1)
-        ph.addStateObjective("Back", A(2)[0] * A(2)[1], [0, 2])
-        ph.addDeltaTimeObjective(0.5)
-        ph.addValueObjective("Front", 1, -1.0)
-        return ph
-
     for mode in ("LGL3", "LGL5", "LGL7", "Trapezoidal"):
-        zoo[f"regions_{mode}"] = (lambda mode=mode: regions(mode))
-    zoo["regions_LGL5_block_constant"] = lambda: regions("LGL5", "BlockConstant")
-    zoo["regions_LGL7_highest_order_spline"] = lambda: regions("LGL7", "HighestOrderSpline")
+        zoo[f"regions_{mode}"] = (lambda mode=mode: regions_phase(mode))
+    zoo["regions_LGL5_block_constant"] = lambda: regions_phase("LGL5", "BlockConstant")
+    zoo["regions_LGL7_highest_order_spline"] = lambda: regions_phase("LGL7", "HighestOrderSpline")
 
     def ocp_multispacecraft(nphase=3, nseg=5):
         """Config 4 of BASELINE.json (examples/MultiSpacecraftOptimization.py:60-121): one BlockConstant LGL5 two-body

@@ -182,3 +182,18 @@ def test_partial_matrix_modes_through_the_fused_flow(ode, tm, nseg, control, mod
     slots, the mode's fused kernels, the mode's per-function programs at the mesh ends, the same gather lists."""
     ph = W.make_phase(ode, tm, nseg, control_mode=control)
     check(ph.transcribe(), ph, (ode, tm), mode)
+
+
+@pytest.mark.parametrize("mode,control,nseg", [("LGL5", None, 44), ("LGL7", "HighestOrderSpline", 40), ("LGL3", None, 48),
+                                               ("LGL5", "BlockConstant", 44), ("Trapezoidal", "BlockConstant", 48)])
+def test_every_region_flag_with_parameters_through_the_fused_flow(mode, control, nseg, monkeypatch):
+    """A phase with an ODE parameter, static parameters and functions over every region flag (helpers.regions_phase, without
+    its accumulation, which is not fusable by design): rows of parameters and of the end times are far rows of every
+    thread; with block-constant control the satellites join them."""
+    from helpers import regions_phase
+    if control == "BlockConstant":
+        monkeypatch.setenv("ASSET_B200_FUSED_BLOCKED", "1")
+    ph = regions_phase(mode, control, nseg, accumulate=False)
+    nlp = ph.transcribe()
+    assert nlp.fused_info()["ok"], nlp.fused_info()["why"]
+    check(nlp, ph, ("regions", mode, control))

@@ -48,3 +48,28 @@ def test_without_the_switch_block_constant_stays_on_the_per_function_path(monkey
     ph = W.make_phase("lowthrust", "LGL5", 400, control_mode="BlockConstant")
     nlp = ph.transcribe()
     assert not nlp.fused_info()["ok"]
+
+
+@pytest.mark.parametrize("mode,nseg", [("LGL5", 300), ("Trapezoidal", 400), ("LGL7", 200)])
+def test_block_constant_with_parameters_and_every_region_flag(mode, nseg, monkeypatch):
+    """ODE parameter, static parameters, functions over every region flag (helpers.regions_phase without its accumulation)."""
+    from helpers import regions_phase
+    monkeypatch.setenv("ASSET_B200_FUSED_BLOCKED", "1")
+    ph = regions_phase(mode, "BlockConstant", nseg, accumulate=False)
+    nlp = ph.transcribe()
+    assert nlp.fused_info()["ok"], nlp.fused_info()["why"]
+    X = ph.makeSolverInput()
+    LE, LI, sc = problem_inputs(nlp)
+    nlp.to_device(0)
+    nlp.set_solver_coeffs(sc)
+    orc = oracle.Oracle.from_problem(nlp)
+    for m, call in (("KKT", lambda: nlp.evalKKT(0.7, X, LE, LI)), ("RHS", lambda: nlp.evalRHS(0.7, X, LE, LI)),
+                    ("KKT", lambda: nlp.evalKKT(0.7, X, LE, LI))):
+        out = call()
+        ref = orc.eval(m, 0.7, X, LE, LI, sc)
+        for k in MODES[m]:
+            if k == "val":
+                assert abs(out["val"] - ref["val"]) <= TOL * max(abs(ref["val"]), 1.0), (mode, m, k)
+            else:
+                assert rel_err(out[k], ref[k]) < TOL, (mode, m, k, rel_err(out[k], ref[k]))
+    assert nlp.fused_segments() > 0

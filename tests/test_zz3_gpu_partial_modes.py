@@ -17,8 +17,7 @@ CASES = {
     "lowthrust_LGL5": lambda: W.make_phase("lowthrust", "LGL5", 400),
     "lowthrust_LGL7_highest_order_spline": lambda: W.make_phase("lowthrust", "LGL7", 300, control_mode="HighestOrderSpline"),
     "vanderpol_LGL3": lambda: W.make_phase("vanderpol", "LGL3", 500),
-    "hypersens_Trapezoidal": lambda: W.make_phase("hypersens", "Trapezoidal", 500),
-    "minclimb_LGL5": lambda: W.make_phase("minclimb", "LGL5", 300, control_mode="HighestOrderSpline"),
+    "minclimb_LGL3": lambda: W.make_phase("minclimb", "LGL3", 300),
 }
 
 

@@ -788,6 +788,41 @@ def _ascending(cs, what):
         raise ValueError(f"{what} Coordinates must be in ascending order")
 
 
+def _interval(cs, even, t):
+    """InterpTable*::get_*elems: truncating division on an evenly spaced axis, upper_bound otherwise; clamped."""
+    if even:
+        e = int((t - cs[0]) / (cs[1] - cs[0]))
+    else:
+        e = int(np.searchsorted(cs, t, side="right")) - 1
+    return max(min(e, cs.size - 2), 0)
+
+
+def _hermite_nd(axes, even, arrays, cubic, point):
+    """Host evaluation of the tensor-product interpolant the device programs implement (value only): ``arrays[b]`` holds
+    the derivative along every axis whose bit is set in b (cubic) or just the values (linear)."""
+    D = len(axes)
+    cell, weights = [], []
+    for d in range(D):
+        e = _interval(axes[d], even[d], float(point[d]))
+        h = axes[d][e + 1] - axes[d][e]
+        u = (float(point[d]) - axes[d][e]) / h
+        cell.append(e)
+        if cubic:
+            u2, u3 = u * u, u * u * u
+            weights.append((2 * u3 - 3 * u2 + 1, -2 * u3 + 3 * u2, (u3 - 2 * u2 + u) * h, (u3 - u2) * h))
+        else:
+            weights.append((1 - u, u))
+    total = 0.0
+    for fb in range(1 << D if cubic else 1):
+        for cb in range(1 << D):
+            idx = tuple(cell[d] + (cb >> d & 1) for d in range(D))
+            w = 1.0
+            for d in range(D):
+                w *= weights[d][((fb >> d & 1) << 1) | (cb >> d & 1)]
+            total += arrays[fb][idx] * w
+    return total
+
+
 class InterpTable1D:
     """vf.InterpTable1D(ts, Vs, axis=0, kind='cubic') (InterpTable1D.h:9-131): piecewise cubic-Hermite (slopes from
     five-point stencils) or linear interpolation of vector data over a scalar coordinate.  ``tab(f)`` with a scalar
@@ -924,7 +959,15 @@ class InterpTable2D:
                 raise ValueError("InterpTable2D: needs two scalar coordinates")
             f = self.vf().eval(xy)
             return ScalarFunction(f.node, f.ir, 1)
-        raise NotImplementedError("InterpTable2D on numbers: evaluate tab.vf() through the oracle or on the device")
+        xa, ya = np.asarray(x, dtype=np.float64), np.asarray(y, dtype=np.float64)
+        if xa.shape != ya.shape:
+            raise ValueError("InterpTable2D: x and y must have the same shape")
+        # host evaluation (InterpTable2D::interp, InterpTable2D.h:392-408); arrays are indexed [iy][ix]: axis order (y, x)
+        arrays = [self.zs] if self.kind else [self.zs, self.dzys, self.dzxs, self.dzys_dxs]
+        f = lambda a, b: _hermite_nd([self.ys, self.xs], [self.yeven, self.xeven], arrays, self.kind == 0, (b, a))  # noqa: E731
+        if xa.ndim == 0:
+            return f(float(xa), float(ya))
+        return np.vectorize(f)(xa, ya)
 
     interp = __call__
 
@@ -972,7 +1015,10 @@ class _InterpTableND:
         elif all(isinstance(x, VectorFunction) for x in xs):
             x = stack(list(xs))
         else:
-            raise NotImplementedError("InterpTableND on numbers: evaluate tab.vf() through the oracle or on the device")
+            pt = [float(v) for v in xs]
+            if len(pt) != self.D:
+                raise ValueError(f"InterpTable{self.D}D: needs {self.D} coordinates")
+            return _hermite_nd(self.axes, self.even, self.arrays, self.kind == 0, pt)  # host evaluation, value only
         if x.orows != self.D:
             raise ValueError(f"InterpTable{self.D}D: needs {self.D} scalar coordinates")
         f = self.vf().eval(x)

@@ -256,3 +256,20 @@ def test_interp_table_nd_known_answers(D):
         x = rng.uniform(lo, hi)
         fx, _, _, _ = _eval(lin.vf(), x, [1.0])
         assert abs(fx[0] - ref(x[None, :])[0]) < 1e-13
+
+
+def test_interp_tables_host_evaluation_matches_the_oracle():
+    """tab(x, y[, z[, w]]) on numbers (the reference's InterpTable*::interp) against the oracle's evaluation of tab.vf()."""
+    from helpers import interp_tables
+    rng = np.random.default_rng(9)
+    for nm, tab in interp_tables().items():
+        if nm.startswith("1d"):
+            continue
+        if nm.startswith("2d"):
+            lo, hi = np.array([tab.xs[0], tab.ys[0]]), np.array([tab.xs[-1], tab.ys[-1]])
+        else:
+            lo, hi = np.array([a[0] for a in tab.axes]), np.array([a[-1] for a in tab.axes])
+        for _ in range(5):
+            x = rng.uniform(lo, hi)
+            fx, _, _, _ = _eval(tab.vf(), x, [1.0])
+            assert abs(tab(*x) - fx[0]) <= 1e-13 * max(abs(fx[0]), 1.0), nm

@@ -356,7 +356,13 @@ def run_b200(a):
         for _ in range(50):
             nlp.eval_device(EVAL_KKT, 1.0)
         nlp.sync()
-        if len(clocks.lines) >= 3:
+        done = len(clocks.lines) >= 3
+        if world > 1:
+            # every evaluation of a sharded plan contains a collective: the ranks must leave this loop together
+            flag = torch.tensor([int(done)], device="cuda", dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            done = int(flag.item()) == 1
+        if done:
             break
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()

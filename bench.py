@@ -334,7 +334,12 @@ def run_b200(a):
     if not a.no_parity and (sharded or world == 1):
         parity = parity_check(nlp, ph, a.segments * (world if sharded else 1), world if sharded else 1, rank, X, LE, LI, sc,
                               dist if world > 1 else None, windows)
-        if parity is not None and not parity["max_rel"] < 1e-12:
+        bad = parity is not None and not parity["max_rel"] < 1e-12
+        if world > 1:  # rank 0 holds the verdict; every rank must stop, or the others wait in the next collective
+            flag = torch.tensor([int(bad)], device="cuda", dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+            bad = int(flag.item()) == 1
+        if bad:
             raise SystemExit(f"bench.py: the CUDA path differs from the oracle: {parity}")
     stream = torch.cuda.ExternalStream(nlp.stream(), device=local)
 

@@ -31,6 +31,7 @@
 #include <sstream>
 #include <stdexcept>
 #include <string>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -108,6 +109,9 @@ struct Node {
   std::vector<int> ip;
   std::vector<double> d;
   std::vector<std::unique_ptr<Node>> ch;
+  // interpolation tables: the stencil derivatives of the table data, computed on first use (they depend on the data only)
+  mutable std::vector<std::vector<double>> aux;
+  mutable std::once_flag aux_once;
 };
 
 struct Parser {
@@ -436,11 +440,12 @@ void Eval::outer(const Node& n, const Vec& Y, const std::vector<int>& off, doubl
       const double t = Y[0];
       const int e = interval_of(ts, nt, even, t);
       const double h = ts[e + 1] - ts[e], u = (t - ts[e]) / h;
-      Vec dv;
-      if (cubic) {  // slopes recomputed here (calc_derivs, :133-178), not taken from the description
-        dv.resize((size_t) vlen * nt);
-        for (int k = 0; k < vlen; k++) stencil_axis(ts, nt, vs + (size_t) k * nt, &dv[(size_t) k * nt], 1);
-      }
+      if (cubic)  // slopes recomputed here (calc_derivs, :133-178), not taken from the description
+        std::call_once(n.aux_once, [&]() {
+          n.aux.assign(1, Vec((size_t) vlen * nt));
+          for (int k = 0; k < vlen; k++) stencil_axis(ts, nt, vs + (size_t) k * nt, &n.aux[0][(size_t) k * nt], 1);
+        });
+      const Vec& dv = cubic ? n.aux[0] : n.d;
       double h2 = 0;
       for (int k = 0; k < vlen; k++) {
         const double v0 = vs[(size_t) k * nt + e], v1 = vs[(size_t) k * nt + e + 1];
@@ -475,12 +480,16 @@ void Eval::outer(const Node& n, const Vec& Y, const std::vector<int>& off, doubl
       double z, zx, zy, zxx, zxy, zyy;
       if (cubic) {
         const size_t plane = (size_t) nx * ny;
-        Vec dzx(plane), dzy(plane), dzxy(plane);  // calc_derivs (:122-211)
-        for (int c = 0; c < nx; c++) stencil_axis(ys, ny, zs + c, &dzy[c], nx);
-        for (int r = 0; r < ny; r++) {
-          stencil_axis(xs, nx, zs + (size_t) r * nx, &dzx[(size_t) r * nx], 1);
-          stencil_axis(xs, nx, &dzy[(size_t) r * nx], &dzxy[(size_t) r * nx], 1);
-        }
+        std::call_once(n.aux_once, [&]() {  // calc_derivs (:122-211)
+          n.aux.assign(3, Vec(plane));
+          Vec &ax_ = n.aux[0], &ay_ = n.aux[1], &axy_ = n.aux[2];
+          for (int c = 0; c < nx; c++) stencil_axis(ys, ny, zs + c, &ay_[c], nx);
+          for (int r = 0; r < ny; r++) {
+            stencil_axis(xs, nx, zs + (size_t) r * nx, &ax_[(size_t) r * nx], 1);
+            stencil_axis(xs, nx, &ay_[(size_t) r * nx], &axy_[(size_t) r * nx], 1);
+          }
+        });
+        const Vec &dzx = n.aux[0], &dzy = n.aux[1], &dzxy = n.aux[2];
         // Hermite patch in tensor form: sum over corners of value / x-slope / y-slope / twist times 1-D basis products;
         // the same polynomial as xvec^T (L Z R) yvec of get_amatrix (:253-298)
         auto basis = [](double s, double hh, double B[4], double D1[4], double D2[4]) {
@@ -605,19 +614,22 @@ void Eval::outer(const Node& n, const Vec& Y, const std::vector<int>& off, doubl
       }
       const double* vals = p;
       // mixed derivative arrays recomputed here by successive stencils (calc_derivs), lowest set axis last
-      std::vector<Vec> arr((size_t) (cubic ? 1 << D : 1));
-      arr[0].assign(vals, vals + cells);
-      if (cubic)
-        for (int b = 1; b < (1 << D); b++) {
-          int d = 0;
-          while (!((b >> d) & 1)) d++;  // differentiate arr[b without its lowest bit] along that axis
-          const Vec& src = arr[(size_t) (b & (b - 1))];
-          arr[(size_t) b].assign(cells, 0.0);
-          for (size_t base = 0; base < cells; base++) {
-            if ((base / stride[d]) % (size_t) nn[d] != 0) continue;  // first element of each line along axis d
-            stencil_axis(ax[d], nn[d], &src[base], &arr[(size_t) b][base], stride[d]);
+      std::call_once(n.aux_once, [&]() {
+        n.aux.assign((size_t) (cubic ? 1 << D : 1), Vec());
+        n.aux[0].assign(vals, vals + cells);
+        if (cubic)
+          for (int b = 1; b < (1 << D); b++) {
+            int d = 0;
+            while (!((b >> d) & 1)) d++;  // differentiate the array without b's lowest bit along that axis
+            const Vec& src = n.aux[(size_t) (b & (b - 1))];
+            n.aux[(size_t) b].assign(cells, 0.0);
+            for (size_t base = 0; base < cells; base++) {
+              if ((base / stride[d]) % (size_t) nn[d] != 0) continue;  // first element of each line along axis d
+              stencil_axis(ax[d], nn[d], &src[base], &n.aux[(size_t) b][base], stride[d]);
+            }
           }
-        }
+      });
+      const std::vector<Vec>& arr = n.aux;
       double B[4][4], D1[4][4], D2[4][4];
       size_t cell = 0;
       for (int d = 0; d < D; d++) {

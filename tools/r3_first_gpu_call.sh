@@ -15,3 +15,7 @@ python bench.py --steps 20 --warmup 5 --control-mode BlockConstant --no-cpu > gp
 python bench.py --steps 20 --warmup 5 --control-mode BlockConstant --fused-blocked --no-cpu > gpurun_out/r3_bench_blocked_fused.json
 python bench.py --steps 10 --warmup 3 --ode minclimb --no-cpu > gpurun_out/r3_bench_minclimb.json
 python bench.py --steps 10 --warmup 3 --segments 1000000 --no-cpu > gpurun_out/r3_bench_one_million_segments.json
+# In a call of its own (gpurun --gpus 8): the north-star line -- one 1.6 M-segment phase over eight GPUs, rank-local analysis,
+# sliced upload -- which has never completed (host analysis size, then the per-rank exit of the warm loop):
+#   gpurun --gpus 8 --timeout 1500 -- 'python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+#       --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 5 > gpurun_out/r3_bench_eight_gpus.json 2> gpurun_out/r3_bench_eight_gpus.err'

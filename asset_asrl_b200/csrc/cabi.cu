@@ -20,7 +20,27 @@ struct ab_graph {
 };
 struct ab_problem {
   Problem p;
+  // the introspection entry points (ab_problem_fused_*) ask for the same fused plan again and again; keep the last one.
+  // Keyed by everything build_fused reads besides the problem: min_threads, the function count / analysis state and the
+  // ASSET_B200_FUSED_* switches.
+  mutable std::shared_ptr<FusedPlan> fused_cache;
+  mutable std::string fused_key;
 };
+static const FusedPlan& cached_fused(const ab_problem* p, int min_threads) {
+  std::string key = std::to_string(min_threads) + "/" + std::to_string(p->p.funcs.size()) + "/" + std::to_string(p->p.nnz()) + "/"
+                    + std::to_string((int) p->p.analyzed) + "/" + std::to_string((int) p->p.win.on);
+  for (const char* v: {"ASSET_B200_FUSED_BLOCKED", "ASSET_B200_FUSED_PIECES", "ASSET_B200_FUSED_SLOTS", "ASSET_B200_FUSED_EVEN_SPLIT",
+                       "ASSET_B200_FUSED_BALANCE", "ASSET_B200_FUSED_DIRECT", "ASSET_B200_FUSED_REGS", "ASSET_B200_FUSED_REGS_BY_PIECE",
+                       "ASSET_B200_FUSED_ZRUN", "ASSET_B200_FUSED_THREADS", "ASSET_B200_JIT_REGS", "ASSET_B200_JIT_DEBUG"}) {
+    const char* e = getenv(v);
+    key += std::string("/") + (e ? e : "-");
+  }
+  if (!p->fused_cache || p->fused_key != key) {
+    p->fused_cache = std::make_shared<FusedPlan>(build_fused(p->p, min_threads));
+    p->fused_key = key;
+  }
+  return *p->fused_cache;
+}
 struct ab_phase {
   Phase ph;
 };
@@ -574,7 +594,7 @@ int ab_phase_make_input(ab_phase* ph, const double* traj, const double* sp, doub
 // ------------------------------------------------------------------ fused interior (host side; no GPU needed)
 long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long out[12], char* why, long long cap) {
   try {
-    FusedPlan fp = build_fused(p->p, min_threads);
+    const FusedPlan& fp = cached_fused(p, min_threads);
     out[0] = fp.ok ? 1 : 0;
     out[1] = fp.anchor;
     out[2] = fp.t_lo;
@@ -604,7 +624,7 @@ long long ab_problem_fused_info(const ab_problem* p, int min_threads, long long 
 
 int ab_problem_fused_layout(const ab_problem* p, int min_threads, long long out[4], int* ex_lo, int* ex_hi) {
   AB_TRY
-  FusedPlan fp = build_fused(p->p, min_threads);
+  const FusedPlan& fp = cached_fused(p, min_threads);
   if (!fp.ok) return fail(AB_ERR_INVALID, "no fused interior: " + fp.why);
   out[0] = fp.vb;
   out[1] = fp.vs;
@@ -634,7 +654,7 @@ int ab_problem_dest_maps(const ab_problem* p, int f, int* kkt_dest, int* f_dest,
 long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, int mode, char* buf, long long cap) {
   try {
     if (mode < 4 || mode > 7) return fail(AB_ERR_INVALID, "residual-only modes are AB_EVAL_RHS .. AB_EVAL_OBJ");
-    FusedPlan fp = build_fused(p->p, min_threads);
+    const FusedPlan& fp = cached_fused(p, min_threads);
     if (!fp.ok || fp.residual[mode].empty()) return 0;
     const std::string s = fused_ptx(fp, 0, nullptr, nullptr, 0, mode);
     if (buf && cap > 0) {
@@ -650,7 +670,7 @@ long long ab_problem_fused_residual_ptx(const ab_problem* p, int min_threads, in
 long long ab_problem_fused_mode_ptx(const ab_problem* p, int min_threads, int mode, int piece, char* buf, long long cap) {
   try {
     if (mode < 1 || mode > 7) return fail(AB_ERR_INVALID, "modes AB_EVAL_KKTNO .. AB_EVAL_OBJ (evalKKT: ab_problem_fused_ptx)");
-    FusedPlan fp = build_fused(p->p, min_threads);
+    const FusedPlan& fp = cached_fused(p, min_threads);
     if (!fp.ok || piece < 0 || piece >= (int) fp.residual[mode].size()) return 0;
     const std::string s = fused_ptx(fp, piece, nullptr, nullptr, 0, mode);
     if (buf && cap > 0) {
@@ -665,7 +685,7 @@ long long ab_problem_fused_mode_ptx(const ab_problem* p, int min_threads, int mo
 }
 long long ab_problem_fused_ptx(const ab_problem* p, int min_threads, int piece, char* buf, long long cap) {
   try {
-    FusedPlan fp = build_fused(p->p, min_threads);
+    const FusedPlan& fp = cached_fused(p, min_threads);
     if (!fp.ok || piece < 0 || piece >= (int) fp.pieces.size()) return 0;
     const std::string s = fused_ptx(fp, piece, nullptr, nullptr);
     if (buf && cap > 0) {
